@@ -1,0 +1,20 @@
+"""aligner_b200 — B200-native replacement for aligner-core's pairwise alignment hot path.
+
+Host-side mirror of the reference API (``SimpleGlobalAligner``, ``SimpleLocalAligner``,
+``Heuristics``, ``Alignment``, ``AlignmentResult``, ``Protein``, ``DNA``, ``get_blosum62``) over the
+C-ABI CUDA library ``libaligner_b200.so`` (include/aligner_b200.h).  No CPU fallback exists.
+"""
+from . import _native
+from ._native import AlignerError, GLOBAL, LOCAL, NUM_AUTO, NUM_F64, NUM_I16X2, NUM_I32
+from .aligners import (Alignment, AlignmentResult, Heuristics, SimpleGlobalAligner,
+                       SimpleLocalAligner)
+from .batch import BatchResult, DeviceBatch, PackedPairs, align_batch
+from .enums import DNA, Direction, Error, Protein
+from .matrices import dna_matrix, get_blosum62
+
+__all__ = [
+    "AlignerError", "Alignment", "AlignmentResult", "BatchResult", "DNA", "DeviceBatch", "Direction",
+    "Error", "GLOBAL", "Heuristics", "LOCAL", "NUM_AUTO", "NUM_F64", "NUM_I16X2", "NUM_I32",
+    "PackedPairs", "Protein", "SimpleGlobalAligner", "SimpleLocalAligner", "align_batch",
+    "dna_matrix", "get_blosum62",
+]

@@ -1,0 +1,104 @@
+"""ctypes binding of include/aligner_b200.h (the C-ABI shared library).
+
+The library is built in-tree by ``__graft_entry__.build()`` (``make -C aligner_b200/csrc``).
+There is no CPU fallback: if the library is missing, loading raises; if no CUDA device is
+usable, every compute call returns ``ALNR_CUDA_ERROR`` and the wrappers raise.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libaligner_b200.so")
+
+OK = 0
+STATUS_NAMES = {
+    0: "OK", 1: "ProteinNotFound", 2: "CharIsNotMatchable", 3: "UnnecessaryArgument",
+    4: "MissingArgument", 5: "ResultIsEmpty", 6: "CalculationError", 7: "ValidationError",
+    8: "MatrixShapeError", 9: "WrongMatrixSpecified", 10: "EmptyInput", 11: "NoPositiveCell",
+    12: "SymbolOutOfRange", 13: "CudaError", 14: "InvalidArgument", 15: "OutOfMemory",
+}
+GLOBAL, LOCAL = 0, 1
+NUM_AUTO, NUM_I16X2, NUM_I32, NUM_F64 = 0, 1, 2, 3
+
+u8p = C.POINTER(C.c_uint8)
+u32p = C.POINTER(C.c_uint32)
+u64p = C.POINTER(C.c_uint64)
+i32p = C.POINTER(C.c_int32)
+f64p = C.POINTER(C.c_double)
+
+
+class Params(C.Structure):
+    _fields_ = [("mode", C.c_int), ("volume", C.c_int), ("del_", C.c_double), ("ext", C.c_double),
+                ("matrix", f64p), ("device", C.c_int), ("numeric", C.c_int)]
+
+
+class PairResult(C.Structure):
+    _fields_ = [("f", C.c_double), ("corner_score", C.c_double), ("coords", C.c_uint64 * 4),
+                ("q_aln", u8p), ("t_aln", u8p), ("aln_len", C.c_uint64), ("H", f64p), ("D", u8p),
+                ("numeric", C.c_int)]
+
+
+class Batch(C.Structure):
+    _fields_ = [("q", u8p), ("q_off", u64p), ("t", u8p), ("t_off", u64p), ("count", C.c_uint64)]
+
+
+class BatchOut(C.Structure):
+    _fields_ = [("f", f64p), ("corner", f64p), ("coords", u64p), ("aln_off", u64p),
+                ("aln_len", u32p), ("q_aln", u8p), ("t_aln", u8p), ("status", i32p)]
+
+
+# every symbol include/aligner_b200.h declares: name -> (restype, argtypes)
+SIGNATURES = {
+    "alnr_strerror": (C.c_char_p, [C.c_int]),
+    "alnr_last_error_detail": (C.c_char_p, []),
+    "alnr_device_count": (C.c_int, []),
+    "alnr_build_info": (C.c_char_p, []),
+    "alnr_kernel_launch_count": (C.c_uint64, []),
+    "alnr_align_pair": (C.c_int, [C.POINTER(Params), u8p, C.c_uint64, u8p, C.c_uint64, C.c_int,
+                                  C.POINTER(PairResult)]),
+    "alnr_free_pair_result": (None, [C.POINTER(PairResult)]),
+    "alnr_align_batch": (C.c_int, [C.POINTER(Params), C.POINTER(Batch), C.POINTER(BatchOut)]),
+    "alnr_batch_create": (C.c_int, [C.POINTER(Params), C.POINTER(Batch), C.POINTER(C.c_void_p)]),
+    "alnr_batch_run": (C.c_int, [C.c_void_p]),
+    "alnr_batch_sync": (C.c_int, [C.c_void_p]),
+    "alnr_batch_download": (C.c_int, [C.c_void_p, C.POINTER(BatchOut)]),
+    "alnr_batch_stream": (C.c_void_p, [C.c_void_p]),
+    "alnr_batch_run_timed": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
+    "alnr_batch_numeric": (C.c_int, [C.c_void_p]),
+    "alnr_batch_rerun_count": (C.c_uint64, [C.c_void_p]),
+    "alnr_batch_destroy": (None, [C.c_void_p]),
+    "alnr_host_alloc": (C.c_void_p, [C.c_uint64]),
+    "alnr_host_free": (None, [C.c_void_p]),
+}
+
+_lib = None
+
+
+class AlignerError(RuntimeError):
+    def __init__(self, status, detail=""):
+        self.status = status
+        self.name = STATUS_NAMES.get(status, "status %d" % status)
+        super().__init__("%s%s" % (self.name, (": " + detail) if detail else ""))
+
+
+def lib():
+    """Load (once) and return the C-ABI library; raises if it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(
+                "%s is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                "(the CUDA extension is mandatory; there is no CPU fallback)" % LIB_PATH)
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(L, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = L
+    return _lib
+
+
+def check(status):
+    if status != OK:
+        detail = lib().alnr_last_error_detail()
+        raise AlignerError(status, detail.decode() if detail and status in (13, 14, 15) else "")

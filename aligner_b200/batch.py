@@ -1,0 +1,163 @@
+"""Batched alignment of independent pairs over the C ABI (alnr_align_batch / alnr_batch_*).
+
+The reference aligns batches by looping ``perform_alignment`` on OS threads
+(aligner-core/src/statistics/mod.rs:255-286; latent-repeat-search/engine/calc.rs:47-69);
+here one call hands the whole batch to the GPU.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _native as N
+
+
+class PackedPairs:
+    """Concatenated symbol codes + uint64 offsets for queries and targets."""
+
+    def __init__(self, q, q_off, t, t_off):
+        self.q = np.ascontiguousarray(q, dtype=np.uint8)
+        self.t = np.ascontiguousarray(t, dtype=np.uint8)
+        self.q_off = np.ascontiguousarray(q_off, dtype=np.uint64)
+        self.t_off = np.ascontiguousarray(t_off, dtype=np.uint64)
+        self.count = len(self.q_off) - 1
+        assert len(self.t_off) == self.count + 1
+
+    @classmethod
+    def from_lists(cls, queries, targets):
+        assert len(queries) == len(targets)
+        qo = np.zeros(len(queries) + 1, dtype=np.uint64)
+        to = np.zeros(len(targets) + 1, dtype=np.uint64)
+        qo[1:] = np.cumsum([len(x) for x in queries])
+        to[1:] = np.cumsum([len(x) for x in targets])
+        cat = lambda xs: (np.concatenate([np.asarray(x, dtype=np.uint8) for x in xs])
+                          if len(xs) else np.zeros(0, dtype=np.uint8))
+        return cls(cat(queries), qo, cat(targets), to)
+
+    @classmethod
+    def uniform(cls, q2d, t2d):
+        """count x n and count x m code arrays (all pairs the same shape)."""
+        q2d = np.ascontiguousarray(q2d, dtype=np.uint8)
+        t2d = np.ascontiguousarray(t2d, dtype=np.uint8)
+        c, n = q2d.shape
+        m = t2d.shape[1]
+        return cls(q2d.reshape(-1), np.arange(c + 1, dtype=np.uint64) * np.uint64(n),
+                   t2d.reshape(-1), np.arange(c + 1, dtype=np.uint64) * np.uint64(m))
+
+    def pair(self, i):
+        return (self.q[int(self.q_off[i]):int(self.q_off[i + 1])],
+                self.t[int(self.t_off[i]):int(self.t_off[i + 1])])
+
+    def cells(self):
+        n = np.diff(self.q_off).astype(np.float64)
+        m = np.diff(self.t_off).astype(np.float64)
+        return float((n * m).sum())
+
+    def aln_capacity(self):
+        return int(self.q_off[-1]) + int(self.t_off[-1]) + self.count
+
+    def c_struct(self):
+        return N.Batch(self.q.ctypes.data_as(N.u8p), self.q_off.ctypes.data_as(N.u64p),
+                       self.t.ctypes.data_as(N.u8p), self.t_off.ctypes.data_as(N.u64p), self.count)
+
+
+class BatchResult:
+    """Host-side outputs of one batched call (numpy arrays; alignments are slices)."""
+
+    def __init__(self, pairs, want_alignments=True):
+        c = pairs.count
+        self.count = c
+        self.f = np.zeros(c, dtype=np.float64)
+        self.corner = np.zeros(c, dtype=np.float64)
+        self.coords = np.zeros((c, 4), dtype=np.uint64)
+        self.aln_off = np.zeros(c, dtype=np.uint64)
+        self.aln_len = np.zeros(c, dtype=np.uint32)
+        self.status = np.zeros(c, dtype=np.int32)
+        cap = pairs.aln_capacity() if want_alignments else 0
+        self.q_aln = np.zeros(cap, dtype=np.uint8) if want_alignments else None
+        self.t_aln = np.zeros(cap, dtype=np.uint8) if want_alignments else None
+
+    def c_struct(self):
+        ptr = lambda a, ty: a.ctypes.data_as(ty) if a is not None else ty()
+        return N.BatchOut(ptr(self.f, N.f64p), ptr(self.corner, N.f64p), ptr(self.coords, N.u64p),
+                          ptr(self.aln_off, N.u64p), ptr(self.aln_len, N.u32p),
+                          ptr(self.q_aln, N.u8p), ptr(self.t_aln, N.u8p), ptr(self.status, N.i32p))
+
+    def alignment(self, i):
+        o, l = int(self.aln_off[i]), int(self.aln_len[i])
+        return self.q_aln[o:o + l], self.t_aln[o:o + l]
+
+    def bytes_out(self):
+        arrs = [self.f, self.corner, self.coords, self.aln_off, self.aln_len, self.status,
+                self.q_aln, self.t_aln]
+        return int(sum(a.nbytes for a in arrs if a is not None))
+
+
+def make_params(mode, matrix, del_, ext, device=-1, numeric=N.NUM_AUTO):
+    mat = np.ascontiguousarray(matrix, dtype=np.float64)
+    assert mat.ndim == 2 and mat.shape[0] == mat.shape[1]
+    p = N.Params(mode, mat.shape[0], float(del_), float(ext), mat.ctypes.data_as(N.f64p), device, numeric)
+    p._keep = mat  # keep the matrix alive as long as the struct
+    return p
+
+
+def align_batch(mode, pairs, matrix, del_, ext, device=-1, numeric=N.NUM_AUTO, want_alignments=True,
+                out=None):
+    """Host buffers in -> host buffers out (alnr_align_batch)."""
+    p = make_params(mode, matrix, del_, ext, device, numeric)
+    res = out if out is not None else BatchResult(pairs, want_alignments)
+    b = pairs.c_struct()
+    o = res.c_struct()
+    N.check(N.lib().alnr_align_batch(C.byref(p), C.byref(b), C.byref(o)))
+    return res
+
+
+class DeviceBatch:
+    """Device-resident batch: upload once, run many times (alnr_batch_*)."""
+
+    def __init__(self, mode, pairs, matrix, del_, ext, device=-1, numeric=N.NUM_AUTO):
+        self.pairs = pairs
+        self._p = make_params(mode, matrix, del_, ext, device, numeric)
+        self._h = C.c_void_p()
+        b = pairs.c_struct()
+        N.check(N.lib().alnr_batch_create(C.byref(self._p), C.byref(b), C.byref(self._h)))
+
+    def run(self):
+        N.check(N.lib().alnr_batch_run(self._h))
+
+    def sync(self):
+        N.check(N.lib().alnr_batch_sync(self._h))
+
+    def run_timed(self):
+        """One pass between CUDA events on the batch's own stream -> (total ms, fill ms)."""
+        ms, fill = C.c_float(), C.c_float()
+        N.check(N.lib().alnr_batch_run_timed(self._h, C.byref(ms), C.byref(fill)))
+        return ms.value, fill.value
+
+    def download(self, want_alignments=True, out=None):
+        res = out if out is not None else BatchResult(self.pairs, want_alignments)
+        o = res.c_struct()
+        N.check(N.lib().alnr_batch_download(self._h, C.byref(o)))
+        return res
+
+    @property
+    def numeric(self):
+        return N.lib().alnr_batch_numeric(self._h)
+
+    @property
+    def rerun_count(self):
+        return N.lib().alnr_batch_rerun_count(self._h)
+
+    @property
+    def stream(self):
+        return N.lib().alnr_batch_stream(self._h)
+
+    def close(self):
+        if self._h:
+            N.lib().alnr_batch_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -1,0 +1,158 @@
+// api.cu — the extern "C" boundary declared in include/aligner_b200.h.
+#include <cstdlib>
+#include <cstring>
+#include <new>
+
+#include "batch.h"
+
+namespace alnr { const char *get_error_detail(); }
+using alnr::alnr_batch_impl;
+
+struct alnr_batch_handle {
+  alnr_batch_impl impl;
+};
+
+extern "C" {
+
+const char *alnr_strerror(int status) {
+  switch (status) {
+    case ALNR_OK: return "ok";
+    case ALNR_PROTEIN_NOT_FOUND: return "ProteinNotFound";
+    case ALNR_CHAR_IS_NOT_MATCHABLE: return "CharIsNotMatchable";
+    case ALNR_UNNECESSARY_ARGUMENT: return "UnnecessaryArgument";
+    case ALNR_MISSING_ARGUMENT: return "MissingArgument";
+    case ALNR_RESULT_IS_EMPTY: return "ResultIsEmpty";
+    case ALNR_CALCULATION_ERROR: return "CalculationError";
+    case ALNR_VALIDATION_ERROR: return "ValidationError";
+    case ALNR_MATRIX_SHAPE_ERROR: return "MatrixShapeError";
+    case ALNR_WRONG_MATRIX: return "WrongMatrixSpecified";
+    case ALNR_EMPTY_INPUT: return "empty sequence (reference panics: unwrap on None)";
+    case ALNR_NO_POSITIVE_CELL: return "no positive cell in local matrix (reference panics: usize underflow)";
+    case ALNR_SYMBOL_OUT_OF_RANGE: return "symbol code outside the alphabet (reference panics: index out of bounds)";
+    case ALNR_CUDA_ERROR: return "CUDA error";
+    case ALNR_INVALID_ARGUMENT: return "invalid argument";
+    case ALNR_OUT_OF_MEMORY: return "out of device memory";
+    default: return "unknown status";
+  }
+}
+
+const char *alnr_last_error_detail(void) { return alnr::get_error_detail(); }
+
+int alnr_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { (void)cudaGetLastError(); return 0; }
+  return n;
+}
+
+const char *alnr_build_info(void) { return "aligner_b200 sm_100a cuda " __DATE__; }
+
+uint64_t alnr_kernel_launch_count(void) { return alnr::g_launches.load(); }
+
+int alnr_batch_create(const alnr_params *p, const alnr_batch *b, alnr_batch_handle **h) {
+  if (!h) return ALNR_INVALID_ARGUMENT;
+  *h = nullptr;
+  alnr_batch_handle *hh = new (std::nothrow) alnr_batch_handle();
+  if (!hh) return ALNR_OUT_OF_MEMORY;
+  int st = hh->impl.init(p, b, false);
+  if (st) { delete hh; return st; }
+  *h = hh;
+  return ALNR_OK;
+}
+
+int alnr_batch_run(alnr_batch_handle *h) { return h ? h->impl.run() : ALNR_INVALID_ARGUMENT; }
+
+int alnr_batch_sync(alnr_batch_handle *h) {
+  if (!h) return ALNR_INVALID_ARGUMENT;
+  ALNR_CUDA(cudaSetDevice(h->impl.device));
+  ALNR_CUDA(cudaStreamSynchronize(h->impl.stream));
+  return ALNR_OK;
+}
+
+int alnr_batch_download(alnr_batch_handle *h, alnr_batch_out *out) {
+  return h ? h->impl.download(out) : ALNR_INVALID_ARGUMENT;
+}
+
+void *alnr_batch_stream(alnr_batch_handle *h) { return h ? (void *)h->impl.stream : nullptr; }
+
+int alnr_batch_run_timed(alnr_batch_handle *h, float *ms, float *fill_ms) {
+  if (!h) return ALNR_INVALID_ARGUMENT;
+  int st = h->impl.run();  // records ev0 / ev1 around the kernels on the batch stream
+  if (st) return st;
+  ALNR_CUDA(cudaEventSynchronize(h->impl.ev1));
+  float t = 0.f;
+  if (h->impl.count) ALNR_CUDA(cudaEventElapsedTime(&t, h->impl.ev0, h->impl.ev1));
+  if (ms) *ms = t;
+  if (fill_ms) *fill_ms = h->impl.last_fill_ms;
+  return ALNR_OK;
+}
+
+int alnr_batch_numeric(alnr_batch_handle *h) { return h ? h->impl.numeric : 0; }
+uint64_t alnr_batch_rerun_count(alnr_batch_handle *h) { return h ? h->impl.rerun_total : 0; }
+void alnr_batch_destroy(alnr_batch_handle *h) {
+  if (!h) return;
+  cudaSetDevice(h->impl.device);
+  delete h;
+}
+
+int alnr_align_batch(const alnr_params *p, const alnr_batch *b, alnr_batch_out *out) {
+  alnr_batch_handle *h = nullptr;
+  int st = alnr_batch_create(p, b, &h);
+  if (st) return st;
+  st = h->impl.run();
+  if (!st) st = h->impl.download(out);
+  alnr_batch_destroy(h);
+  return st;
+}
+
+int alnr_align_pair(const alnr_params *p, const uint8_t *q, uint64_t n, const uint8_t *t,
+                    uint64_t m, int want_matrices, alnr_pair_result *out) {
+  if (!out || !p) return ALNR_INVALID_ARGUMENT;
+  std::memset(out, 0, sizeof(*out));
+  if (n == 0 || m == 0) return ALNR_EMPTY_INPUT;
+  if (!q || !t) return ALNR_INVALID_ARGUMENT;
+  uint64_t qo[2] = {0, n}, to[2] = {0, m};
+  alnr_batch b{q, qo, t, to, 1};
+  alnr_batch_handle hh;
+  int st = hh.impl.init(p, &b, want_matrices != 0);
+  if (st) return st;
+  st = hh.impl.run();
+  if (st) return st;
+  const size_t cap = n + m + 1, cells = (n + 1) * (m + 1);
+  uint8_t *qa = (uint8_t *)std::malloc(cap), *ta = (uint8_t *)std::malloc(cap);
+  double *H = want_matrices ? (double *)std::malloc(cells * sizeof(double)) : nullptr;
+  uint8_t *D = want_matrices ? (uint8_t *)std::malloc(cells) : nullptr;
+  auto fail = [&](int code) { std::free(qa); std::free(ta); std::free(H); std::free(D); return code; };
+  if (!qa || !ta || (want_matrices && (!H || !D))) return fail(ALNR_OUT_OF_MEMORY);
+  uint64_t off = 0;
+  uint32_t len = 0;
+  int32_t pst = 0;
+  alnr_batch_out bo{&out->f, &out->corner_score, out->coords, &off, &len, qa, ta, &pst};
+  st = hh.impl.download(&bo);
+  if (st) return fail(st);
+  if (pst) return fail(pst);
+  if (want_matrices) {
+    cudaError_t e = cudaMemcpy(H, hh.impl.d_Hout.p, cells * sizeof(double), cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess) e = cudaMemcpy(D, hh.impl.d_Dout.p, cells, cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess) return fail(alnr::cuda_fail(e, "copy H/D", __FILE__, __LINE__));
+  }
+  std::memmove(qa, qa + off, len);  // slot is right-aligned (aligner_b200.h)
+  std::memmove(ta, ta + off, len);
+  out->q_aln = qa; out->t_aln = ta; out->aln_len = len; out->H = H; out->D = D;
+  out->numeric = hh.impl.numeric;
+  return ALNR_OK;
+}
+
+void alnr_free_pair_result(alnr_pair_result *r) {
+  if (!r) return;
+  std::free(r->q_aln); std::free(r->t_aln); std::free(r->H); std::free(r->D);
+  r->q_aln = r->t_aln = nullptr; r->H = nullptr; r->D = nullptr;
+}
+
+void *alnr_host_alloc(uint64_t bytes) {
+  void *p = nullptr;
+  if (cudaMallocHost(&p, bytes ? bytes : 1) != cudaSuccess) { (void)cudaGetLastError(); return nullptr; }
+  return p;
+}
+void alnr_host_free(void *p) { if (p) cudaFreeHost(p); }
+
+}  // extern "C"

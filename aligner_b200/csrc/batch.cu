@@ -1,0 +1,267 @@
+// batch.cu — host layer: packs a batch into device-resident buffers, picks the numeric
+// domain, plans chunks against a scratch budget and enqueues fill + traceback kernels.
+#include "batch.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <numeric>
+
+#include "kernels_exact.cuh"
+#include "kernels_trace.cuh"
+#include "strip_launch.h"
+
+namespace alnr {
+
+std::atomic<uint64_t> g_launches{0};
+static thread_local std::string t_detail;
+void set_error_detail(const std::string &s) { t_detail = s; }
+const char *get_error_detail() { return t_detail.c_str(); }
+
+alnr_batch_impl::~alnr_batch_impl() {
+  if (ev0) cudaEventDestroy(ev0);
+  if (ev1) cudaEventDestroy(ev1);
+  if (ev2) cudaEventDestroy(ev2);
+  if (stream) cudaStreamDestroy(stream);
+}
+
+// Integer kernels are bit-exact iff every value the reference computes is an integer that
+// the chosen lane width holds: |H| <= (n + m + 2) * max(|s|, |del|, |ext|).
+int alnr_batch_impl::classify() {
+  auto integral = [](double v) { return std::isfinite(v) && v == std::nearbyint(v) && std::fabs(v) <= 1048576.0; };
+  bool all_int = integral(del) && integral(ext);
+  double mag = std::max(std::fabs(del), std::fabs(ext));
+  for (double v : matrix) { all_int = all_int && integral(v); mag = std::max(mag, std::fabs(v)); }
+  // -(x as f64) * del with del == 0 is -0.0 in the reference (simple/mod.rs:60): keep f64 there.
+  if (mode == ALNR_GLOBAL && del == 0.0) all_int = false;
+  const double bound = ((double)n_max + (double)m_max + 2.0) * std::max(mag, 1.0);
+  int best;
+  if (!all_int || bound >= 1073741824.0) best = ALNR_NUM_F64;
+  else if (strip_eligible(*this, bound)) best = ALNR_NUM_I16X2;
+  else best = ALNR_NUM_I32;
+  if (numeric == ALNR_NUM_AUTO) { numeric = best; return ALNR_OK; }
+  // a forced domain must still be exact
+  if (numeric == ALNR_NUM_F64) return ALNR_OK;
+  if (numeric == ALNR_NUM_I32 && best != ALNR_NUM_F64) return ALNR_OK;
+  if (numeric == ALNR_NUM_I16X2 && best == ALNR_NUM_I16X2) return ALNR_OK;
+  set_error_detail("forced numeric domain cannot represent this problem exactly");
+  return ALNR_INVALID_ARGUMENT;
+}
+
+static uint64_t scratch_budget_bytes() {
+  size_t free_b = 0, total_b = 0;
+  if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) return 1ull << 30;
+  uint64_t b = free_b / 3;
+  const uint64_t cap = 24ull << 30;
+  return std::max<uint64_t>(std::min<uint64_t>(b, cap), 64ull << 20);
+}
+
+int alnr_batch_impl::plan_chunks(const uint64_t *q_off, const uint64_t *t_off) {
+  chunks.clear();
+  if (count == 0) return ALNR_OK;
+  std::vector<uint32_t> order;
+  if (!uniform) {
+    order.resize(count);
+    std::iota(order.begin(), order.end(), 0u);
+    std::sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) {
+      uint64_t ma = t_off[a + 1] - t_off[a], mb = t_off[b + 1] - t_off[b];
+      if (ma != mb) return ma > mb;
+      uint64_t na = q_off[a + 1] - q_off[a], nb = q_off[b + 1] - q_off[b];
+      if (na != nb) return na > nb;
+      return a < b;
+    });
+    ALNR_CUDA(d_order.alloc(count));
+    ALNR_CUDA(cudaMemcpyAsync(d_order.p, order.data(), count * sizeof(uint32_t), cudaMemcpyHostToDevice, stream));
+    ALNR_CUDA(cudaStreamSynchronize(stream));
+  }
+  auto dims = [&](uint64_t slot, uint32_t &m, uint32_t &n) {
+    uint64_t p = uniform ? slot : order[slot];
+    m = (uint32_t)(t_off[p + 1] - t_off[p]);
+    n = (uint32_t)(q_off[p + 1] - q_off[p]);
+  };
+  // suffix maximum of n over slots (m is non-increasing after the sort)
+  std::vector<uint32_t> nsuf;
+  if (!uniform) {
+    nsuf.resize(count);
+    uint32_t mx = 0;
+    for (uint64_t s = count; s-- > 0;) { uint32_t m, n; dims(s, m, n); mx = std::max(mx, n); nsuf[s] = mx; }
+  }
+  const uint64_t budget = scratch_budget_bytes();
+  const size_t num_sz = numeric == ALNR_NUM_F64 ? 8 : 4;
+  uint64_t s = 0;
+  while (s < count) {
+    uint32_t m, n;
+    dims(s, m, n);
+    if (!uniform) n = nsuf[s];
+    m = std::max(m, 1u); n = std::max(n, 1u);
+    const uint32_t rpw = d_rows_per_word(*this, m);
+    const uint64_t nstrips = (m + rpw - 1) / rpw;
+    const uint64_t per_group = (nstrips * n * 4 + ((uint64_t)m + 1) * num_sz + (uint64_t)(n + 1) * 4) * 32;
+    uint64_t groups = std::max<uint64_t>(budget / per_group, 1);
+    uint64_t c = std::min<uint64_t>(groups * 32, count - s);
+    if (c < count - s) c = std::max<uint64_t>(c / 64 * 64, 32);  // keep duo-kernel warps whole
+    c = std::min<uint64_t>(c, 1u << 22);
+    chunks.push_back(Chunk{(uint32_t)s, (uint32_t)c, m, n});
+    s += c;
+  }
+  return ALNR_OK;
+}
+
+int alnr_batch_impl::init(const alnr_params *p, const alnr_batch *b, bool want_mats) {
+  if (!p || !b || !p->matrix) return ALNR_INVALID_ARGUMENT;
+  if (p->mode != ALNR_GLOBAL && p->mode != ALNR_LOCAL) return ALNR_INVALID_ARGUMENT;
+  if (p->volume < 1 || p->volume > 32) return ALNR_MATRIX_SHAPE_ERROR;
+  if (b->count >= (1ull << 31)) return ALNR_INVALID_ARGUMENT;
+  if (b->count && (!b->q_off || !b->t_off)) return ALNR_INVALID_ARGUMENT;
+  mode = p->mode; V = p->volume; del = p->del; ext = p->ext; numeric = p->numeric;
+  device = p->device < 0 ? 0 : p->device;
+  want_matrices = want_mats;
+  matrix.assign(p->matrix, p->matrix + (size_t)V * V);
+  count = b->count;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0 || device >= ndev) {
+    (void)cudaGetLastError();
+    set_error_detail("no usable CUDA device (this library has no CPU fallback)");
+    return ALNR_CUDA_ERROR;
+  }
+  ALNR_CUDA(cudaSetDevice(device));
+  ALNR_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+  ALNR_CUDA(cudaEventCreate(&ev0));
+  ALNR_CUDA(cudaEventCreate(&ev1));
+  ALNR_CUDA(cudaEventCreate(&ev2));
+
+  q_total = count ? b->q_off[count] : 0;
+  t_total = count ? b->t_off[count] : 0;
+  n_max = m_max = 0;
+  uniform = true;
+  for (uint64_t i = 0; i < count; ++i) {
+    if (b->q_off[i + 1] < b->q_off[i] || b->t_off[i + 1] < b->t_off[i]) return ALNR_INVALID_ARGUMENT;
+    uint64_t n = b->q_off[i + 1] - b->q_off[i], m = b->t_off[i + 1] - b->t_off[i];
+    if (n >= (1ull << 31) || m >= (1ull << 31)) return ALNR_INVALID_ARGUMENT;
+    if (i && (n != b->q_off[1] - b->q_off[0] || m != b->t_off[1] - b->t_off[0])) uniform = false;
+    n_max = std::max<uint32_t>(n_max, (uint32_t)n);
+    m_max = std::max<uint32_t>(m_max, (uint32_t)m);
+  }
+  int st = classify();
+  if (st) return st;
+
+  ALNR_CUDA(d_q.alloc(q_total + 16));
+  ALNR_CUDA(d_t.alloc(t_total + 16));
+  ALNR_CUDA(d_qoff.alloc(count + 1));
+  ALNR_CUDA(d_toff.alloc(count + 1));
+  if (count) {
+    ALNR_CUDA(cudaMemcpyAsync(d_q.p, b->q, q_total, cudaMemcpyHostToDevice, stream));
+    ALNR_CUDA(cudaMemcpyAsync(d_t.p, b->t, t_total, cudaMemcpyHostToDevice, stream));
+    ALNR_CUDA(cudaMemcpyAsync(d_qoff.p, b->q_off, (count + 1) * 8, cudaMemcpyHostToDevice, stream));
+    ALNR_CUDA(cudaMemcpyAsync(d_toff.p, b->t_off, (count + 1) * 8, cudaMemcpyHostToDevice, stream));
+  }
+  ALNR_CUDA(d_matd.alloc((size_t)V * V));
+  ALNR_CUDA(d_mati.alloc((size_t)V * V));
+  std::vector<int> mi((size_t)V * V);
+  for (size_t i = 0; i < mi.size(); ++i) mi[i] = numeric == ALNR_NUM_F64 ? 0 : (int)matrix[i];
+  ALNR_CUDA(cudaMemcpyAsync(d_matd.p, matrix.data(), matrix.size() * 8, cudaMemcpyHostToDevice, stream));
+  ALNR_CUDA(cudaMemcpyAsync(d_mati.p, mi.data(), mi.size() * 4, cudaMemcpyHostToDevice, stream));
+  ALNR_CUDA(cudaStreamSynchronize(stream));
+
+  st = plan_chunks(b->q_off, b->t_off);
+  if (st) return st;
+
+  ALNR_CUDA(d_f.alloc(count));
+  ALNR_CUDA(d_corner.alloc(count));
+  ALNR_CUDA(d_start.alloc(count * 2));
+  ALNR_CUDA(d_status.alloc(count));
+  ALNR_CUDA(d_coords.alloc(count * 4));
+  ALNR_CUDA(d_alnoff.alloc(count));
+  ALNR_CUDA(d_alnlen.alloc(count));
+  ALNR_CUDA(d_qaln.alloc(q_total + t_total + count));
+  ALNR_CUDA(d_taln.alloc(q_total + t_total + count));
+  ALNR_CUDA(d_flags.alloc(4));
+  ALNR_CUDA(d_rerun.alloc(count + 1));
+
+  uint64_t dwords = 1, hcol = 1;
+  for (const Chunk &c : chunks) {
+    DLayout dl{d_rows_per_word(*this, c.m_max), 0, c.n_max};
+    dl.nstrips = (c.m_max + dl.rows_per_word - 1) / dl.rows_per_word;
+    dwords = std::max<uint64_t>(dwords, dl.words_for(c.count));
+    hcol = std::max<uint64_t>(hcol, (uint64_t)((c.count + 31) / 32) * 32 * ((uint64_t)std::max(c.m_max, c.n_max) + 1));
+  }
+  ALNR_CUDA(d_D.alloc(dwords));
+  if (numeric == ALNR_NUM_F64) ALNR_CUDA(d_hcol_d.alloc(hcol));
+  else ALNR_CUDA(d_hcol_i.alloc(hcol));
+  if (want_matrices && count == 1) {
+    ALNR_CUDA(d_Hout.alloc(((size_t)m_max + 1) * ((size_t)n_max + 1)));
+    ALNR_CUDA(d_Dout.alloc(((size_t)m_max + 1) * ((size_t)n_max + 1)));
+  }
+  if (numeric == ALNR_NUM_I16X2) {
+    st = strip_prepare(*this);
+    if (st) return st;
+  }
+  return ALNR_OK;
+}
+
+template <typename T>
+static int launch_exact(alnr_batch_impl &B, const Chunk &c, const ChunkView &cv, const DLayout &dl,
+                        const FillOut &fo, T *hcol, const T *mat) {
+  ExactArgs<T> a;
+  a.cv = cv; a.mode = B.mode; a.V = B.V; a.del = (T)B.del; a.ext = (T)B.ext;
+  a.matrix = mat; a.hcol = hcol; a.hrows = c.m_max + 1; a.D = B.d_D.p; a.dl = dl; a.fo = fo;
+  a.H_out = B.d_Hout.p; a.D_out = B.d_Dout.p;
+  const uint32_t blocks = (c.count + 127) / 128;
+  fill_exact_kernel<T><<<blocks, 128, (size_t)B.V * B.V * sizeof(T), B.stream>>>(a);
+  ALNR_LAUNCHED();
+  return ALNR_OK;
+}
+
+int alnr_batch_impl::run() {
+  ALNR_CUDA(cudaSetDevice(device));
+  if (count == 0) return ALNR_OK;
+  FillOut fo{d_f.p, d_corner.p, d_start.p, d_status.p};
+  TraceOut to{d_coords.p, d_alnoff.p, d_alnlen.p, d_qaln.p, d_taln.p, nullptr};
+  // symbol validation: one coalesced sweep; the per-pair scan only runs if it found something
+  ALNR_CUDA(cudaMemsetAsync(d_flags.p, 0, 4 * sizeof(int), stream));
+  any_symbol_out_of_range_kernel<<<148 * 8, 256, 0, stream>>>(d_q.p, q_total, V, d_flags.p);
+  ALNR_LAUNCHED();
+  any_symbol_out_of_range_kernel<<<148 * 8, 256, 0, stream>>>(d_t.p, t_total, V, d_flags.p);
+  ALNR_LAUNCHED();
+  rerun_total = 0;
+  ALNR_CUDA(cudaEventRecord(ev0, stream));
+  for (const Chunk &c : chunks) {
+    ChunkView cv{d_q.p, d_t.p, d_qoff.p, d_toff.p, uniform ? nullptr : d_order.p, c.first, c.count};
+    DLayout dl{d_rows_per_word(*this, c.m_max), 0, c.n_max};
+    dl.nstrips = (c.m_max + dl.rows_per_word - 1) / dl.rows_per_word;
+    validate_kernel<<<(c.count + 127) / 128, 128, 0, stream>>>(cv, V, d_status.p, d_flags.p);
+    ALNR_LAUNCHED();
+    int st;
+    if (numeric == ALNR_NUM_F64) st = launch_exact<double>(*this, c, cv, dl, fo, d_hcol_d.p, d_matd.p);
+    else if (numeric == ALNR_NUM_I32) st = launch_exact<int>(*this, c, cv, dl, fo, d_hcol_i.p, d_mati.p);
+    else st = strip_run_chunk(*this, c, cv, dl, fo);
+    if (st) return st;
+    TraceArgs ta{cv, mode, V, d_D.p, dl, fo, to};
+    traceback_kernel<<<(c.count + 127) / 128, 128, 0, stream>>>(ta);
+    ALNR_LAUNCHED();
+  }
+  ALNR_CUDA(cudaEventRecord(ev1, stream));
+  return ALNR_OK;
+}
+
+int alnr_batch_impl::download(alnr_batch_out *out) {
+  if (!out) return ALNR_INVALID_ARGUMENT;
+  ALNR_CUDA(cudaSetDevice(device));
+  if (count == 0) return ALNR_OK;
+  auto cp = [&](void *dst, const void *src, size_t bytes) -> cudaError_t {
+    if (!dst) return cudaSuccess;
+    return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, stream);
+  };
+  ALNR_CUDA(cp(out->f, d_f.p, count * 8));
+  ALNR_CUDA(cp(out->corner, d_corner.p, count * 8));
+  ALNR_CUDA(cp(out->coords, d_coords.p, count * 32));
+  ALNR_CUDA(cp(out->aln_off, d_alnoff.p, count * 8));
+  ALNR_CUDA(cp(out->aln_len, d_alnlen.p, count * 4));
+  ALNR_CUDA(cp(out->status, d_status.p, count * 4));
+  ALNR_CUDA(cp(out->q_aln, d_qaln.p, q_total + t_total + count));
+  ALNR_CUDA(cp(out->t_aln, d_taln.p, q_total + t_total + count));
+  ALNR_CUDA(cudaStreamSynchronize(stream));
+  return ALNR_OK;
+}
+
+}  // namespace alnr

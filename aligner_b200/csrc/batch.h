@@ -1,0 +1,51 @@
+// batch.h — device-resident batch of independent pairs (host-side class behind
+// alnr_batch_* and alnr_align_batch / alnr_align_pair).
+#pragma once
+#include <vector>
+
+#include "common.cuh"
+#include "host_util.h"
+
+namespace alnr {
+
+struct Chunk {
+  uint32_t first, count;      // slots
+  uint32_t m_max, n_max;      // chunk-wide maxima
+};
+
+struct alnr_batch_impl {
+  // configuration
+  int mode = 0, V = 0, device = 0, numeric = 0;
+  double del = 0, ext = 0;
+  std::vector<double> matrix;
+  bool want_matrices = false;   // single-pair calls: also produce H and D (reference layout)
+
+  // shape
+  uint64_t count = 0, q_total = 0, t_total = 0;
+  uint32_t n_max = 0, m_max = 0;
+  bool uniform = true;
+  std::vector<Chunk> chunks;
+
+  // device state
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr;
+  DevBuf<uint8_t> d_q, d_t, d_qaln, d_taln, d_Dout;
+  DevBuf<uint64_t> d_qoff, d_toff, d_coords, d_alnoff;
+  DevBuf<uint32_t> d_order, d_start, d_alnlen, d_D, d_rerun;
+  DevBuf<int32_t> d_status;
+  DevBuf<int> d_flags;
+  DevBuf<double> d_f, d_corner, d_matd, d_Hout, d_hcol_d;
+  DevBuf<int> d_mati, d_hcol_i;
+  DevBuf<uint32_t> d_pack;      // packed sequences for the strip kernel
+  uint64_t rerun_total = 0;
+  float last_fill_ms = 0.f;
+
+  ~alnr_batch_impl();
+  int init(const alnr_params *p, const alnr_batch *b, bool want_mats);
+  int run();                     // enqueue all kernels on `stream`
+  int download(alnr_batch_out *out);
+  int classify();
+  int plan_chunks(const uint64_t *q_off, const uint64_t *t_off);
+};
+
+}  // namespace alnr

@@ -1,0 +1,62 @@
+// common.cuh — shared device/host definitions for the alignment kernels (sm_100a).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace alnr {
+
+enum : int { DIR_TOP = 0, DIR_LEFT = 1, DIR_DIAGONAL = 2, DIR_BEGINNING = 3 };
+constexpr int kBlank = 98;
+
+// ---------------------------------------------------------------------------------------
+// Direction scratch ("D") layout in HBM — shared by every fill kernel and the traceback.
+// Pairs of a chunk are numbered by slot s = 0..chunk-1; 32 consecutive slots form a group
+// so that the 32 lanes of a warp store one 128-byte line.  A cell (y, x), y,x >= 1, lives
+// in 32-bit word (strip, x-1) of its pair, strip = (y-1) / rows_per_word, at bit
+// 2 * ((y-1) % rows_per_word).  rows_per_word <= 16 (2 bits per cell, 0.25 B/cell).
+//   word index = ((group * nstrips + strip) * ncols + (x-1)) * 32 + lane
+// nstrips / ncols are the chunk-wide maxima.  Row 0 and column 0 are never stored: their
+// directions are fixed by the mode (simple/mod.rs:59-67 global, :181-183 local).
+// ---------------------------------------------------------------------------------------
+struct DLayout {
+  uint32_t rows_per_word;
+  uint32_t nstrips;
+  uint32_t ncols;
+  __host__ __device__ inline uint64_t word(uint32_t slot, uint32_t strip, uint32_t xm1) const {
+    uint32_t group = slot >> 5, lane = slot & 31;
+    return (((uint64_t)group * nstrips + strip) * ncols + xm1) * 32ull + lane;
+  }
+  __host__ __device__ inline uint64_t words_for(uint64_t slots) const {
+    return ((slots + 31) / 32) * (uint64_t)nstrips * ncols * 32ull;
+  }
+};
+
+// Per-chunk view of the batch that every kernel receives.
+struct ChunkView {
+  const uint8_t *q;        // concatenated query codes (device)
+  const uint8_t *t;        // concatenated target codes
+  const uint64_t *q_off;   // count+1
+  const uint64_t *t_off;   // count+1
+  const uint32_t *order;   // slot -> pair index (nullptr = identity), whole batch
+  uint32_t first;          // first slot of this chunk in `order`
+  uint32_t count;          // slots in this chunk
+};
+
+// Per-pair results produced by the fill kernels and consumed by the traceback.
+struct FillOut {
+  double *f;        // local: max(H); global: 0.0            [pair]
+  double *corner;   // H[m][n]                               [pair]
+  uint32_t *start;  // traceback start (y, x)                [pair*2]
+  int32_t *status;  // alnr_status per pair                  [pair]
+};
+
+struct TraceOut {
+  uint64_t *coords;   // [pair*4]
+  uint64_t *aln_off;  // [pair]
+  uint32_t *aln_len;  // [pair]
+  uint8_t *q_aln;     // slots, see aligner_b200.h
+  uint8_t *t_aln;
+  double *freq;       // optional V*V count matrix per pair (alignment.rs:13-23), or nullptr
+};
+
+}  // namespace alnr

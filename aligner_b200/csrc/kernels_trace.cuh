@@ -1,0 +1,113 @@
+// kernels_trace.cuh — validation and on-device traceback.
+#pragma once
+#include "common.cuh"
+
+namespace alnr {
+
+// One thread per pair: empty sequences and out-of-alphabet symbols become statuses
+// (the reference panics: simple/mod.rs:103-104 unwrap, matrix[[t,q]] bounds check).
+// The per-symbol scan only runs when the coalesced sweep below flagged the batch.
+__global__ void validate_kernel(ChunkView cv, int V, int32_t *status, const int *flag) {
+  const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+  if (slot >= cv.count) return;
+  const uint32_t pair = cv.order ? cv.order[cv.first + slot] : cv.first + slot;
+  const uint64_t q0 = cv.q_off[pair], q1 = cv.q_off[pair + 1];
+  const uint64_t t0 = cv.t_off[pair], t1 = cv.t_off[pair + 1];
+  int st = 0;
+  if (q1 == q0 || t1 == t0) st = 10;  // ALNR_EMPTY_INPUT
+  if (*flag) {
+    for (uint64_t i = q0; i < q1 && !st; ++i) if (cv.q[i] >= V) st = 12;  // SYMBOL_OUT_OF_RANGE
+    for (uint64_t i = t0; i < t1 && !st; ++i) if (cv.t[i] >= V) st = 12;
+  }
+  status[pair] = st;
+}
+
+// Fast whole-buffer symbol check (coalesced 16-byte loads); flags[0] != 0 iff some byte >= V.
+__global__ void any_symbol_out_of_range_kernel(const uint8_t *buf, uint64_t len, int V, int *flag) {
+  const uint64_t tid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  bool bad = false;
+  const uint64_t nvec = len / 16;
+  const uint4 *v = reinterpret_cast<const uint4 *>(buf);
+  for (uint64_t i = tid; i < nvec; i += stride) {
+    uint4 w = v[i];
+    uint32_t ws[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+#pragma unroll
+      for (int b = 0; b < 4; ++b) bad |= ((ws[k] >> (8 * b)) & 0xff) >= (uint32_t)V;
+  }
+  for (uint64_t i = nvec * 16 + tid; i < len; i += stride) bad |= buf[i] >= V;
+  if (bad) *flag = 1;
+}
+
+struct TraceArgs {
+  ChunkView cv;
+  int mode;
+  int V;
+  const uint32_t *D;
+  DLayout dl;
+  FillOut fo;
+  TraceOut to;
+};
+
+// One thread per pair walks the 2-bit D scratch from the start cell until Beginning
+// (simple/mod.rs:99-130 global, :213-245 local).  The reference seeds the output with the
+// start pair BEFORE the walk and reverses at the end; writing backwards from the end of the
+// pair's slot yields the same string right-aligned with no reversal pass.
+__global__ void __launch_bounds__(128) traceback_kernel(TraceArgs a) {
+  const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+  if (slot >= a.cv.count) return;
+  const uint32_t pair = a.cv.order ? a.cv.order[a.cv.first + slot] : a.cv.first + slot;
+  const uint64_t qo = a.cv.q_off[pair], to = a.cv.t_off[pair];
+  const uint32_t n = (uint32_t)(a.cv.q_off[pair + 1] - qo);
+  const uint32_t m = (uint32_t)(a.cv.t_off[pair + 1] - to);
+  const uint64_t slot_begin = qo + to + pair;
+  const uint64_t slot_end = slot_begin + n + m + 1;
+  double *freq = a.to.freq ? a.to.freq + (size_t)pair * a.V * a.V : nullptr;
+  if (freq) for (int i = 0; i < a.V * a.V; ++i) freq[i] = 0.0;
+  if (a.fo.status[pair] != 0) {
+    if (a.to.aln_len) a.to.aln_len[pair] = 0;
+    if (a.to.aln_off) a.to.aln_off[pair] = slot_end;
+    if (a.to.coords) for (int k = 0; k < 4; ++k) a.to.coords[4 * (size_t)pair + k] = 0;
+    return;
+  }
+  const uint8_t *q = a.cv.q + qo;
+  const uint8_t *t = a.cv.t + to;
+  const bool glob = a.mode == 0;
+  const uint32_t sy = a.fo.start[2 * (size_t)pair], sx = a.fo.start[2 * (size_t)pair + 1];
+  uint32_t cy = sy, cx = sx;
+  uint64_t pos = slot_end;
+  const uint32_t rpw = a.dl.rows_per_word;
+  const bool wr = a.to.q_aln != nullptr && a.to.t_aln != nullptr;
+
+  auto emit = [&](uint8_t qc, uint8_t tc) {
+    --pos;
+    if (wr) { a.to.q_aln[pos] = qc; a.to.t_aln[pos] = tc; }
+    if (freq && qc != kBlank && tc != kBlank) freq[(int)tc * a.V + qc] += 1.0;  // alignment.rs:16-20
+  };
+  emit(q[cx - 1], t[cy - 1]);  // seed (simple/mod.rs:102-105, :213-216)
+  for (;;) {
+    int d;
+    if (cy == 0 || cx == 0) {
+      if (!glob || (cy == 0 && cx == 0)) d = DIR_BEGINNING;
+      else d = (cy == 0) ? DIR_LEFT : DIR_TOP;  // simple/mod.rs:59-67
+    } else {
+      const uint32_t w = a.D[a.dl.word(slot, (cy - 1) / rpw, cx - 1)];
+      d = (w >> (2 * ((cy - 1) % rpw))) & 3;
+    }
+    if (d == DIR_BEGINNING) break;
+    if (d == DIR_TOP) { emit(kBlank, t[cy - 1]); --cy; }
+    else if (d == DIR_LEFT) { emit(q[cx - 1], kBlank); --cx; }
+    else { emit(q[cx - 1], t[cy - 1]); --cx; --cy; }
+  }
+  if (a.to.aln_len) a.to.aln_len[pair] = (uint32_t)(slot_end - pos);
+  if (a.to.aln_off) a.to.aln_off[pair] = pos;
+  if (a.to.coords) {
+    uint64_t *c = a.to.coords + 4 * (size_t)pair;
+    if (glob) { c[0] = 1; c[1] = n; c[2] = 1; c[3] = m; }                      // simple/mod.rs:137
+    else { c[0] = cx + 1; c[1] = sx + 1; c[2] = cy + 1; c[3] = sy + 1; }        // :254-257
+  }
+}
+
+}  // namespace alnr

@@ -1,0 +1,17 @@
+// strip_launch.h — host entry points of the s16x2 strip kernel family (kernels_strip.cu).
+#pragma once
+#include "batch.h"
+
+namespace alnr {
+
+// true when the batch can run in packed 16-bit lanes (two pairs per thread) exactly.
+bool strip_eligible(const alnr_batch_impl &B, double value_bound);
+// rows per 32-bit D word for a chunk whose longest target has m rows (<= 16).
+uint32_t d_rows_per_word(const alnr_batch_impl &B, uint32_t m);
+// one-time per-batch preparation (packed sequences, profile table).
+int strip_prepare(alnr_batch_impl &B);
+// enqueue the fill of one chunk (+ exact re-runs of pairs whose speculation failed).
+int strip_run_chunk(alnr_batch_impl &B, const Chunk &c, const ChunkView &cv, const DLayout &dl,
+                    const FillOut &fo);
+
+}  // namespace alnr

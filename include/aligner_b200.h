@@ -1,0 +1,159 @@
+/*
+ * aligner_b200.h — C ABI of the B200-native replacement for aligner-core's pairwise
+ * alignment hot path.  Plain pointers and sizes only; no C++ or torch types.
+ *
+ * The reference has no FFI: its boundary is the Rust trait
+ *   AlignerTrait::perform_alignment(&mut self, del: f64, ext: f64, matrix: &Array2<f64>,
+ *                                   heuristics: Option<Heuristics>)
+ *       -> Result<AlignmentResult<T, A>>                 aligner-core/src/lib.rs:27-40
+ * implemented by SimpleGlobalAligner / SimpleLocalAligner (aligner-core/src/simple/mod.rs:42,
+ * :168) and HeuristicAligner (aligner-core/src/heuristic/mod.rs:36).  Each entry point below
+ * names the reference item it replaces; INTEGRATION.md shows the Rust `-sys` binding.
+ *
+ * Conventions
+ *  - Symbols are the reference's numeric codes (aligner-core/src/enums.rs:55-84, :138-147):
+ *    Protein A R N D C Q E G H I L K M F P S T W Y V B J Z X = 0..23, DNA A T C G = 0..3,
+ *    Blank = 98 in returned alignments.  query has n symbols, target has m symbols.
+ *  - matrix is row-major V x V doubles, indexed matrix[target_symbol * V + query_symbol]
+ *    (simple/mod.rs:85, :198).
+ *  - Directions: 0 Top, 1 Left, 2 Diagonal, 3 Beginning (enums.rs:9-15).
+ *  - coords[4] = {q_from, q_to, t_from, t_to} = Alignment.coords ((a,b),(c,d))
+ *    (aligner-core/src/alignment.rs:8).
+ *  - Every function returns an alnr_status; nothing throws or aborts across the boundary.
+ *    Inputs on which the reference panics return a status instead.
+ *  - All compute runs on the GPU.  There is no CPU fallback: without a usable CUDA device
+ *    every compute entry point returns ALNR_CUDA_ERROR.
+ *  - Thread-safe: calls may be issued concurrently from many host threads (the reference's
+ *    callers do so, aligner-core/src/statistics/mod.rs:255-286); each call/handle uses its
+ *    own CUDA stream.
+ */
+#ifndef ALIGNER_B200_H
+#define ALIGNER_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* 0 OK, then aligner_core::Error in declaration order (lib.rs:47-57), then
+ * aligner_helpers::Error (aligner-helpers/src/lib.rs:12-14), then panics-turned-statuses. */
+typedef enum {
+  ALNR_OK = 0,
+  ALNR_PROTEIN_NOT_FOUND = 1,
+  ALNR_CHAR_IS_NOT_MATCHABLE = 2,
+  ALNR_UNNECESSARY_ARGUMENT = 3,
+  ALNR_MISSING_ARGUMENT = 4,
+  ALNR_RESULT_IS_EMPTY = 5,
+  ALNR_CALCULATION_ERROR = 6,
+  ALNR_VALIDATION_ERROR = 7,
+  ALNR_MATRIX_SHAPE_ERROR = 8,
+  ALNR_WRONG_MATRIX = 9,         /* transform_matrix: Roots::No (matrices/mod.rs:45) */
+  ALNR_EMPTY_INPUT = 10,         /* simple/mod.rs:103-104 unwrap() on an empty sequence */
+  ALNR_NO_POSITIVE_CELL = 11,    /* simple/mod.rs:214 underflow: arg-max is (0,0) */
+  ALNR_SYMBOL_OUT_OF_RANGE = 12, /* matrix[[t,q]] out of bounds (Blank/Pos/Any in input) */
+  ALNR_CUDA_ERROR = 13,
+  ALNR_INVALID_ARGUMENT = 14,
+  ALNR_OUT_OF_MEMORY = 15
+} alnr_status;
+
+enum { ALNR_GLOBAL = 0, ALNR_LOCAL = 1 };
+enum { ALNR_DIR_TOP = 0, ALNR_DIR_LEFT = 1, ALNR_DIR_DIAGONAL = 2, ALNR_DIR_BEGINNING = 3 };
+#define ALNR_BLANK 98
+#define ALNR_POS 99
+
+/* Which arithmetic a call ran in (reported, never chosen by the caller unless forced). */
+enum {
+  ALNR_NUM_AUTO = 0, /* integer kernels when matrix, del, ext are integral and bounded */
+  ALNR_NUM_I16X2 = 1,
+  ALNR_NUM_I32 = 2,
+  ALNR_NUM_F64 = 3
+};
+
+typedef struct {
+  int mode;            /* ALNR_GLOBAL: simple/mod.rs:42-144; ALNR_LOCAL: simple/mod.rs:168-264 */
+  int volume;          /* V = BioData::volume(): 24 Protein, 4 DNA (enums.rs:398-400, :562-564) */
+  double del;          /* perform_alignment(del, ..) */
+  double ext;          /* perform_alignment(.., ext, ..) — the reference's stateful rule, not Gotoh */
+  const double *matrix; /* V*V, [t][q] */
+  int device;          /* CUDA ordinal; -1 = device 0 */
+  int numeric;         /* ALNR_NUM_AUTO or a forced domain (tests) */
+} alnr_params;
+
+/* ---- library / device ---------------------------------------------------------------- */
+const char *alnr_strerror(int status);
+const char *alnr_last_error_detail(void); /* thread-local text of the last CUDA failure */
+int alnr_device_count(void);              /* 0 when no usable CUDA device */
+const char *alnr_build_info(void);        /* "sm_100a ..." */
+/* Number of kernel launches issued by this library since load (all threads). */
+uint64_t alnr_kernel_launch_count(void);
+
+/* ---- one pair: AlignerTrait::perform_alignment for Simple{Global,Local}Aligner -------- */
+typedef struct {
+  double f;            /* Alignment.f: 0.0 in global mode (simple/mod.rs:139), max(H) in local */
+  double corner_score; /* alignment_matrix[[m, n]] — where the global score lives */
+  uint64_t coords[4];
+  uint8_t *q_aln;      /* Alignment.query, aln_len codes, library-allocated */
+  uint8_t *t_aln;      /* Alignment.target */
+  uint64_t aln_len;
+  double *H;           /* AlignmentResult.alignment_matrix, (m+1)*(n+1) row-major, if requested */
+  uint8_t *D;          /* AlignmentResult.direction_matrix, same shape, 1 byte per cell */
+  int numeric;         /* domain actually used */
+} alnr_pair_result;
+
+/* want_matrices != 0 also returns H and D (alignment_result.rs:8-9). */
+int alnr_align_pair(const alnr_params *p, const uint8_t *q, uint64_t n, const uint8_t *t,
+                    uint64_t m, int want_matrices, alnr_pair_result *out);
+void alnr_free_pair_result(alnr_pair_result *r);
+
+/* ---- batches of independent pairs (replaces the callers' thread pools:
+ *      statistics/mod.rs:255-286, latent-repeat-search/engine/calc.rs:47-69) -------------- */
+typedef struct {
+  const uint8_t *q;      /* concatenated query codes */
+  const uint64_t *q_off; /* count+1 offsets */
+  const uint8_t *t;      /* concatenated target codes */
+  const uint64_t *t_off; /* count+1 offsets */
+  uint64_t count;
+} alnr_batch;
+
+/* Caller-provided output arrays (host memory; pinned memory makes copies faster).
+ * Any pointer may be NULL to skip that output.  Alignment i is written into the slot
+ * [slot_off(i), slot_off(i) + n_i + m_i + 1) of q_aln / t_aln with
+ * slot_off(i) = q_off[i] + t_off[i] + i, RIGHT-aligned: it starts at aln_off[i] and has
+ * aln_len[i] symbols.  q_aln/t_aln therefore need q_off[count] + t_off[count] + count bytes. */
+typedef struct {
+  double *f;           /* [count] */
+  double *corner;      /* [count] */
+  uint64_t *coords;    /* [count*4] */
+  uint64_t *aln_off;   /* [count] */
+  uint32_t *aln_len;   /* [count] */
+  uint8_t *q_aln;
+  uint8_t *t_aln;
+  int32_t *status;     /* [count] per-pair status (EMPTY_INPUT, NO_POSITIVE_CELL, ...) */
+} alnr_batch_out;
+
+/* Host buffers in, host buffers out (H2D + kernels + D2H, chunked and overlapped). */
+int alnr_align_batch(const alnr_params *p, const alnr_batch *b, alnr_batch_out *out);
+
+/* Device-resident form of the same call: upload once, run many times, download. */
+typedef struct alnr_batch_handle alnr_batch_handle;
+int alnr_batch_create(const alnr_params *p, const alnr_batch *b, alnr_batch_handle **h);
+int alnr_batch_run(alnr_batch_handle *h);               /* kernels only, asynchronous */
+int alnr_batch_sync(alnr_batch_handle *h);
+int alnr_batch_download(alnr_batch_handle *h, alnr_batch_out *out);
+void *alnr_batch_stream(alnr_batch_handle *h);          /* cudaStream_t the kernels run on */
+/* Runs the batch once between two CUDA events on its own stream; *ms = device time. */
+int alnr_batch_run_timed(alnr_batch_handle *h, float *ms, float *fill_ms);
+int alnr_batch_numeric(alnr_batch_handle *h);           /* domain selected for this batch */
+uint64_t alnr_batch_rerun_count(alnr_batch_handle *h);  /* pairs whose speculation was redone */
+void alnr_batch_destroy(alnr_batch_handle *h);
+
+/* pinned host memory helpers for callers without a CUDA binding */
+void *alnr_host_alloc(uint64_t bytes);
+void alnr_host_free(void *p);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,184 @@
+"""CPU tests of the oracle (oracle/*.cpp): the reference's one golden vector, the SURVEY §8c
+substitute known answers, lean == faithful, and a differential test against the independent
+Python restatement (oracle/py_restatement.py)."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+import oracle_lib as O
+from conftest import ROOT, load_golden, sha16
+
+sys.path.insert(0, os.path.join(ROOT, "oracle"))
+import py_restatement as PY  # noqa: E402
+
+from aligner_b200 import DNA, Protein, dna_matrix, get_blosum62  # noqa: E402
+
+
+def _book50():
+    g = load_golden("legacy_global.json")
+    M = np.zeros((24, 24))
+    for tl, row in g["blosum50_sub"].items():
+        for ql, v in row.items():
+            M[Protein.match_with_char(tl), Protein.match_with_char(ql)] = v
+    return g, M
+
+
+def test_legacy_golden_global_matrix():
+    """src/tests/test_alignment.rs:14-39 — the only reference test that pins this path."""
+    g, M = _book50()
+    q, t = Protein.str_to_vec(g["query"]), Protein.str_to_vec(g["target"])
+    r = O.align_pair("global", q, t, 8.0, 8.0, M)
+    assert r["status"] == 0
+    assert (r["H"] == np.array(g["H"], dtype=np.float64)).all()
+    assert (r["D"] == np.array(g["D"], dtype=np.uint8)).all()
+    # aligner-core's strings = legacy golden strings + the duplicated seed column
+    qa, ta = Protein.vec_to_str(r["q_aln"]), Protein.vec_to_str(r["t_aln"])
+    assert qa == "HEAGAWGHE_EE" and ta == "_PA__W_HEAEE"
+    assert r["coords"] == ((1, 10), (1, 7)) and r["f"] == 0.0
+
+
+def test_blosum62_table_matches_reference_fixture():
+    assert (get_blosum62() == np.array(load_golden("blosum62.json")["rows"], dtype=np.float64)).all()
+
+
+KNOWN = [
+    # (example, mode, del, ext, expected)  — SURVEY.md §8c substitute known answers
+    ("book", "global", 8, 8, dict(corner=-8, q="HEAGAWGHE_EE", t="_PA__W_HEAEE", dsha="52108b126abb566d")),
+    ("book", "global", 11, 2, dict(corner=21, q="HEAGAWGHE_EE", t="P_A__W_HEAEE", dsha="2aa9c7a135d60d73")),
+    ("book", "local", 11, 2, dict(f=27, coords=((5, 11), (1, 8)), q="_AWGHE_EE", t="PAW_HEAEE")),
+    ("protein", "local", 11, 2, dict(f=1554, coords=((1, 341), (1, 342)), alen=342, dsha="21a6e7676bbc9088",
+                                      qsha="b41b36ae69b35a56", tsha="e47ac5f55dcfa857")),
+    ("protein", "local", 11, 1, dict(f=1561, alen=352, dsha="0b6f2d50afd5324a")),
+    ("protein", "local", 11, 11, dict(f=1545, alen=342, dsha="8c835feb49a8f10d")),
+    ("protein", "global", 11, 2, dict(corner=1554, dsha="38b4806113e499a6")),
+    ("gene", "global", 8, 8, dict(corner=-209, alen=1257, dsha="449c8cbeb9bcaec1")),
+    ("gene", "local", 10, 2, dict(f=2081, coords=((11, 1195), (1, 1021)), alen=1484, dsha="e61b77fa78135f90")),
+]
+
+
+@pytest.mark.parametrize("ex,mode,d,e,want", KNOWN)
+def test_survey_known_answers(examples, ex, mode, d, e, want):
+    q, t = examples[ex]
+    sym = DNA if ex == "gene" else Protein
+    M = dna_matrix(5, -4) if ex == "gene" else get_blosum62()
+    r = O.align_pair(mode, q, t, float(d), float(e), M)
+    assert r["status"] == 0
+    if "corner" in want:
+        assert r["corner"] == want["corner"]
+    if "f" in want:
+        assert r["f"] == want["f"]
+    if "coords" in want:
+        assert r["coords"] == want["coords"]
+    if "q" in want:
+        assert sym.vec_to_str(r["q_aln"]) == want["q"] and sym.vec_to_str(r["t_aln"]) == want["t"]
+    if "alen" in want:
+        assert len(r["q_aln"]) == want["alen"]
+    if "dsha" in want:
+        assert sha16(r["D"]) == want["dsha"]
+    if "qsha" in want:
+        assert sha16(Protein.vec_to_str(r["q_aln"]).encode()) == want["qsha"]
+        assert sha16(Protein.vec_to_str(r["t_aln"]).encode()) == want["tsha"]
+    # lean layout gives the same answers
+    rl = O.align_pair(mode, q, t, float(d), float(e), M, lean=True)
+    assert rl["status"] == 0 and rl["f"] == r["f"] and rl["corner"] == r["corner"]
+    assert rl["coords"] == r["coords"] and rl["d_sha"] == sha16(r["D"])
+    assert (rl["q_aln"] == r["q_aln"]).all() and (rl["t_aln"] == r["t_aln"]).all()
+
+
+def _rand_case(rng, V, integral):
+    n, m = int(rng.integers(1, 14)), int(rng.integers(1, 14))
+    q = rng.integers(0, V, n).astype(np.uint8)
+    t = rng.integers(0, V, m).astype(np.uint8)
+    if integral:
+        M = rng.integers(-4, 6, (V, V)).astype(np.float64)
+        d, e = float(rng.integers(0, 12)), float(rng.integers(0, 6))
+    else:
+        M = rng.normal(0, 2.0, (V, V))
+        d, e = float(rng.uniform(0, 8)), float(rng.uniform(0, 4))
+    return q, t, M, d, e
+
+
+@pytest.mark.parametrize("integral", [True, False])
+def test_differential_vs_python_restatement(integral):
+    rng = np.random.default_rng(7 if integral else 8)
+    nerr = 0
+    for it in range(300):
+        V = 4 if it % 2 else 24
+        q, t, M, d, e = _rand_case(rng, V, integral)
+        for mode in ("global", "local"):
+            r = O.align_pair(mode, q, t, d, e, M)
+            try:
+                p = PY.align(mode, list(q), list(t), d, e, M.tolist())
+            except ValueError:
+                assert r["status"] == 2  # no positive cell
+                nerr += 1
+                continue
+            assert r["status"] == 0
+            assert (r["H"] == np.array(p["H"])).all() and (r["D"] == np.array(p["D"], dtype=np.uint8)).all()
+            assert list(r["q_aln"]) == p["q_aln"] and list(r["t_aln"]) == p["t_aln"]
+            assert r["coords"] == p["coords"] and r["f"] == p["f"]
+    assert nerr < 300
+
+
+def test_status_cases():
+    M = dna_matrix()
+    a = np.array([0, 1, 2], dtype=np.uint8)
+    assert O.align_pair("global", a[:0], a, 1, 1, M)["status"] == 1
+    assert O.align_pair("local", a, a[:0], 1, 1, M)["status"] == 1
+    assert O.align_pair("local", np.array([98], dtype=np.uint8), a, 1, 1, M)["status"] == 3
+    # all-negative matrix: arg-max stays at (0,0) -> the reference panics (simple/mod.rs:214)
+    assert O.align_pair("local", a, a, 1, 1, -np.ones((4, 4)))["status"] == 2
+
+
+def test_transform_matrix_vs_python_and_constraints():
+    rng = np.random.default_rng(3)
+    for it in range(50):
+        V = 24 if it % 2 else 4
+        M = rng.integers(-1, 2, (V, V)).astype(np.float64) if it % 3 else rng.normal(0, 1, (V, V))
+        fr = rng.uniform(0.5, 1.5, V)
+        fr /= fr.sum()
+        kd, r2 = -1.0 - 0.1 * it, float(V * V)
+        st, T = O.transform_matrix(M, kd, r2, fr)
+        try:
+            P = np.array(PY.transform_matrix(M.tolist(), kd, r2, list(fr)))
+        except ValueError:
+            assert st == 4
+            continue
+        assert st == 0 and (T == P).all()
+        # the two constraints the transform enforces (matrices/mod.rs:19-68)
+        p = np.outer(fr, np.full(V, 1.0 / V))
+        assert abs((p * T).sum() - kd) < 1e-9 and abs((T * T).sum() - r2) < 1e-7
+
+
+def test_heuristic_vs_python():
+    rng = np.random.default_rng(11)
+    for it in range(20):
+        V = 4
+        n, m = int(rng.integers(8, 30)), int(rng.integers(8, 30))
+        q = rng.integers(0, V, n).astype(np.uint8)
+        t = q[: min(n, m)].copy() if it % 2 else rng.integers(0, V, m).astype(np.uint8)
+        M = rng.integers(-1, 2, (V, V)).astype(np.float64)
+        fr = np.bincount(np.concatenate([q, t]), minlength=V).astype(np.float64)
+        fr /= fr.sum()
+        r = O.heuristic(q, t, 5.0, 5.0, M, -1.0, 0.0, fr)
+        try:
+            p, T, passes = PY.heuristic(list(q), list(t), 5.0, 5.0, M.tolist(), -1.0, 0.0, list(fr))
+        except ValueError as exc:
+            assert r["status"] in (2, 4), (r["status"], exc)
+            continue
+        assert r["status"] == 0 and r["passes"] == passes and passes >= 2
+        assert r["f"] == p["f"] and (r["matrix"] == np.array(T)).all()
+        assert list(r["q_aln"]) == p["q_aln"] and r["coords"] == p["coords"]
+
+
+def test_oracle_batch_threads_agree():
+    from aligner_b200 import workloads as W
+    pairs = W.dna_read_batch(0, 200, n=40)
+    a = O.align_batch("local", pairs, 10.0, 2.0, dna_matrix(), threads=1)
+    b = O.align_batch("local", pairs, 10.0, 2.0, dna_matrix(), threads=4)
+    for k in ("f", "coords", "aln_len", "q_aln", "t_aln", "status"):
+        assert (a[k] == b[k]).all()
+    one = O.align_pair("local", *pairs.pair(17), 10.0, 2.0, dna_matrix())
+    assert one["f"] == a["f"][17] and (one["q_aln"] == a["q_aln"][17][: len(one["q_aln"])]).all()
