@@ -63,7 +63,7 @@ SIGNATURES = {
     "alnr_batch_sync": (C.c_int, [C.c_void_p]),
     "alnr_batch_download": (C.c_int, [C.c_void_p, C.POINTER(BatchOut)]),
     "alnr_batch_stream": (C.c_void_p, [C.c_void_p]),
-    "alnr_batch_run_timed": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
+    "alnr_batch_run_timed": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
     "alnr_batch_numeric": (C.c_int, [C.c_void_p]),
     "alnr_batch_rerun_count": (C.c_uint64, [C.c_void_p]),
     "alnr_batch_destroy": (None, [C.c_void_p]),

@@ -127,10 +127,11 @@ class DeviceBatch:
     def sync(self):
         N.check(N.lib().alnr_batch_sync(self._h))
 
-    def run_timed(self):
-        """One pass between CUDA events on the batch's own stream -> (total ms, fill ms)."""
+    def run_timed(self, steps=1, profile_fill=True):
+        """`steps` passes between CUDA events on the batch's own stream -> (total ms, fill ms)."""
         ms, fill = C.c_float(), C.c_float()
-        N.check(N.lib().alnr_batch_run_timed(self._h, C.byref(ms), C.byref(fill)))
+        N.check(N.lib().alnr_batch_run_timed(self._h, steps, C.byref(ms),
+                                             C.byref(fill) if profile_fill else None))
         return ms.value, fill.value
 
     def download(self, want_alignments=True, out=None):

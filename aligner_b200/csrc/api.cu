@@ -74,15 +74,29 @@ int alnr_batch_download(alnr_batch_handle *h, alnr_batch_out *out) {
 
 void *alnr_batch_stream(alnr_batch_handle *h) { return h ? (void *)h->impl.stream : nullptr; }
 
-int alnr_batch_run_timed(alnr_batch_handle *h, float *ms, float *fill_ms) {
-  if (!h) return ALNR_INVALID_ARGUMENT;
-  int st = h->impl.run();  // records ev0 / ev1 around the kernels on the batch stream
-  if (st) return st;
-  ALNR_CUDA(cudaEventSynchronize(h->impl.ev1));
+int alnr_batch_run_timed(alnr_batch_handle *h, int steps, float *ms_total, float *fill_ms_total) {
+  if (!h || steps < 1) return ALNR_INVALID_ARGUMENT;
+  alnr_batch_impl &B = h->impl;
+  ALNR_CUDA(cudaSetDevice(B.device));
+  ALNR_CUDA(cudaStreamSynchronize(B.stream));
+  B.profile = fill_ms_total != nullptr;
+  B.fill_events_used = 0;
+  ALNR_CUDA(cudaEventRecord(B.ev0, B.stream));
+  for (int s = 0; s < steps; ++s) {
+    int st = B.run();
+    if (st) { B.profile = false; return st; }
+  }
+  ALNR_CUDA(cudaEventRecord(B.ev1, B.stream));
+  ALNR_CUDA(cudaEventSynchronize(B.ev1));
   float t = 0.f;
-  if (h->impl.count) ALNR_CUDA(cudaEventElapsedTime(&t, h->impl.ev0, h->impl.ev1));
-  if (ms) *ms = t;
-  if (fill_ms) *fill_ms = h->impl.last_fill_ms;
+  ALNR_CUDA(cudaEventElapsedTime(&t, B.ev0, B.ev1));
+  if (ms_total) *ms_total = t;
+  if (B.profile) {
+    int st = B.collect_fill_ms();
+    B.profile = false;
+    if (st) return st;
+    *fill_ms_total = B.last_fill_ms;
+  }
   return ALNR_OK;
 }
 

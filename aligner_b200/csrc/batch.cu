@@ -22,7 +22,30 @@ alnr_batch_impl::~alnr_batch_impl() {
   if (ev0) cudaEventDestroy(ev0);
   if (ev1) cudaEventDestroy(ev1);
   if (ev2) cudaEventDestroy(ev2);
+  for (cudaEvent_t e : fill_events) cudaEventDestroy(e);
   if (stream) cudaStreamDestroy(stream);
+}
+
+int alnr_batch_impl::fill_mark(bool) {
+  if (!profile) return ALNR_OK;
+  if (fill_events_used == fill_events.size()) {
+    cudaEvent_t e;
+    ALNR_CUDA(cudaEventCreate(&e));
+    fill_events.push_back(e);
+  }
+  ALNR_CUDA(cudaEventRecord(fill_events[fill_events_used++], stream));
+  return ALNR_OK;
+}
+
+int alnr_batch_impl::collect_fill_ms() {
+  last_fill_ms = 0.f;
+  for (size_t i = 0; i + 1 < fill_events_used; i += 2) {
+    float t = 0.f;
+    ALNR_CUDA(cudaEventElapsedTime(&t, fill_events[i], fill_events[i + 1]));
+    last_fill_ms += t;
+  }
+  fill_events_used = 0;
+  return ALNR_OK;
 }
 
 // Integer kernels are bit-exact iff every value the reference computes is an integer that
@@ -224,23 +247,24 @@ int alnr_batch_impl::run() {
   any_symbol_out_of_range_kernel<<<148 * 8, 256, 0, stream>>>(d_t.p, t_total, V, d_flags.p);
   ALNR_LAUNCHED();
   rerun_total = 0;
-  ALNR_CUDA(cudaEventRecord(ev0, stream));
   for (const Chunk &c : chunks) {
     ChunkView cv{d_q.p, d_t.p, d_qoff.p, d_toff.p, uniform ? nullptr : d_order.p, c.first, c.count};
     DLayout dl{d_rows_per_word(*this, c.m_max), 0, c.n_max};
     dl.nstrips = (c.m_max + dl.rows_per_word - 1) / dl.rows_per_word;
     validate_kernel<<<(c.count + 127) / 128, 128, 0, stream>>>(cv, V, d_status.p, d_flags.p);
     ALNR_LAUNCHED();
-    int st;
+    int st = fill_mark(false);
+    if (st) return st;
     if (numeric == ALNR_NUM_F64) st = launch_exact<double>(*this, c, cv, dl, fo, d_hcol_d.p, d_matd.p);
     else if (numeric == ALNR_NUM_I32) st = launch_exact<int>(*this, c, cv, dl, fo, d_hcol_i.p, d_mati.p);
     else st = strip_run_chunk(*this, c, cv, dl, fo);
+    if (st) return st;
+    st = fill_mark(true);
     if (st) return st;
     TraceArgs ta{cv, mode, V, d_D.p, dl, fo, to};
     traceback_kernel<<<(c.count + 127) / 128, 128, 0, stream>>>(ta);
     ALNR_LAUNCHED();
   }
-  ALNR_CUDA(cudaEventRecord(ev1, stream));
   return ALNR_OK;
 }
 

@@ -38,7 +38,12 @@ struct alnr_batch_impl {
   DevBuf<int> d_mati, d_hcol_i;
   DevBuf<uint32_t> d_pack;      // packed sequences for the strip kernel
   uint64_t rerun_total = 0;
+  bool profile = false;                 // record events around every fill launch
+  std::vector<cudaEvent_t> fill_events; // pairs (begin, end), filled when profile is set
+  size_t fill_events_used = 0;
   float last_fill_ms = 0.f;
+  int fill_mark(bool end);              // record the next profile event on `stream`
+  int collect_fill_ms();                // after a sync: sum of the fill intervals
 
   ~alnr_batch_impl();
   int init(const alnr_params *p, const alnr_batch *b, bool want_mats);

@@ -134,3 +134,43 @@ def pair_frequencies(pairs, V):
         c = np.bincount(np.concatenate([q, t]), minlength=V).astype(np.float64)
         fr[i] = c / c.sum()
     return fr
+
+
+def dna_read_pairs_torch(first, count, n=150, seed=0xA11C0DE, sub_rate=0.10, device="cuda", block=1 << 20,
+                         out_q=None, out_t=None):
+    """Same pairs as dna_read_pairs, generated on the GPU with torch (bench input setup only —
+    not the product path).  int64 arithmetic wraps like uint64; logical shifts are emulated.
+    Returns (q2d, t2d) uint8 host arrays (written into out_q/out_t when given)."""
+    import torch
+
+    def i64(v):
+        v &= (1 << 64) - 1
+        return v - (1 << 64) if v >= (1 << 63) else v
+
+    G, M1, M2 = i64(0x9E3779B97F4A7C15), i64(0xBF58476D1CE4E5B9), i64(0x94D049BB133111EB)
+
+    def lsr(z, k):
+        return (z >> k) & ((1 << (64 - k)) - 1)
+
+    def mix(z):
+        z = (z ^ lsr(z, 30)) * M1
+        z = (z ^ lsr(z, 27)) * M2
+        return z ^ lsr(z, 31)
+
+    q = out_q if out_q is not None else np.empty((count, n), dtype=np.uint8)
+    t = out_t if out_t is not None else np.empty((count, n), dtype=np.uint8)
+    pos = torch.arange(n, dtype=torch.int64, device=device)[None, :] * M1
+    thr = int(sub_rate * 65536.0)
+    for b0 in range(0, count, block):
+        b1 = min(b0 + block, count)
+        idx = torch.arange(first + b0, first + b1, dtype=torch.int64, device=device)[:, None]
+        s = (idx + i64(seed)) * G + pos
+        h = mix(s + i64(1 * 0x94D049BB133111EB))
+        qb = (h & 3).to(torch.uint8)
+        g = mix(s + i64(2 * 0x94D049BB133111EB))
+        replace = (g & 0xFFFF) < thr
+        rb = (lsr(g, 16) & 3).to(torch.uint8)
+        tb = torch.where(replace, rb, qb)
+        q[b0:b1] = qb.cpu().numpy()
+        t[b0:b1] = tb.cpu().numpy()
+    return q, t

@@ -143,8 +143,10 @@ int alnr_batch_run(alnr_batch_handle *h);               /* kernels only, asynchr
 int alnr_batch_sync(alnr_batch_handle *h);
 int alnr_batch_download(alnr_batch_handle *h, alnr_batch_out *out);
 void *alnr_batch_stream(alnr_batch_handle *h);          /* cudaStream_t the kernels run on */
-/* Runs the batch once between two CUDA events on its own stream; *ms = device time. */
-int alnr_batch_run_timed(alnr_batch_handle *h, float *ms, float *fill_ms);
+/* Runs the batch `steps` times back to back between two CUDA events recorded on its own
+ * stream and waits; *ms_total = device time of all steps.  If fill_ms_total != NULL every
+ * fill-kernel launch is additionally bracketed by events and their sum is returned. */
+int alnr_batch_run_timed(alnr_batch_handle *h, int steps, float *ms_total, float *fill_ms_total);
 int alnr_batch_numeric(alnr_batch_handle *h);           /* domain selected for this batch */
 uint64_t alnr_batch_rerun_count(alnr_batch_handle *h);  /* pairs whose speculation was redone */
 void alnr_batch_destroy(alnr_batch_handle *h);
