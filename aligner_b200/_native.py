@@ -67,6 +67,7 @@ SIGNATURES = {
     "alnr_batch_numeric": (C.c_int, [C.c_void_p]),
     "alnr_batch_rerun_count": (C.c_uint64, [C.c_void_p]),
     "alnr_batch_destroy": (None, [C.c_void_p]),
+    "alnr_measure_int_peak": (C.c_int, [C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "alnr_host_alloc": (C.c_void_p, [C.c_uint64]),
     "alnr_host_free": (None, [C.c_void_p]),
 }

@@ -1,6 +1,8 @@
 // peak.cu — INT32 issue-rate micro-benchmarks used as the roofline denominator
 // (MEASURED_PEAKS.json has no integer peak, so it is measured here).
 // "op" = one 32-bit-lane integer instruction (IADD3 / LOP3 / VIMNMX / IMAD).
+#include <algorithm>
+
 #include "host_util.h"
 
 namespace alnr {

@@ -300,14 +300,8 @@ def main():
 
 
 def measure_int_peak(lib, device):
-    try:
-        fn = lib.alnr_measure_int_peak
-    except AttributeError:
-        return {}
-    fn.restype = C.c_int
-    fn.argtypes = [C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
     alu, mixed = C.c_double(), C.c_double()
-    if fn(device, C.byref(alu), C.byref(mixed)) != 0:
+    if lib.alnr_measure_int_peak(device, C.byref(alu), C.byref(mixed)) != 0:
         return {}
     return {"alu_tops": alu.value / 1e12, "mixed_tops": mixed.value / 1e12}
 

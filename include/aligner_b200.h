@@ -151,6 +151,11 @@ int alnr_batch_numeric(alnr_batch_handle *h);           /* domain selected for t
 uint64_t alnr_batch_rerun_count(alnr_batch_handle *h);  /* pairs whose speculation was redone */
 void alnr_batch_destroy(alnr_batch_handle *h);
 
+/* Roofline denominators measured on the device: arithmetic INT32 ops/s (an op = one
+ * 32-bit add / max / logic op / multiply-add lane) of alu-pipe-only chains and of a 1:1
+ * alu-pipe + fma-pipe mix over all SMs. */
+int alnr_measure_int_peak(int device, double *alu_ops_per_s, double *mixed_ops_per_s);
+
 /* pinned host memory helpers for callers without a CUDA binding */
 void *alnr_host_alloc(uint64_t bytes);
 void alnr_host_free(void *p);
