@@ -285,6 +285,12 @@ int alnr_batch_impl::download(alnr_batch_out *out) {
   ALNR_CUDA(cp(out->q_aln, d_qaln.p, q_total + t_total + count));
   ALNR_CUDA(cp(out->t_aln, d_taln.p, q_total + t_total + count));
   ALNR_CUDA(cudaStreamSynchronize(stream));
+  if (numeric == ALNR_NUM_I16X2 && mode == ALNR_LOCAL && del != ext) {
+    uint64_t fc[4];
+    int st = strip_fail_counts(*this, fc);
+    if (st) return st;
+    rerun_total = fc[0];
+  }
   return ALNR_OK;
 }
 

@@ -49,6 +49,8 @@ struct ExactArgs {
   FillOut fo;
   double *H_out;     // optional, single-pair calls only: (m+1)*(n+1) row-major
   uint8_t *D_out;    // optional, 1 byte per cell
+  const uint32_t *list = nullptr;        // optional: chunk slots to process (strip leftovers)
+  const uint32_t *list_count = nullptr;
 };
 
 // grid: ceil(count/128) blocks of 128 threads; smem: V*V*sizeof(T)
@@ -59,17 +61,24 @@ __global__ void __launch_bounds__(128) fill_exact_kernel(ExactArgs<T> a) {
   for (int i = threadIdx.x; i < a.V * a.V; i += blockDim.x) smat[i] = a.matrix[i];
   __syncthreads();
 
-  const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
+  uint32_t slot = idx;
+  if (a.list) {
+    if (idx >= *a.list_count) return;
+    slot = a.list[idx];
+  }
   if (slot >= a.cv.count) return;
   const uint32_t pair = a.cv.order ? a.cv.order[a.cv.first + slot] : a.cv.first + slot;
-  if (a.fo.status[pair] != 0) return;  // rejected by validation (empty / bad symbol)
+  // rejected by validation (empty / bad symbol); 11 may be left over from a speculative pass
+  if (a.fo.status[pair] != 0 && !(a.list && a.fo.status[pair] == 11)) return;
+  if (a.list) a.fo.status[pair] = 0;
 
   const uint8_t *q = a.cv.q + a.cv.q_off[pair];
   const uint8_t *t = a.cv.t + a.cv.t_off[pair];
   const uint32_t n = (uint32_t)(a.cv.q_off[pair + 1] - a.cv.q_off[pair]);
   const uint32_t m = (uint32_t)(a.cv.t_off[pair + 1] - a.cv.t_off[pair]);
   const bool glob = a.mode == 0;
-  const uint32_t group = slot >> 5, lane = slot & 31;
+  const uint32_t group = idx >> 5, lane = idx & 31;  // score-column scratch is per thread
   T *hc = a.hcol + (uint64_t)group * a.hrows * 32 + lane;  // hc[y*32]
   const uint32_t rpw = a.dl.rows_per_word;
   const size_t W = (size_t)n + 1;

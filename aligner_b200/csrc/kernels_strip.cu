@@ -1,15 +1,158 @@
-// kernels_strip.cu — s16x2 strip kernel family (placeholder: not yet eligible for any batch).
+// kernels_strip.cu — host side of the s16x2 strip kernel family: eligibility, one-time packing,
+// and the per-chunk launch sequence (speculative pass, re-run passes, exact leftovers).
+#include <algorithm>
+#include <cmath>
+
+#include "kernels_exact.cuh"
+#include "kernels_strip.cuh"
 #include "strip_launch.h"
 
 namespace alnr {
 
-bool strip_eligible(const alnr_batch_impl &, double) { return false; }
-uint32_t d_rows_per_word(const alnr_batch_impl &, uint32_t) { return 16; }
-int strip_prepare(alnr_batch_impl &) { return ALNR_OK; }
-int strip_run_chunk(alnr_batch_impl &, const Chunk &, const ChunkView &, const DLayout &,
-                    const FillOut &) {
-  set_error_detail("strip kernel not built");
-  return ALNR_CALCULATION_ERROR;
+static const int kRedoPasses = 3;
+
+// Packed 16-bit lanes are exact when: DNA-sized alphabet (4 score bytes per query symbol),
+// scores fit a signed byte, 1 <= ext <= del (penalty update by one multiply-add without
+// carries between lanes), every |H| < 2^15 with headroom, uniform lengths, and the strip's
+// boundary row fits shared memory.
+bool strip_eligible(const alnr_batch_impl &B, double bound) {
+  if (B.V > 4 || !B.uniform || B.count < 1) return false;
+  if (B.want_matrices) return false;  // single-pair calls that also return H and D
+  if (B.n_max < 1 || B.m_max < 1) return false;
+  if (bound >= 30000.0) return false;
+  if (!(B.ext >= 1.0 && B.del >= B.ext && B.del <= 4096.0)) return false;
+  for (double v : B.matrix) if (std::fabs(v) > 127.0) return false;
+  if (((size_t)B.n_max + 1) * kStripBlock * 4 > 200 * 1024) return false;
+  return true;
+}
+
+static uint32_t pick_rows(uint32_t m) {
+  const uint32_t p16 = (m + 15) / 16 * 16 - m, p15 = (m + 14) / 15 * 15 - m;
+  return p15 < p16 ? 15 : 16;
+}
+
+uint32_t d_rows_per_word(const alnr_batch_impl &B, uint32_t m) {
+  return B.numeric == ALNR_NUM_I16X2 ? pick_rows(m) : 16;
+}
+
+int strip_prepare(alnr_batch_impl &B) {
+  const uint32_t nwq = (B.n_max + 15) / 16, nwt = (B.m_max + 15) / 16;
+  const uint64_t groups = (B.count + 31) / 32;
+  ALNR_CUDA(B.d_pack.alloc(groups * 32 * ((uint64_t)nwq + nwt)));
+  uint32_t *qpk = B.d_pack.p, *tpk = B.d_pack.p + groups * 32 * nwq;
+  const uint32_t *order = B.uniform ? nullptr : B.d_order.p;
+  uint64_t threads = groups * 32 * nwq;
+  pack2bit_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, B.stream>>>(B.d_q.p, B.d_qoff.p, order,
+                                                                          (uint32_t)B.count, nwq, qpk);
+  ALNR_LAUNCHED();
+  threads = groups * 32 * nwt;
+  pack2bit_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, B.stream>>>(B.d_t.p, B.d_toff.p, order,
+                                                                          (uint32_t)B.count, nwt, tpk);
+  ALNR_LAUNCHED();
+  // speculation plumbing: two z buffers, two lists, counters (sized for the largest chunk)
+  uint32_t cmax = 0;
+  for (const Chunk &c : B.chunks) cmax = std::max(cmax, c.count);
+  const uint32_t nzw = (B.n_max + 31) / 32;
+  // layout of d_rerun: [counters 8 per chunk][list0 cmax][list1 cmax][z0 cmax*nzw][z1 cmax*nzw]
+  ALNR_CUDA(B.d_rerun.alloc(8 * B.chunks.size() + 2ull * cmax + 2ull * cmax * nzw));
+  return ALNR_OK;
+}
+
+template <int R>
+static int launch_strip(alnr_batch_impl &B, const StripArgs &a, uint32_t duos, bool local, bool stateful) {
+  const size_t smem = ((size_t)a.n + 1) * kStripBlock * 4;
+  const unsigned blocks = (duos + kStripBlock - 1) / kStripBlock;
+  if (blocks == 0) return ALNR_OK;
+#define ALNR_STRIP_LAUNCH(L, S)                                                                   \
+  do {                                                                                            \
+    static bool attr_done = false;                                                                \
+    if (!attr_done) {                                                                             \
+      ALNR_CUDA(cudaFuncSetAttribute(fill_strip_kernel<R, L, S>,                                  \
+                                     cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));   \
+      attr_done = true;                                                                           \
+    }                                                                                             \
+    fill_strip_kernel<R, L, S><<<blocks, kStripBlock, smem, B.stream>>>(a);                       \
+  } while (0)
+  if (!local) ALNR_STRIP_LAUNCH(false, false);
+  else if (stateful) ALNR_STRIP_LAUNCH(true, true);
+  else ALNR_STRIP_LAUNCH(true, false);
+#undef ALNR_STRIP_LAUNCH
+  ALNR_LAUNCHED();
+  return ALNR_OK;
+}
+
+int strip_run_chunk(alnr_batch_impl &B, const Chunk &c, const ChunkView &cv, const DLayout &dl,
+                    const FillOut &fo) {
+  const uint32_t nwq = (B.n_max + 15) / 16, nwt = (B.m_max + 15) / 16;
+  const uint64_t groups = (B.count + 31) / 32;
+  uint32_t cmax = 0;
+  for (const Chunk &k : B.chunks) cmax = std::max(cmax, k.count);
+  const uint32_t nzw = (B.n_max + 31) / 32;
+  const size_t ci = &c - B.chunks.data(), base = 8 * B.chunks.size();
+  uint32_t *counters = B.d_rerun.p + 8 * ci;
+  uint32_t *lists[2] = {B.d_rerun.p + base, B.d_rerun.p + base + cmax};
+  uint32_t *zbuf[2] = {B.d_rerun.p + base + 2ull * cmax, B.d_rerun.p + base + 2ull * cmax + (uint64_t)cmax * nzw};
+
+  const bool local = B.mode == ALNR_LOCAL;
+  const bool stateful = local && B.del != B.ext;
+  StripArgs a;
+  a.qpk = B.d_pack.p;
+  a.tpk = B.d_pack.p + groups * 32 * nwq;
+  a.nwq = nwq; a.nwt = nwt; a.n = B.n_max; a.m = B.m_max;
+  a.first = c.first; a.count = c.count;
+  a.order = cv.order;
+  for (int qs = 0; qs < 4; ++qs) {
+    uint32_t w = 0;
+    for (int ts = 0; ts < 4; ++ts) {
+      int v = (qs < B.V && ts < B.V) ? (int)B.matrix[(size_t)ts * B.V + qs] : 0;
+      w |= ((uint32_t)v & 0xffu) << (8 * ts);
+    }
+    a.wtab[qs] = w;
+  }
+  a.del = (int)B.del; a.ext = (int)B.ext;
+  a.D = B.d_D.p; a.dl = dl; a.fo = fo;
+  a.list = nullptr; a.list_count = nullptr; a.z_in = nullptr; a.z_out = zbuf[0]; a.nzw = nzw;
+  a.fail_list = lists[0]; a.fail_count = counters + 0;
+  const uint32_t R = dl.rows_per_word;
+  auto go = [&](const StripArgs &args, uint32_t duos) {
+    return R == 15 ? launch_strip<15>(B, args, duos, local, stateful)
+                   : launch_strip<16>(B, args, duos, local, stateful);
+  };
+  if (stateful) ALNR_CUDA(cudaMemsetAsync(counters, 0, 8 * sizeof(uint32_t), B.stream));
+  int st = go(a, (c.count + 63) / 64 * 32);
+  if (st || !stateful) return st;
+
+  // re-run passes over the (device-side) fail list; grids are sized for the worst case and
+  // exit at once past the list length, so no host synchronisation is needed.
+  for (int pass = 0; pass < kRedoPasses; ++pass) {
+    StripArgs r = a;
+    r.list = lists[pass & 1]; r.list_count = counters + pass;
+    r.z_in = zbuf[pass & 1]; r.z_out = zbuf[(pass + 1) & 1];
+    r.fail_list = lists[(pass + 1) & 1]; r.fail_count = counters + pass + 1;
+    // expected fail fraction shrinks quickly; cap the grid at the full chunk anyway
+    st = go(r, (c.count + 1) / 2);
+    if (st) return st;
+  }
+  // leftovers: exact column-major kernel over the last list
+  ExactArgs<int> e;
+  e.cv = cv; e.mode = B.mode; e.V = B.V; e.del = (int)B.del; e.ext = (int)B.ext;
+  e.matrix = B.d_mati.p; e.hcol = B.d_hcol_i.p; e.hrows = c.m_max + 1; e.D = B.d_D.p; e.dl = dl; e.fo = fo;
+  e.H_out = nullptr; e.D_out = nullptr;
+  e.list = lists[kRedoPasses & 1]; e.list_count = counters + kRedoPasses;
+  fill_exact_kernel<int><<<(c.count + 127) / 128, 128, (size_t)B.V * B.V * sizeof(int), B.stream>>>(e);
+  ALNR_LAUNCHED();
+  return ALNR_OK;
+}
+
+// pairs re-run after pass k (k = 0: after the speculative pass), summed over chunks (diagnostic)
+int strip_fail_counts(alnr_batch_impl &B, uint64_t out[4]) {
+  std::vector<uint32_t> h(8 * B.chunks.size());
+  ALNR_CUDA(cudaMemcpyAsync(h.data(), B.d_rerun.p, h.size() * sizeof(uint32_t), cudaMemcpyDeviceToHost, B.stream));
+  ALNR_CUDA(cudaStreamSynchronize(B.stream));
+  for (int k = 0; k < 4; ++k) out[k] = 0;
+  for (size_t c = 0; c < B.chunks.size(); ++c)
+    for (int k = 0; k < 4; ++k) out[k] += h[8 * c + k];
+  return ALNR_OK;
 }
 
 }  // namespace alnr

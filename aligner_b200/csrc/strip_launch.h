@@ -14,4 +14,7 @@ int strip_prepare(alnr_batch_impl &B);
 int strip_run_chunk(alnr_batch_impl &B, const Chunk &c, const ChunkView &cv, const DLayout &dl,
                     const FillOut &fo);
 
+// diagnostic: pairs on the re-run list after pass 0..3, summed over chunks (synchronises).
+int strip_fail_counts(alnr_batch_impl &B, uint64_t out[4]);
+
 }  // namespace alnr

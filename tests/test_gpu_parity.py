@@ -158,3 +158,61 @@ def test_device_batch_rerun_is_idempotent():
     for k in ("f", "coords", "aln_len", "aln_off", "q_aln", "t_aln"):
         assert (getattr(a, k) == getattr(b, k)).all()
     db.close()
+
+
+# ---- the packed 16-bit strip kernel (two pairs per thread) -------------------------------
+def _rand_uniform_pairs(rng, count, n, m, related=True):
+    q = rng.integers(0, 4, (count, n)).astype(np.uint8)
+    if related and n == m:
+        t = np.where(rng.random((count, n)) < 0.12, rng.integers(0, 4, (count, n)), q).astype(np.uint8)
+    else:
+        t = rng.integers(0, 4, (count, m)).astype(np.uint8)
+    return ab.PackedPairs.uniform(q, t)
+
+
+@pytest.mark.parametrize("n,m,count", [(150, 150, 640), (150, 150, 33), (37, 61, 200), (64, 16, 130),
+                                       (1, 1, 70), (5, 150, 64), (151, 149, 257), (300, 31, 65)])
+@pytest.mark.parametrize("mode,d,e", [("local", 10, 2), ("local", 6, 6), ("global", 10, 2), ("global", 4, 4)])
+def test_strip_kernel_shapes(n, m, count, mode, d, e):
+    rng = np.random.default_rng(n * 1000 + m + count)
+    pairs = _rand_uniform_pairs(rng, count, n, m)
+    _check_batch(mode, pairs, d, e, ab.dna_matrix(5, -4), numeric=N.NUM_I16X2)
+
+
+def test_strip_kernel_many_speculation_failures():
+    """+1/-1 scores with del=2, ext=1 on unrelated pairs: H[m][x] == 0 is frequent, so the
+    speculative pass fails for most pairs and the re-run passes / exact leftovers do the work."""
+    rng = np.random.default_rng(123)
+    pairs = _rand_uniform_pairs(rng, 1500, 60, 45, related=False)
+    M = ab.dna_matrix(1, -1)
+    ref = O.align_batch("local", pairs, 2.0, 1.0, M, threads=8)
+    db = ab.DeviceBatch(N.LOCAL, pairs, M, 2, 1, numeric=N.NUM_I16X2)
+    db.run(); db.sync()
+    res = db.download()
+    assert db.numeric == N.NUM_I16X2 and db.rerun_count > 100
+    ok = ref["status"] == 0
+    assert ((res.status == 0) == ok).all()
+    assert (res.f[ok] == ref["f"][ok]).all() and (res.coords[ok] == ref["coords"][ok]).all()
+    for i in np.nonzero(ok)[0]:
+        qa, ta = res.alignment(i)
+        L = int(ref["aln_len"][i])
+        assert (qa == ref["q_aln"][i, :L]).all() and (ta == ref["t_aln"][i, :L]).all(), i
+    db.close()
+
+
+def test_strip_matches_exact_domains_on_asymmetric_matrix():
+    rng = np.random.default_rng(77)
+    pairs = _rand_uniform_pairs(rng, 300, 90, 90)
+    M = rng.integers(-6, 8, (4, 4)).astype(np.float64)
+    for mode, d, e in [("local", 9, 3), ("global", 7, 2)]:
+        a = _check_batch(mode, pairs, d, e, M, numeric=N.NUM_I16X2)
+        b = _check_batch(mode, pairs, d, e, M, numeric=N.NUM_I32)
+        c = _check_batch(mode, pairs, d, e, M, numeric=N.NUM_F64)
+        assert (a.f == b.f).all() and (b.f == c.f).all()
+
+
+def test_auto_selects_strip_for_config3():
+    pairs = W.dna_read_batch(0, 256, n=150)
+    db = ab.DeviceBatch(N.LOCAL, pairs, ab.dna_matrix(), 10, 2)
+    assert db.numeric == N.NUM_I16X2
+    db.close()
