@@ -119,7 +119,7 @@ int alnr_batch_impl::plan_chunks(const uint64_t *q_off, const uint64_t *t_off) {
     m = std::max(m, 1u); n = std::max(n, 1u);
     const uint32_t rpw = d_rows_per_word(*this, m);
     const uint64_t nstrips = (m + rpw - 1) / rpw;
-    const uint64_t per_group = (nstrips * n * 4 + ((uint64_t)m + 1) * num_sz + (uint64_t)(n + 1) * 4) * 32;
+    const uint64_t per_group = (nstrips * ((n + 3) / 4 * 4) * 4 + ((uint64_t)m + 1) * num_sz + (uint64_t)(n + 1) * 4) * 32;
     uint64_t groups = std::max<uint64_t>(budget / per_group, 1);
     uint64_t c = std::min<uint64_t>(groups * 32, count - s);
     if (c < count - s) c = std::max<uint64_t>(c / 64 * 64, 32);  // keep duo-kernel warps whole
@@ -203,8 +203,7 @@ int alnr_batch_impl::init(const alnr_params *p, const alnr_batch *b, bool want_m
 
   uint64_t dwords = 1, hcol = 1;
   for (const Chunk &c : chunks) {
-    DLayout dl{d_rows_per_word(*this, c.m_max), 0, c.n_max};
-    dl.nstrips = (c.m_max + dl.rows_per_word - 1) / dl.rows_per_word;
+    const DLayout dl = DLayout::make(d_rows_per_word(*this, c.m_max), c.m_max, c.n_max, numeric == ALNR_NUM_I16X2);
     dwords = std::max<uint64_t>(dwords, dl.words_for(c.count));
     hcol = std::max<uint64_t>(hcol, (uint64_t)((c.count + 31) / 32) * 32 * ((uint64_t)std::max(c.m_max, c.n_max) + 1));
   }
@@ -249,8 +248,7 @@ int alnr_batch_impl::run() {
   rerun_total = 0;
   for (const Chunk &c : chunks) {
     ChunkView cv{d_q.p, d_t.p, d_qoff.p, d_toff.p, uniform ? nullptr : d_order.p, c.first, c.count};
-    DLayout dl{d_rows_per_word(*this, c.m_max), 0, c.n_max};
-    dl.nstrips = (c.m_max + dl.rows_per_word - 1) / dl.rows_per_word;
+    const DLayout dl = DLayout::make(d_rows_per_word(*this, c.m_max), c.m_max, c.n_max, numeric == ALNR_NUM_I16X2);
     validate_kernel<<<(c.count + 127) / 128, 128, 0, stream>>>(cv, V, d_status.p, d_flags.p);
     ALNR_LAUNCHED();
     int st = fill_mark(false);
@@ -262,7 +260,13 @@ int alnr_batch_impl::run() {
     st = fill_mark(true);
     if (st) return st;
     TraceArgs ta{cv, mode, V, d_D.p, dl, fo, to};
-    traceback_kernel<<<(c.count + 127) / 128, 128, 0, stream>>>(ta);
+    const uint32_t nmw = (c.n_max + c.m_max + 1 + 15) / 16;  // 2-bit move words per pair
+    if ((size_t)nmw * kTraceBlock * 4 <= 44 * 1024 && to.freq == nullptr) {
+      traceback_coop_kernel<<<(c.count + kTraceBlock - 1) / kTraceBlock, kTraceBlock,
+                              (size_t)nmw * kTraceBlock * 4, stream>>>(ta, nmw);
+    } else {
+      traceback_kernel<<<(c.count + 127) / 128, 128, 0, stream>>>(ta);
+    }
     ALNR_LAUNCHED();
   }
   return ALNR_OK;

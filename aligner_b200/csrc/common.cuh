@@ -18,16 +18,33 @@ constexpr int kBlank = 98;
 // nstrips / ncols are the chunk-wide maxima.  Row 0 and column 0 are never stored: their
 // directions are fixed by the mode (simple/mod.rs:59-67 global, :181-183 local).
 // ---------------------------------------------------------------------------------------
+//
+// Two address maps share that word numbering:
+//  * interleaved (above): used by the one-pair-per-thread exact kernel, whose 32 lanes store
+//    word (strip, x) of 32 different pairs in the same instruction -> one 128-byte line;
+//  * contiguous: word index = (slot * nstrips + strip) * ncols + (x-1), ncols a multiple of 4.
+//    Used by the strip kernel, which stores 4 columns of one pair as one 16-byte vector, so a
+//    traceback that moves along x reads 8 consecutive cells' words from one 32-byte sector.
 struct DLayout {
   uint32_t rows_per_word;
   uint32_t nstrips;
   uint32_t ncols;
+  uint32_t contiguous;
   __host__ __device__ inline uint64_t word(uint32_t slot, uint32_t strip, uint32_t xm1) const {
+    if (contiguous) return ((uint64_t)slot * nstrips + strip) * ncols + xm1;
     uint32_t group = slot >> 5, lane = slot & 31;
     return (((uint64_t)group * nstrips + strip) * ncols + xm1) * 32ull + lane;
   }
   __host__ __device__ inline uint64_t words_for(uint64_t slots) const {
     return ((slots + 31) / 32) * (uint64_t)nstrips * ncols * 32ull;
+  }
+  static inline DLayout make(uint32_t rows_per_word, uint32_t m_max, uint32_t n_max, bool contig) {
+    DLayout d;
+    d.rows_per_word = rows_per_word;
+    d.nstrips = (m_max + rows_per_word - 1) / rows_per_word;
+    d.ncols = contig ? (n_max + 3) / 4 * 4 : n_max;
+    d.contiguous = contig ? 1u : 0u;
+    return d;
   }
 };
 

@@ -68,85 +68,62 @@ struct Best {
   int strip;
 };
 
-template <int R, bool LOCAL, bool STATEFUL>
-__global__ void __launch_bounds__(kStripBlock) fill_strip_kernel(StripArgs a) {
-  extern __shared__ uint32_t smem[];
-  __shared__ uint32_t swt[4];
-  const uint32_t tid = threadIdx.x;
-  uint32_t *hrow = smem + tid;  // hrow[x * kStripBlock]: bottom row of the previous strip
-  if (tid < 4) swt[tid] = a.wtab[tid];
-  __syncthreads();
-
-  // ---- which two slots ---------------------------------------------------------------
-  const uint32_t duo = blockIdx.x * kStripBlock + tid;
+// Per-thread state that lives across strips.
+struct StripCtx {
+  const uint32_t *qA, *qB, *tA, *tB;
+  uint32_t *dA, *dB;      // D words of the two slots (contiguous layout), strip 0
+  uint4 *hrow;            // smem: bottom row of the previous strip, [group*kStripBlock], x-1 = 4*group + j
   uint32_t sA, sB;
-  bool dupB = false;
-  if (a.list) {
-    const uint32_t cnt = *a.list_count;
-    if (2 * duo >= cnt) return;
-    sA = a.list[2 * duo];
-    if (2 * duo + 1 < cnt) sB = a.list[2 * duo + 1]; else { sB = sA; dupB = true; }
-  } else {
-    sA = (duo >> 5) * 64 + (duo & 31);
-    if (sA >= a.count) return;
-    sB = sA + 32;
-    if (sB >= a.count) { sB = sA; dupB = true; }
-  }
-  const uint32_t bA = a.first + sA, bB = a.first + sB;  // batch slots
-  const uint32_t *qA = a.qpk + ((size_t)(bA >> 5) * a.nwq) * 32 + (bA & 31);
-  const uint32_t *qB = a.qpk + ((size_t)(bB >> 5) * a.nwq) * 32 + (bB & 31);
-  const uint32_t *tA = a.tpk + ((size_t)(bA >> 5) * a.nwt) * 32 + (bA & 31);
-  const uint32_t *tB = a.tpk + ((size_t)(bB >> 5) * a.nwt) * 32 + (bB & 31);
-  const uint32_t n = a.n, m = a.m;
-  const uint32_t nstrips = (m + R - 1) / R;
-  const size_t dstrip = (size_t)a.dl.ncols * 32;  // words between strips of one slot
-  uint32_t *dA = a.D + a.dl.word(sA, 0, 0);
-  uint32_t *dB = a.D + a.dl.word(sB, 0, 0);
+  bool dupB;
+  Best bestA, bestB;
+  uint32_t mismatch;      // bit0: pair A, bit16: pair B
+  uint32_t corner;
+};
 
+// One strip of R rows swept over all columns.  LASTSTRIP: the strip holding row m (it may
+// have fewer than R valid rows); only there are z bits observed and the corner recorded.
+template <int R, bool LOCAL, bool STATEFUL, bool LASTSTRIP>
+__device__ __forceinline__ void strip_sweep(const StripArgs &a, StripCtx &c, const uint32_t *swt,
+                                            uint32_t strip) {
+  const uint32_t n = a.n, m = a.m, tid = threadIdx.x;
+  const uint32_t y0 = strip * R;
+  const uint32_t rv = LASTSTRIP ? m - y0 : R;  // valid rows
   const uint32_t ndel2 = pack2(-a.del, -a.del), next2 = pack2(-a.ext, -a.ext);
-  const int dme = a.del - a.ext;
+  const uint32_t dme = (uint32_t)(a.del - a.ext);
   const uint32_t one2 = 0x00010001u;
 
-  // ---- row 0 (simple/mod.rs:59-62,69 global; zeros local) -------------------------------
-  for (uint32_t x = 0; x <= n; ++x) {
-    int v = 0;
-    if (!LOCAL && x > 0) v = (x == n) ? -(int)(n + 1) * a.del : -(int)x * a.del;
-    hrow[x * kStripBlock] = pack2(v, v);
-  }
-
-  Best bestA{0, 0, 0, -1}, bestB{0, 0, 0, -1};
-  uint32_t mismatch = 0;  // bit0: pair A, bit16: pair B
-  uint32_t corner = 0;
-
-  for (uint32_t strip = 0; strip < nstrips; ++strip) {
-    const uint32_t y0 = strip * R;
-    const bool last = strip + 1 == nstrips;
-    const uint32_t rv = last ? m - y0 : R;  // valid rows in this strip
-    uint32_t sel[R], h[R];
+  uint32_t sel[R], h[R];
 #pragma unroll
-    for (int r = 0; r < R; ++r) {
-      const uint32_t y = y0 + r;  // 0-based target index
-      const uint32_t ta = y < m ? sym2(tA, y) : 0u, tb = y < m ? sym2(tB, y) : 0u;
-      sel[r] = ta | ((8u | ta) << 4) | ((4u + tb) << 8) | ((12u + tb) << 12);
-      int v = 0;
-      if (!LOCAL) v = (y + 1 == m) ? -(int)(m + 1) * a.del : -(int)(y + 1) * a.del;  // :64-67,:70
-      h[r] = pack2(v, v);
-    }
-    uint32_t hdiag0 = hrow[0];
-    hrow[0] = h[R - 1];
-    int thrA = (bestA.strip == (int)strip) ? bestA.v : bestA.v + 1;
-    int thrB = (bestB.strip == (int)strip) ? bestB.v : bestB.v + 1;
-    uint32_t nthr = pack2(-thrA, -thrB);
-    uint32_t zacc = 0, zaccB = 0;
-    uint32_t qwA = 0, qwB = 0;
-    uint32_t *dpA = dA + strip * dstrip, *dpB = dB + strip * dstrip;
+  for (int r = 0; r < R; ++r) {
+    const uint32_t y = y0 + r;  // 0-based target index
+    const uint32_t ta = y < m ? sym2(c.tA, y) : 0u, tb = y < m ? sym2(c.tB, y) : 0u;
+    sel[r] = ta | ((8u | ta) << 4) | ((4u + tb) << 8) | ((12u + tb) << 12);
+    int v = 0;
+    if (!LOCAL) v = (y + 1 == m) ? -(int)(m + 1) * a.del : -(int)(y + 1) * a.del;  // :64-67,:70
+    h[r] = pack2(v, v);
+  }
+  // H[y0][0]: 0 in local mode, -y0*del in global mode (the -(m+1)*del quirk sits on row m only)
+  uint32_t hdiag0 = LOCAL ? 0u : pack2(-(int)y0 * a.del, -(int)y0 * a.del);
+  int thrA = (c.bestA.strip == (int)strip) ? c.bestA.v : c.bestA.v + 1;
+  int thrB = (c.bestB.strip == (int)strip) ? c.bestB.v : c.bestB.v + 1;
+  uint32_t nthr = pack2(-thrA, -thrB);
+  uint32_t zacc = 0, zaccB = 0;
+  uint32_t qwA = 0, qwB = 0;
+  const size_t dstrip = (size_t)a.dl.ncols;
+  uint32_t *dpA = c.dA + strip * dstrip, *dpB = c.dB + strip * dstrip;
+  const uint32_t ngroups = (n + 3) >> 2;
 
-    for (uint32_t x = 1; x <= n; ++x) {
-      const uint32_t xm1 = x - 1;
-      if ((xm1 & 15) == 0) { qwA = qA[(size_t)(xm1 >> 4) * 32]; qwB = qB[(size_t)(xm1 >> 4) * 32]; }
-      const uint32_t Wa = swt[qwA & 3], Wb = swt[qwB & 3];
-      qwA >>= 2; qwB >>= 2;
-      uint32_t hup = hrow[x * kStripBlock];
+  for (uint32_t g = 0; g < ngroups; ++g) {
+    if ((g & 3) == 0) { qwA = c.qA[(size_t)(g >> 2) * 32]; qwB = c.qB[(size_t)(g >> 2) * 32]; }
+    const uint4 hu = c.hrow[g * kStripBlock + tid];
+    uint32_t hv[4] = {hu.x, hu.y, hu.z, hu.w};
+    uint32_t wA[4] = {0, 0, 0, 0}, wB[4] = {0, 0, 0, 0};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const uint32_t xm1 = 4 * g + j, x = xm1 + 1;
+      if (x > n) break;
+      const uint32_t Wa = swt[(qwA >> (2 * j)) & 3], Wb = swt[(qwB >> (2 * j)) & 3];
+      uint32_t hup = hv[j];
       uint32_t diag = hdiag0;
       hdiag0 = hup;
       // penalty of the strip's first row
@@ -155,12 +132,12 @@ __global__ void __launch_bounds__(kStripBlock) fill_strip_kernel(StripArgs a) {
         if (strip == 0) {
           int zA = x == 1, zB = x == 1;
           if (a.z_in && x > 1) {
-            zA = (a.z_in[(size_t)sA * a.nzw + ((x - 2) >> 5)] >> ((x - 2) & 31)) & 1;
-            zB = (a.z_in[(size_t)sB * a.nzw + ((x - 2) >> 5)] >> ((x - 2) & 31)) & 1;
+            zA = (a.z_in[(size_t)c.sA * a.nzw + ((x - 2) >> 5)] >> ((x - 2) & 31)) & 1;
+            zB = (a.z_in[(size_t)c.sB * a.nzw + ((x - 2) >> 5)] >> ((x - 2) & 31)) & 1;
           }
           np = pack2(zA ? -a.del : -a.ext, zB ? -a.del : -a.ext);
         } else {
-          np = __vminu2(hup, one2) * (uint32_t)dme + ndel2;  // cell above: Beginning iff == 0
+          np = __vminu2(hup, one2) * dme + ndel2;  // cell above: Beginning iff == 0
         }
       } else {
         np = (!LOCAL && strip == 0 && x == 1) ? ndel2 : next2;  // simple/mod.rs:72: first cell pays del
@@ -181,8 +158,8 @@ __global__ void __launch_bounds__(kStripBlock) fill_strip_kernel(StripArgs a) {
           const uint32_t b0 = (~nz | (neT & ~neL)) & one2;
           const uint32_t b1 = (~nz | (neT & neL)) & one2;
           code = b0 + 2 * b1;
-          if (STATEFUL) np = nz * (uint32_t)dme + ndel2;  // simple/mod.rs:201-205
-          if (STATEFUL && last && (uint32_t)r + 1 == rv) nzm = nz;  // row m
+          if (STATEFUL) np = nz * dme + ndel2;  // simple/mod.rs:201-205
+          if (STATEFUL && LASTSTRIP && (uint32_t)r + 1 == rv) nzm = nz;  // row m
         } else {
           code = neT + (neT & neL);  // enums.rs:21-27
           np = next2;
@@ -191,11 +168,11 @@ __global__ void __launch_bounds__(kStripBlock) fill_strip_kernel(StripArgs a) {
         diag = h[r];
         h[r] = mx;
         hup = mx;
-        if (LOCAL) { if (!last || (uint32_t)r < rv) cm = __vmaxs2(cm, mx); }
+        if (LOCAL) { if (!LASTSTRIP || (uint32_t)r < rv) cm = __vmaxs2(cm, mx); }
       }
-      hrow[x * kStripBlock] = h[R - 1];
-      dpA[(size_t)xm1 * 32] = (accLo & 0xffffu) | (accHi << 16);
-      dpB[(size_t)xm1 * 32] = (accLo >> 16) | (accHi & 0xffff0000u);
+      hv[j] = h[R - 1];
+      wA[j] = (accLo & 0xffffu) | (accHi << 16);
+      wB[j] = (accLo >> 16) | (accHi & 0xffff0000u);
 
       if (LOCAL) {
         // any lane with column max >= threshold?  (threshold = best, or best+1 if the best
@@ -208,19 +185,19 @@ __global__ void __launch_bounds__(kStripBlock) fill_strip_kernel(StripArgs a) {
 #pragma unroll
             for (int r = R - 1; r >= 0; --r) if (lane_lo(h[r]) == cA && (uint32_t)r < rv) r0 = r;
             const uint32_t y = y0 + r0 + 1;
-            if (cA > bestA.v || y < bestA.y) { bestA = Best{cA, y, x, (int)strip}; thrA = cA; }
+            if (cA > c.bestA.v || y < c.bestA.y) { c.bestA = Best{cA, y, x, (int)strip}; thrA = cA; }
           }
           if (cB >= thrB) {
             uint32_t r0 = 0;
 #pragma unroll
             for (int r = R - 1; r >= 0; --r) if (lane_hi(h[r]) == cB && (uint32_t)r < rv) r0 = r;
             const uint32_t y = y0 + r0 + 1;
-            if (cB > bestB.v || y < bestB.y) { bestB = Best{cB, y, x, (int)strip}; thrB = cB; }
+            if (cB > c.bestB.v || y < c.bestB.y) { c.bestB = Best{cB, y, x, (int)strip}; thrB = cB; }
           }
           nthr = pack2(-thrA, -thrB);
         }
       }
-      if (STATEFUL && last) {
+      if (STATEFUL && LASTSTRIP) {
         // observe z[x-1] = (H[m][x] == 0); it sets the penalty of cell (1, x+1)
         const uint32_t z = nzm ^ one2;
         zacc |= (z & 1u) << (xm1 & 31);
@@ -228,24 +205,84 @@ __global__ void __launch_bounds__(kStripBlock) fill_strip_kernel(StripArgs a) {
         if ((xm1 & 31) == 31 || x == n) {
           const uint32_t w = xm1 >> 5;
           uint32_t asA = 0, asB = 0;
-          if (a.z_in) { asA = a.z_in[(size_t)sA * a.nzw + w]; asB = a.z_in[(size_t)sB * a.nzw + w]; }
+          if (a.z_in) { asA = a.z_in[(size_t)c.sA * a.nzw + w]; asB = a.z_in[(size_t)c.sB * a.nzw + w]; }
           // bits at column index >= n-1 never feed a penalty (there is no column n+1)
           const uint32_t nb = (n - 1) - (w << 5);
           const uint32_t valid = (n - 1 <= (w << 5)) ? 0u : (nb >= 32 ? 0xffffffffu : ((1u << nb) - 1u));
-          if ((zacc ^ asA) & valid) mismatch |= 1u;
-          if ((zaccB ^ asB) & valid) mismatch |= 0x10000u;
-          a.z_out[(size_t)sA * a.nzw + w] = zacc;
-          if (!dupB) a.z_out[(size_t)sB * a.nzw + w] = zaccB;
+          if ((zacc ^ asA) & valid) c.mismatch |= 1u;
+          if ((zaccB ^ asB) & valid) c.mismatch |= 0x10000u;
+          a.z_out[(size_t)c.sA * a.nzw + w] = zacc;
+          if (!c.dupB) a.z_out[(size_t)c.sB * a.nzw + w] = zaccB;
           zacc = zaccB = 0;
         }
       }
-      if (last && x == n) {
-        corner = h[R - 1];
+      if (LASTSTRIP && x == n) {
+        c.corner = h[R - 1];
 #pragma unroll
-        for (int r = 0; r < R - 1; ++r) if ((uint32_t)r + 1 == rv) corner = h[r];
+        for (int r = 0; r < R - 1; ++r) if ((uint32_t)r + 1 == rv) c.corner = h[r];
       }
     }
+    qwA >>= 8; qwB >>= 8;
+    if (!LASTSTRIP) c.hrow[g * kStripBlock + tid] = make_uint4(hv[0], hv[1], hv[2], hv[3]);
+    *reinterpret_cast<uint4 *>(dpA + 4 * g) = make_uint4(wA[0], wA[1], wA[2], wA[3]);
+    if (!c.dupB) *reinterpret_cast<uint4 *>(dpB + 4 * g) = make_uint4(wB[0], wB[1], wB[2], wB[3]);
   }
+}
+
+template <int R, bool LOCAL, bool STATEFUL>
+__global__ void __launch_bounds__(kStripBlock) fill_strip_kernel(StripArgs a) {
+  extern __shared__ uint4 smem4[];
+  __shared__ uint32_t swt[4];
+  const uint32_t tid = threadIdx.x;
+  if (tid < 4) swt[tid] = a.wtab[tid];
+  __syncthreads();
+
+  // ---- which two slots ---------------------------------------------------------------
+  const uint32_t duo = blockIdx.x * kStripBlock + tid;
+  StripCtx c;
+  c.dupB = false;
+  if (a.list) {
+    const uint32_t cnt = *a.list_count;
+    if (2 * duo >= cnt) return;
+    c.sA = a.list[2 * duo];
+    if (2 * duo + 1 < cnt) c.sB = a.list[2 * duo + 1]; else { c.sB = c.sA; c.dupB = true; }
+  } else {
+    c.sA = (duo >> 5) * 64 + (duo & 31);
+    if (c.sA >= a.count) return;
+    c.sB = c.sA + 32;
+    if (c.sB >= a.count) { c.sB = c.sA; c.dupB = true; }
+  }
+  const uint32_t bA = a.first + c.sA, bB = a.first + c.sB;  // batch slots
+  c.qA = a.qpk + ((size_t)(bA >> 5) * a.nwq) * 32 + (bA & 31);
+  c.qB = a.qpk + ((size_t)(bB >> 5) * a.nwq) * 32 + (bB & 31);
+  c.tA = a.tpk + ((size_t)(bA >> 5) * a.nwt) * 32 + (bA & 31);
+  c.tB = a.tpk + ((size_t)(bB >> 5) * a.nwt) * 32 + (bB & 31);
+  const uint32_t n = a.n, m = a.m;
+  const uint32_t nstrips = (m + R - 1) / R;
+  c.dA = a.D + a.dl.word(c.sA, 0, 0);
+  c.dB = a.D + a.dl.word(c.sB, 0, 0);
+  c.hrow = smem4;
+  c.bestA = Best{0, 0, 0, -1};
+  c.bestB = Best{0, 0, 0, -1};
+  c.mismatch = 0;
+  c.corner = 0;
+
+  // ---- row 0 (simple/mod.rs:59-62,69 global; zeros local): index x-1 ---------------------
+  for (uint32_t g = 0; g < (n + 3) / 4; ++g) {
+    uint32_t v[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const uint32_t x = 4 * g + j + 1;
+      int hv = 0;
+      if (!LOCAL) hv = (x == n) ? -(int)(n + 1) * a.del : -(int)x * a.del;
+      v[j] = pack2(hv, hv);
+    }
+    c.hrow[g * kStripBlock + tid] = make_uint4(v[0], v[1], v[2], v[3]);
+  }
+
+  for (uint32_t strip = 0; strip + 1 < nstrips; ++strip)
+    strip_sweep<R, LOCAL, STATEFUL, false>(a, c, swt, strip);
+  strip_sweep<R, LOCAL, STATEFUL, true>(a, c, swt, nstrips - 1);
 
   // ---- per-pair results ---------------------------------------------------------------
   auto finish = [&](uint32_t bslot, uint32_t slot, const Best &b, int cval, bool mism) {
@@ -264,8 +301,8 @@ __global__ void __launch_bounds__(kStripBlock) fill_strip_kernel(StripArgs a) {
     }
     if (STATEFUL && mism) a.fail_list[atomicAdd(a.fail_count, 1u)] = slot;
   };
-  finish(bA, sA, bestA, lane_lo(corner), (mismatch & 1u) != 0);
-  if (!dupB) finish(bB, sB, bestB, lane_hi(corner), (mismatch >> 16) != 0);
+  finish(bA, c.sA, c.bestA, lane_lo(c.corner), (c.mismatch & 1u) != 0);
+  if (!c.dupB) finish(bB, c.sB, c.bestB, lane_hi(c.corner), (c.mismatch >> 16) != 0);
 }
 
 // 2-bit packing of one sequence set into the coalesced [(group*nw + w)*32 + lane] layout.

@@ -110,4 +110,100 @@ __global__ void __launch_bounds__(128) traceback_kernel(TraceArgs a) {
   }
 }
 
+// Two-phase traceback for short pairs (n + m + 1 moves fit shared memory).
+//  phase A: one thread per pair chases the 2-bit directions and records its moves
+//           (2 bits each) in shared memory — no global stores on the dependent chain;
+//  phase B: each warp expands the 32 move strings of its pairs cooperatively: 32 moves at a
+//           time, symbol positions by ballot/popc prefix counts, 32 consecutive output bytes
+//           per store instead of one scattered byte per thread.
+constexpr int kTraceBlock = 128;
+
+__global__ void __launch_bounds__(kTraceBlock) traceback_coop_kernel(TraceArgs a, uint32_t nmw) {
+  extern __shared__ uint32_t mv[];  // mv[w * kTraceBlock + tid]
+  __shared__ uint32_t s_len[kTraceBlock], s_sy[kTraceBlock], s_sx[kTraceBlock];
+  const uint32_t tid = threadIdx.x;
+  const uint32_t slot = blockIdx.x * kTraceBlock + tid;
+  const bool glob = a.mode == 0;
+  const uint32_t rpw = a.dl.rows_per_word;
+  uint32_t K = 0xffffffffu;  // marker: no alignment for this thread
+  if (slot < a.cv.count) {
+    const uint32_t pair = a.cv.order ? a.cv.order[a.cv.first + slot] : a.cv.first + slot;
+    const uint64_t qo = a.cv.q_off[pair], to = a.cv.t_off[pair];
+    const uint32_t n = (uint32_t)(a.cv.q_off[pair + 1] - qo);
+    const uint32_t m = (uint32_t)(a.cv.t_off[pair + 1] - to);
+    const uint64_t slot_end = qo + to + pair + n + m + 1;
+    if (a.fo.status[pair] != 0) {
+      if (a.to.aln_len) a.to.aln_len[pair] = 0;
+      if (a.to.aln_off) a.to.aln_off[pair] = slot_end;
+      if (a.to.coords) for (int k = 0; k < 4; ++k) a.to.coords[4 * (size_t)pair + k] = 0;
+    } else {
+      const uint32_t sy = a.fo.start[2 * (size_t)pair], sx = a.fo.start[2 * (size_t)pair + 1];
+      uint32_t cy = sy, cx = sx, acc = 0;
+      K = 0;
+      for (;;) {
+        int d;
+        if (cy == 0 || cx == 0) {
+          if (!glob || (cy == 0 && cx == 0)) d = DIR_BEGINNING;
+          else d = (cy == 0) ? DIR_LEFT : DIR_TOP;
+        } else {
+          const uint32_t w = a.D[a.dl.word(slot, (cy - 1) / rpw, cx - 1)];
+          d = (w >> (2 * ((cy - 1) % rpw))) & 3;
+        }
+        if (d == DIR_BEGINNING) break;
+        acc |= (uint32_t)d << (2 * (K & 15));
+        ++K;
+        if ((K & 15) == 0) { mv[((K >> 4) - 1) * kTraceBlock + tid] = acc; acc = 0; }
+        if (d != DIR_LEFT) --cy;
+        if (d != DIR_TOP) --cx;
+      }
+      if (K & 15) mv[(K >> 4) * kTraceBlock + tid] = acc;
+      if (a.to.aln_len) a.to.aln_len[pair] = K + 1;
+      if (a.to.aln_off) a.to.aln_off[pair] = slot_end - (K + 1);
+      if (a.to.coords) {
+        uint64_t *c = a.to.coords + 4 * (size_t)pair;
+        if (glob) { c[0] = 1; c[1] = n; c[2] = 1; c[3] = m; }
+        else { c[0] = cx + 1; c[1] = sx + 1; c[2] = cy + 1; c[3] = sy + 1; }
+      }
+      s_sy[tid] = sy; s_sx[tid] = sx;
+    }
+  }
+  s_len[tid] = K;
+  __syncwarp();
+  if (a.to.q_aln == nullptr || a.to.t_aln == nullptr) return;
+
+  // ---- phase B: this warp expands its own 32 pairs ------------------------------------
+  const uint32_t lane = tid & 31, wbase = tid & ~31u;
+  const uint32_t ltmask = (1u << lane) - 1u;
+  for (uint32_t pi = 0; pi < 32; ++pi) {
+    const uint32_t col = wbase + pi;
+    const uint32_t Kp = s_len[col];
+    if (Kp == 0xffffffffu) continue;
+    const uint32_t pslot = blockIdx.x * kTraceBlock + col;
+    const uint32_t pair = a.cv.order ? a.cv.order[a.cv.first + pslot] : a.cv.first + pslot;
+    const uint64_t qo = a.cv.q_off[pair], to = a.cv.t_off[pair];
+    const uint8_t *q = a.cv.q + qo, *t = a.cv.t + to;
+    const uint64_t slot_end = qo + to + pair + (a.cv.q_off[pair + 1] - qo) + (a.cv.t_off[pair + 1] - to) + 1;
+    uint32_t cy = s_sy[col], cx = s_sx[col];
+    if (lane == 0) {  // seed column (simple/mod.rs:102-105, :213-216)
+      a.to.q_aln[slot_end - 1] = q[cx - 1];
+      a.to.t_aln[slot_end - 1] = t[cy - 1];
+    }
+    for (uint32_t i0 = 0; i0 < Kp; i0 += 32) {
+      const uint32_t i = i0 + lane;
+      const bool valid = i < Kp;
+      const uint32_t code = valid ? (mv[(i >> 4) * kTraceBlock + col] >> (2 * (i & 15))) & 3u : 3u;
+      const bool cq = valid && code != DIR_TOP, ct = valid && code != DIR_LEFT;
+      const uint32_t bq = __ballot_sync(0xffffffffu, cq), bt = __ballot_sync(0xffffffffu, ct);
+      if (valid) {
+        const uint32_t xi = cx - __popc(bq & ltmask), yi = cy - __popc(bt & ltmask);
+        const uint64_t pos = slot_end - 2 - i;
+        a.to.q_aln[pos] = cq ? q[xi - 1] : (uint8_t)kBlank;
+        a.to.t_aln[pos] = ct ? t[yi - 1] : (uint8_t)kBlank;
+      }
+      cx -= __popc(bq);
+      cy -= __popc(bt);
+    }
+  }
+}
+
 }  // namespace alnr

@@ -209,7 +209,6 @@ def main():
     barrier()
     clocks = sampler.stop()
     numeric = db.numeric
-    reruns = int(db.rerun_count)
     t = torch.tensor([ms_total, fill_total], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -221,6 +220,7 @@ def main():
     if rank == 0:
         import oracle_lib as O
         res = db.download()
+        reruns = int(db.rerun_count)
         sub = W.dna_read_batch(0, 512, n)
         ref = O.align_batch(a.mode, sub, a.dele, a.ext, M, threads=4)
         okp = bool((res.f[:512] == ref["f"]).all() and (res.coords[:512] == ref["coords"]).all()
