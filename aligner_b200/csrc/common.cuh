@@ -30,6 +30,15 @@ struct DLayout {
   uint32_t nstrips;
   uint32_t ncols;
   uint32_t contiguous;
+  // Bit format inside a word.  0: code of row r at bits [2r, 2r+1].  1 ("planes", strip
+  // kernel): bit r = code bit 0, bit 16+r = code bit 1 — the kernel builds whole bit-planes.
+  uint32_t planes;
+  __host__ __device__ inline uint32_t put(uint32_t code, uint32_t r) const {
+    return planes ? (((code & 1u) << r) | ((code >> 1) << (16 + r))) : (code << (2 * r));
+  }
+  __host__ __device__ inline uint32_t get(uint32_t w, uint32_t r) const {
+    return planes ? (((w >> r) & 1u) | (((w >> (16 + r)) & 1u) << 1)) : ((w >> (2 * r)) & 3u);
+  }
   __host__ __device__ inline uint64_t word(uint32_t slot, uint32_t strip, uint32_t xm1) const {
     if (contiguous) return ((uint64_t)slot * nstrips + strip) * ncols + xm1;
     uint32_t group = slot >> 5, lane = slot & 31;
@@ -44,6 +53,7 @@ struct DLayout {
     d.nstrips = (m_max + rows_per_word - 1) / rows_per_word;
     d.ncols = contig ? (n_max + 3) / 4 * 4 : n_max;
     d.contiguous = contig ? 1u : 0u;
+    d.planes = contig ? 1u : 0u;
     return d;
   }
 };

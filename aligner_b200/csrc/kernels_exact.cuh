@@ -123,7 +123,7 @@ __global__ void __launch_bounds__(128) fill_exact_kernel(ExactArgs<T> a) {
       hup = mx;
       hc[(size_t)y * 32] = mx;
       const uint32_t r = (y - 1) % rpw;
-      dword |= (uint32_t)d << (2 * r);
+      dword |= a.dl.put((uint32_t)d, r);
       if (r == rpw - 1 || y == m) {
         a.D[a.dl.word(slot, (y - 1) / rpw, x - 1)] = dword;
         dword = 0;

@@ -60,7 +60,7 @@ int strip_prepare(alnr_batch_impl &B) {
 
 template <int R>
 static int launch_strip(alnr_batch_impl &B, const StripArgs &a, uint32_t duos, bool local, bool stateful) {
-  const size_t smem = (((size_t)a.n + 3) / 4) * kStripBlock * 16;
+  const size_t smem = (size_t)a.n * kStripBlock * 4;
   const unsigned blocks = (duos + kStripBlock - 1) / kStripBlock;
   if (blocks == 0) return ALNR_OK;
 #define ALNR_STRIP_LAUNCH(L, S)                                                                   \

@@ -72,7 +72,7 @@ struct Best {
 struct StripCtx {
   const uint32_t *qA, *qB, *tA, *tB;
   uint32_t *dA, *dB;      // D words of the two slots (contiguous layout), strip 0
-  uint4 *hrow;            // smem: bottom row of the previous strip, [group*kStripBlock], x-1 = 4*group + j
+  uint32_t *hrow;         // smem: bottom row of the previous strip, hrow[(x-1) * kStripBlock]
   uint32_t sA, sB;
   bool dupB;
   Best bestA, bestB;
@@ -80,12 +80,31 @@ struct StripCtx {
   uint32_t corner;
 };
 
+// First row (ascending) whose packed value equals the column maximum, per lane.
+template <int R>
+__device__ __forceinline__ uint32_t first_rows_equal(const uint32_t (&h)[R], uint32_t cm, uint32_t rv) {
+  uint32_t eq = 0;  // bit r (lane A) / bit 16+r (lane B): h[r] != cm
+#pragma unroll
+  for (int r = 0; r < R; ++r) eq += __vminu2(h[r] ^ cm, 0x00010001u) << r;
+  const uint32_t valid = (1u << rv) - 1u;
+  const uint32_t ea = ~eq & valid, eb = ~(eq >> 16) & valid;
+  return (uint32_t)(__ffs(ea) - 1) | ((uint32_t)(__ffs(eb) - 1) << 16);
+}
 // One strip of R rows swept over all columns.  LASTSTRIP: the strip holding row m (it may
 // have fewer than R valid rows); only there are z bits observed and the corner recorded.
+//
+// Per cell (two pairs at once): PRMT score, 2 VIADD.16x2 (top/left minus penalty),
+// VIADDMNMX.S16x2 + VIMNMX.S16x2 (max of three), 2 XOR + 3 VIMNMX.U16x2 against 1 (the flags
+// "max != top", "max != left", "max != 0" as 0/1 per lane), one VIMNMX for the column max,
+// and on the fma pipe 3 shift-accumulates of the flags into row bit-planes plus the next
+// penalty (nz * (del-ext) - del).  Direction codes are formed once per COLUMN from the three
+// planes: P0 = Z | (T & ~L), P1 = Z | (T & L)  (code = P0 + 2*P1: 0 Top, 1 Left, 2 Diagonal,
+// 3 Beginning; enums.rs:18-46), stored as one word per pair: P0 in the low, P1 in the high
+// 16 bits ("plane" D format).
 template <int R, bool LOCAL, bool STATEFUL, bool LASTSTRIP>
 __device__ __forceinline__ void strip_sweep(const StripArgs &a, StripCtx &c, const uint32_t *swt,
                                             uint32_t strip) {
-  const uint32_t n = a.n, m = a.m, tid = threadIdx.x;
+  const uint32_t n = a.n, m = a.m;
   const uint32_t y0 = strip * R;
   const uint32_t rv = LASTSTRIP ? m - y0 : R;  // valid rows
   const uint32_t ndel2 = pack2(-a.del, -a.del), next2 = pack2(-a.ext, -a.ext);
@@ -109,129 +128,121 @@ __device__ __forceinline__ void strip_sweep(const StripArgs &a, StripCtx &c, con
   uint32_t nthr = pack2(-thrA, -thrB);
   uint32_t zacc = 0, zaccB = 0;
   uint32_t qwA = 0, qwB = 0;
-  const size_t dstrip = (size_t)a.dl.ncols;
-  uint32_t *dpA = c.dA + strip * dstrip, *dpB = c.dB + strip * dstrip;
-  const uint32_t ngroups = (n + 3) >> 2;
+  uint32_t *dpA = c.dA + (size_t)strip * a.dl.ncols, *dpB = c.dB + (size_t)strip * a.dl.ncols;
+  uint32_t a0 = 0, a1 = 0, a2 = 0, a3 = 0, b0 = 0, b1 = 0, b2 = 0, b3 = 0;  // 4 pending D words per pair
+  uint32_t *hp = c.hrow;
 
-  for (uint32_t g = 0; g < ngroups; ++g) {
-    if ((g & 3) == 0) { qwA = c.qA[(size_t)(g >> 2) * 32]; qwB = c.qB[(size_t)(g >> 2) * 32]; }
-    const uint4 hu = c.hrow[g * kStripBlock + tid];
-    uint32_t hv[4] = {hu.x, hu.y, hu.z, hu.w};
-    uint32_t wA[4] = {0, 0, 0, 0}, wB[4] = {0, 0, 0, 0};
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const uint32_t xm1 = 4 * g + j, x = xm1 + 1;
-      if (x > n) break;
-      const uint32_t Wa = swt[(qwA >> (2 * j)) & 3], Wb = swt[(qwB >> (2 * j)) & 3];
-      uint32_t hup = hv[j];
-      uint32_t diag = hdiag0;
-      hdiag0 = hup;
-      // penalty of the strip's first row
-      uint32_t np;
-      if (STATEFUL) {
-        if (strip == 0) {
-          int zA = x == 1, zB = x == 1;
-          if (a.z_in && x > 1) {
-            zA = (a.z_in[(size_t)c.sA * a.nzw + ((x - 2) >> 5)] >> ((x - 2) & 31)) & 1;
-            zB = (a.z_in[(size_t)c.sB * a.nzw + ((x - 2) >> 5)] >> ((x - 2) & 31)) & 1;
-          }
-          np = pack2(zA ? -a.del : -a.ext, zB ? -a.del : -a.ext);
-        } else {
-          np = __vminu2(hup, one2) * dme + ndel2;  // cell above: Beginning iff == 0
+#pragma unroll 1
+  for (uint32_t xm1 = 0; xm1 < n; ++xm1, hp += kStripBlock) {
+    const uint32_t x = xm1 + 1;
+    if ((xm1 & 15) == 0) { qwA = c.qA[(size_t)(xm1 >> 4) * 32]; qwB = c.qB[(size_t)(xm1 >> 4) * 32]; }
+    const uint32_t Wa = swt[qwA & 3], Wb = swt[qwB & 3];
+    qwA >>= 2; qwB >>= 2;
+    uint32_t hup = *hp;
+    uint32_t diag = hdiag0;
+    hdiag0 = hup;
+    // penalty of the strip's first row
+    uint32_t np;
+    if (STATEFUL) {
+      if (strip == 0) {
+        int zA = x == 1, zB = x == 1;
+        if (a.z_in && x > 1) {
+          zA = (a.z_in[(size_t)c.sA * a.nzw + ((x - 2) >> 5)] >> ((x - 2) & 31)) & 1;
+          zB = (a.z_in[(size_t)c.sB * a.nzw + ((x - 2) >> 5)] >> ((x - 2) & 31)) & 1;
         }
+        np = pack2(zA ? -a.del : -a.ext, zB ? -a.del : -a.ext);
       } else {
-        np = (!LOCAL && strip == 0 && x == 1) ? ndel2 : next2;  // simple/mod.rs:72: first cell pays del
+        np = __vminu2(hup, one2) * dme + ndel2;  // cell above: Beginning iff == 0
       }
-      uint32_t accLo = 0, accHi = 0, cm = 0x80008000u, nzm = one2;
+    } else {
+      np = (!LOCAL && strip == 0 && x == 1) ? ndel2 : next2;  // simple/mod.rs:72: first cell pays del
+    }
+    uint32_t accT = 0, accL = 0, accN = 0, cm = 0x80008000u;
 #pragma unroll
-      for (int r = 0; r < R; ++r) {
-        const uint32_t s = prmt_sx(Wa, Wb, sel[r]);
-        const uint32_t top = __vadd2(hup, np);
-        const uint32_t left = __vadd2(h[r], np);
-        const uint32_t mx = __vmaxs2(__viaddmax_s16x2(diag, s, top), left);
-        const uint32_t neT = __vminu2(mx ^ top, one2);
-        const uint32_t neL = __vminu2(mx ^ left, one2);
-        uint32_t code;
-        if (LOCAL) {
-          const uint32_t nz = __vminu2(mx, one2);
-          // 3 if !nz; else 0 if !neT; else 1 if !neL; else 2   (enums.rs:37-45)
-          const uint32_t b0 = (~nz | (neT & ~neL)) & one2;
-          const uint32_t b1 = (~nz | (neT & neL)) & one2;
-          code = b0 + 2 * b1;
-          if (STATEFUL) np = nz * dme + ndel2;  // simple/mod.rs:201-205
-          if (STATEFUL && LASTSTRIP && (uint32_t)r + 1 == rv) nzm = nz;  // row m
-        } else {
-          code = neT + (neT & neL);  // enums.rs:21-27
-          np = next2;
-        }
-        if (r < 8) accLo += code << (2 * r); else accHi += code << (2 * (r - 8));
-        diag = h[r];
-        h[r] = mx;
-        hup = mx;
-        if (LOCAL) { if (!LASTSTRIP || (uint32_t)r < rv) cm = __vmaxs2(cm, mx); }
-      }
-      hv[j] = h[R - 1];
-      wA[j] = (accLo & 0xffffu) | (accHi << 16);
-      wB[j] = (accLo >> 16) | (accHi & 0xffff0000u);
-
+    for (int r = 0; r < R; ++r) {
+      const uint32_t s = prmt_sx(Wa, Wb, sel[r]);
+      const uint32_t top = __vadd2(hup, np);
+      const uint32_t left = __vadd2(h[r], np);
+      const uint32_t mx = __vmaxs2(__viaddmax_s16x2(diag, s, top), left);
+      accT += __vminu2(mx ^ top, one2) << r;
+      accL += __vminu2(mx ^ left, one2) << r;
       if (LOCAL) {
-        // any lane with column max >= threshold?  (threshold = best, or best+1 if the best
-        // sits in an earlier strip: ties there win by smaller y)
-        const uint32_t dlt = __vadd2(cm, nthr);
-        if ((dlt & 0x80008000u) != 0x80008000u) {
-          const int cA = lane_lo(cm), cB = lane_hi(cm);
-          if (cA >= thrA) {
-            uint32_t r0 = 0;
-#pragma unroll
-            for (int r = R - 1; r >= 0; --r) if (lane_lo(h[r]) == cA && (uint32_t)r < rv) r0 = r;
-            const uint32_t y = y0 + r0 + 1;
-            if (cA > c.bestA.v || y < c.bestA.y) { c.bestA = Best{cA, y, x, (int)strip}; thrA = cA; }
-          }
-          if (cB >= thrB) {
-            uint32_t r0 = 0;
-#pragma unroll
-            for (int r = R - 1; r >= 0; --r) if (lane_hi(h[r]) == cB && (uint32_t)r < rv) r0 = r;
-            const uint32_t y = y0 + r0 + 1;
-            if (cB > c.bestB.v || y < c.bestB.y) { c.bestB = Best{cB, y, x, (int)strip}; thrB = cB; }
-          }
-          nthr = pack2(-thrA, -thrB);
-        }
+        const uint32_t nz = __vminu2(mx, one2);
+        accN += nz << r;
+        if (STATEFUL) np = nz * dme + ndel2;  // simple/mod.rs:201-205
       }
-      if (STATEFUL && LASTSTRIP) {
-        // observe z[x-1] = (H[m][x] == 0); it sets the penalty of cell (1, x+1)
-        const uint32_t z = nzm ^ one2;
-        zacc |= (z & 1u) << (xm1 & 31);
-        zaccB |= (z >> 16) << (xm1 & 31);
-        if ((xm1 & 31) == 31 || x == n) {
-          const uint32_t w = xm1 >> 5;
-          uint32_t asA = 0, asB = 0;
-          if (a.z_in) { asA = a.z_in[(size_t)c.sA * a.nzw + w]; asB = a.z_in[(size_t)c.sB * a.nzw + w]; }
-          // bits at column index >= n-1 never feed a penalty (there is no column n+1)
-          const uint32_t nb = (n - 1) - (w << 5);
-          const uint32_t valid = (n - 1 <= (w << 5)) ? 0u : (nb >= 32 ? 0xffffffffu : ((1u << nb) - 1u));
-          if ((zacc ^ asA) & valid) c.mismatch |= 1u;
-          if ((zaccB ^ asB) & valid) c.mismatch |= 0x10000u;
-          a.z_out[(size_t)c.sA * a.nzw + w] = zacc;
-          if (!c.dupB) a.z_out[(size_t)c.sB * a.nzw + w] = zaccB;
-          zacc = zaccB = 0;
+      if (!STATEFUL) np = next2;
+      diag = h[r];
+      h[r] = mx;
+      hup = mx;
+      if (LOCAL) { if (!LASTSTRIP || (uint32_t)r < rv) cm = __vmaxs2(cm, mx); }
+    }
+    if (!LASTSTRIP) *hp = h[R - 1];
+    // direction planes of this column (both pairs at once), then one word per pair
+    uint32_t P0, P1;
+    if (LOCAL) { P0 = ~accN | (accT & ~accL); P1 = ~accN | (accT & accL); }
+    else { P0 = accT & ~accL; P1 = accT & accL; }
+    a0 = a1; a1 = a2; a2 = a3; a3 = __byte_perm(P0, P1, 0x5410);
+    b0 = b1; b1 = b2; b2 = b3; b3 = __byte_perm(P0, P1, 0x7632);
+    if ((xm1 & 3) == 3) {
+      *reinterpret_cast<uint4 *>(dpA + (xm1 - 3)) = make_uint4(a0, a1, a2, a3);
+      if (!c.dupB) *reinterpret_cast<uint4 *>(dpB + (xm1 - 3)) = make_uint4(b0, b1, b2, b3);
+    }
+
+    if (LOCAL) {
+      // any lane with column max >= threshold?  (threshold = best, or best+1 if the best
+      // sits in an earlier strip: ties there win by smaller y)
+      const uint32_t dlt = __vadd2(cm, nthr);
+      if ((dlt & 0x80008000u) != 0x80008000u) {
+        const int cA = lane_lo(cm), cB = lane_hi(cm);
+        const uint32_t r0 = first_rows_equal<R>(h, cm, rv);
+        if (cA >= thrA) {
+          const uint32_t y = y0 + (r0 & 0xffffu) + 1;
+          if (cA > c.bestA.v || y < c.bestA.y) { c.bestA = Best{cA, y, x, (int)strip}; thrA = cA; }
         }
-      }
-      if (LASTSTRIP && x == n) {
-        c.corner = h[R - 1];
-#pragma unroll
-        for (int r = 0; r < R - 1; ++r) if ((uint32_t)r + 1 == rv) c.corner = h[r];
+        if (cB >= thrB) {
+          const uint32_t y = y0 + (r0 >> 16) + 1;
+          if (cB > c.bestB.v || y < c.bestB.y) { c.bestB = Best{cB, y, x, (int)strip}; thrB = cB; }
+        }
+        nthr = pack2(-thrA, -thrB);
       }
     }
-    qwA >>= 8; qwB >>= 8;
-    if (!LASTSTRIP) c.hrow[g * kStripBlock + tid] = make_uint4(hv[0], hv[1], hv[2], hv[3]);
-    *reinterpret_cast<uint4 *>(dpA + 4 * g) = make_uint4(wA[0], wA[1], wA[2], wA[3]);
-    if (!c.dupB) *reinterpret_cast<uint4 *>(dpB + 4 * g) = make_uint4(wB[0], wB[1], wB[2], wB[3]);
+    if (STATEFUL && LASTSTRIP) {
+      // observe z[x-1] = (H[m][x] == 0); it sets the penalty of cell (1, x+1)
+      const uint32_t z = ~(accN >> (rv - 1));
+      zacc |= (z & 1u) << (xm1 & 31);
+      zaccB |= ((z >> 16) & 1u) << (xm1 & 31);
+      if ((xm1 & 31) == 31 || x == n) {
+        const uint32_t w = xm1 >> 5;
+        uint32_t asA = 0, asB = 0;
+        if (a.z_in) { asA = a.z_in[(size_t)c.sA * a.nzw + w]; asB = a.z_in[(size_t)c.sB * a.nzw + w]; }
+        // bits at column index >= n-1 never feed a penalty (there is no column n+1)
+        const uint32_t nb = (n - 1) - (w << 5);
+        const uint32_t valid = (n - 1 <= (w << 5)) ? 0u : (nb >= 32 ? 0xffffffffu : ((1u << nb) - 1u));
+        if ((zacc ^ asA) & valid) c.mismatch |= 1u;
+        if ((zaccB ^ asB) & valid) c.mismatch |= 0x10000u;
+        a.z_out[(size_t)c.sA * a.nzw + w] = zacc;
+        if (!c.dupB) a.z_out[(size_t)c.sB * a.nzw + w] = zaccB;
+        zacc = zaccB = 0;
+      }
+    }
+  }
+  // flush a partial group of D words (n not a multiple of 4)
+  if (n & 3) {
+    for (uint32_t k = n & 3; k < 4; ++k) { a0 = a1; a1 = a2; a2 = a3; a3 = 0; b0 = b1; b1 = b2; b2 = b3; b3 = 0; }
+    *reinterpret_cast<uint4 *>(dpA + (n & ~3u)) = make_uint4(a0, a1, a2, a3);
+    if (!c.dupB) *reinterpret_cast<uint4 *>(dpB + (n & ~3u)) = make_uint4(b0, b1, b2, b3);
+  }
+  if (LASTSTRIP) {
+    c.corner = h[R - 1];
+#pragma unroll
+    for (int r = 0; r < R - 1; ++r) if ((uint32_t)r + 1 == rv) c.corner = h[r];
   }
 }
 
 template <int R, bool LOCAL, bool STATEFUL>
 __global__ void __launch_bounds__(kStripBlock) fill_strip_kernel(StripArgs a) {
-  extern __shared__ uint4 smem4[];
+  extern __shared__ uint32_t smem_h[];
   __shared__ uint32_t swt[4];
   const uint32_t tid = threadIdx.x;
   if (tid < 4) swt[tid] = a.wtab[tid];
@@ -261,23 +272,17 @@ __global__ void __launch_bounds__(kStripBlock) fill_strip_kernel(StripArgs a) {
   const uint32_t nstrips = (m + R - 1) / R;
   c.dA = a.D + a.dl.word(c.sA, 0, 0);
   c.dB = a.D + a.dl.word(c.sB, 0, 0);
-  c.hrow = smem4;
+  c.hrow = smem_h + tid;
   c.bestA = Best{0, 0, 0, -1};
   c.bestB = Best{0, 0, 0, -1};
   c.mismatch = 0;
   c.corner = 0;
 
   // ---- row 0 (simple/mod.rs:59-62,69 global; zeros local): index x-1 ---------------------
-  for (uint32_t g = 0; g < (n + 3) / 4; ++g) {
-    uint32_t v[4];
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const uint32_t x = 4 * g + j + 1;
-      int hv = 0;
-      if (!LOCAL) hv = (x == n) ? -(int)(n + 1) * a.del : -(int)x * a.del;
-      v[j] = pack2(hv, hv);
-    }
-    c.hrow[g * kStripBlock + tid] = make_uint4(v[0], v[1], v[2], v[3]);
+  for (uint32_t x = 1; x <= n; ++x) {
+    int hv = 0;
+    if (!LOCAL) hv = (x == n) ? -(int)(n + 1) * a.del : -(int)x * a.del;
+    c.hrow[(x - 1) * kStripBlock] = pack2(hv, hv);
   }
 
   for (uint32_t strip = 0; strip + 1 < nstrips; ++strip)

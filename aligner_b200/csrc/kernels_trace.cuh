@@ -94,7 +94,7 @@ __global__ void __launch_bounds__(128) traceback_kernel(TraceArgs a) {
       else d = (cy == 0) ? DIR_LEFT : DIR_TOP;  // simple/mod.rs:59-67
     } else {
       const uint32_t w = a.D[a.dl.word(slot, (cy - 1) / rpw, cx - 1)];
-      d = (w >> (2 * ((cy - 1) % rpw))) & 3;
+      d = a.dl.get(w, (cy - 1) % rpw);
     }
     if (d == DIR_BEGINNING) break;
     if (d == DIR_TOP) { emit(kBlank, t[cy - 1]); --cy; }
@@ -147,7 +147,7 @@ __global__ void __launch_bounds__(kTraceBlock) traceback_coop_kernel(TraceArgs a
           else d = (cy == 0) ? DIR_LEFT : DIR_TOP;
         } else {
           const uint32_t w = a.D[a.dl.word(slot, (cy - 1) / rpw, cx - 1)];
-          d = (w >> (2 * ((cy - 1) % rpw))) & 3;
+          d = a.dl.get(w, (cy - 1) % rpw);
         }
         if (d == DIR_BEGINNING) break;
         acc |= (uint32_t)d << (2 * (K & 15));
