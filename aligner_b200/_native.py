@@ -70,6 +70,7 @@ SIGNATURES = {
     "alnr_measure_int_peak": (C.c_int, [C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "alnr_host_alloc": (C.c_void_p, [C.c_uint64]),
     "alnr_host_free": (None, [C.c_void_p]),
+    "alnr_release_cached_memory": (None, []),
 }
 
 _lib = None

@@ -105,16 +105,34 @@ uint64_t alnr_batch_rerun_count(alnr_batch_handle *h) { return h ? h->impl.rerun
 void alnr_batch_destroy(alnr_batch_handle *h) {
   if (!h) return;
   cudaSetDevice(h->impl.device);
+  if (h->impl.stream) cudaStreamSynchronize(h->impl.stream);  // buffers go back to the pool
   delete h;
 }
 
 int alnr_align_batch(const alnr_params *p, const alnr_batch *b, alnr_batch_out *out) {
-  alnr_batch_handle *h = nullptr;
-  int st = alnr_batch_create(p, b, &h);
-  if (st) return st;
-  st = h->impl.run();
-  if (!st) st = h->impl.download(out);
-  alnr_batch_destroy(h);
+  if (!out) return ALNR_INVALID_ARGUMENT;
+  alnr_batch_handle *hh = new (std::nothrow) alnr_batch_handle();
+  if (!hh) return ALNR_OUT_OF_MEMORY;
+  alnr_batch_impl &B = hh->impl;
+  // uniform batches stream chunk by chunk (copies overlap compute); init() finds out which
+  B.resident = false;
+  B.max_chunk = 1u << 20;
+  int st = B.init(p, b, false);
+  if (!st) {
+    if (B.uniform) {
+      st = B.stream_all(b, out);
+    } else {
+      cudaError_t e = cudaSuccess;
+      if (B.count) {
+        e = cudaMemcpyAsync(B.d_q.p, b->q, B.q_total, cudaMemcpyHostToDevice, B.stream);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(B.d_t.p, b->t, B.t_total, cudaMemcpyHostToDevice, B.stream);
+      }
+      if (e != cudaSuccess) st = alnr::cuda_fail(e, "H2D", __FILE__, __LINE__);
+      if (!st) st = B.run();
+      if (!st) st = B.download(out);
+    }
+  }
+  alnr_batch_destroy(hh);
   return st;
 }
 

@@ -123,8 +123,10 @@ int alnr_batch_impl::plan_chunks(const uint64_t *q_off, const uint64_t *t_off) {
     uint64_t groups = std::max<uint64_t>(budget / per_group, 1);
     uint64_t c = std::min<uint64_t>(groups * 32, count - s);
     if (c < count - s) c = std::max<uint64_t>(c / 64 * 64, 32);  // keep duo-kernel warps whole
-    c = std::min<uint64_t>(c, 1u << 22);
-    chunks.push_back(Chunk{(uint32_t)s, (uint32_t)c, m, n});
+    if (c > max_chunk) c = max_chunk;
+    Chunk ck{(uint32_t)s, (uint32_t)c, m, n, 0, 0, 0, 0};
+    if (uniform) { ck.q0 = q_off[s]; ck.q1 = q_off[s + c]; ck.t0 = t_off[s]; ck.t1 = t_off[s + c]; }
+    chunks.push_back(ck);
     s += c;
   }
   return ALNR_OK;
@@ -173,8 +175,10 @@ int alnr_batch_impl::init(const alnr_params *p, const alnr_batch *b, bool want_m
   ALNR_CUDA(d_qoff.alloc(count + 1));
   ALNR_CUDA(d_toff.alloc(count + 1));
   if (count) {
-    ALNR_CUDA(cudaMemcpyAsync(d_q.p, b->q, q_total, cudaMemcpyHostToDevice, stream));
-    ALNR_CUDA(cudaMemcpyAsync(d_t.p, b->t, t_total, cudaMemcpyHostToDevice, stream));
+    if (resident) {
+      ALNR_CUDA(cudaMemcpyAsync(d_q.p, b->q, q_total, cudaMemcpyHostToDevice, stream));
+      ALNR_CUDA(cudaMemcpyAsync(d_t.p, b->t, t_total, cudaMemcpyHostToDevice, stream));
+    }
     ALNR_CUDA(cudaMemcpyAsync(d_qoff.p, b->q_off, (count + 1) * 8, cudaMemcpyHostToDevice, stream));
     ALNR_CUDA(cudaMemcpyAsync(d_toff.p, b->t_off, (count + 1) * 8, cudaMemcpyHostToDevice, stream));
   }
@@ -237,39 +241,118 @@ static int launch_exact(alnr_batch_impl &B, const Chunk &c, const ChunkView &cv,
 int alnr_batch_impl::run() {
   ALNR_CUDA(cudaSetDevice(device));
   if (count == 0) return ALNR_OK;
-  FillOut fo{d_f.p, d_corner.p, d_start.p, d_status.p};
-  TraceOut to{d_coords.p, d_alnoff.p, d_alnlen.p, d_qaln.p, d_taln.p, nullptr};
-  // symbol validation: one coalesced sweep; the per-pair scan only runs if it found something
   ALNR_CUDA(cudaMemsetAsync(d_flags.p, 0, 4 * sizeof(int), stream));
-  any_symbol_out_of_range_kernel<<<148 * 8, 256, 0, stream>>>(d_q.p, q_total, V, d_flags.p);
-  ALNR_LAUNCHED();
-  any_symbol_out_of_range_kernel<<<148 * 8, 256, 0, stream>>>(d_t.p, t_total, V, d_flags.p);
-  ALNR_LAUNCHED();
-  rerun_total = 0;
-  for (const Chunk &c : chunks) {
-    ChunkView cv{d_q.p, d_t.p, d_qoff.p, d_toff.p, uniform ? nullptr : d_order.p, c.first, c.count};
-    const DLayout dl = DLayout::make(d_rows_per_word(*this, c.m_max), c.m_max, c.n_max, numeric == ALNR_NUM_I16X2);
-    validate_kernel<<<(c.count + 127) / 128, 128, 0, stream>>>(cv, V, d_status.p, d_flags.p);
+  if (!uniform) {  // sorted order: chunks are not contiguous symbol ranges, sweep everything first
+    any_symbol_out_of_range_kernel<<<148 * 8, 256, 0, stream>>>(d_q.p, q_total, V, d_flags.p);
     ALNR_LAUNCHED();
-    int st = fill_mark(false);
-    if (st) return st;
-    if (numeric == ALNR_NUM_F64) st = launch_exact<double>(*this, c, cv, dl, fo, d_hcol_d.p, d_matd.p);
-    else if (numeric == ALNR_NUM_I32) st = launch_exact<int>(*this, c, cv, dl, fo, d_hcol_i.p, d_mati.p);
-    else st = strip_run_chunk(*this, c, cv, dl, fo);
-    if (st) return st;
-    st = fill_mark(true);
-    if (st) return st;
-    TraceArgs ta{cv, mode, V, d_D.p, dl, fo, to};
-    const uint32_t nmw = (c.n_max + c.m_max + 1 + 15) / 16;  // 2-bit move words per pair
-    if ((size_t)nmw * kTraceBlock * 4 <= 44 * 1024 && to.freq == nullptr) {
-      traceback_coop_kernel<<<(c.count + kTraceBlock - 1) / kTraceBlock, kTraceBlock,
-                              (size_t)nmw * kTraceBlock * 4, stream>>>(ta, nmw);
-    } else {
-      traceback_kernel<<<(c.count + 127) / 128, 128, 0, stream>>>(ta);
-    }
+    any_symbol_out_of_range_kernel<<<148 * 8, 256, 0, stream>>>(d_t.p, t_total, V, d_flags.p);
     ALNR_LAUNCHED();
   }
+  rerun_total = 0;
+  for (size_t ci = 0; ci < chunks.size(); ++ci) {
+    int st = run_chunk(ci);
+    if (st) return st;
+  }
   return ALNR_OK;
+}
+
+int alnr_batch_impl::run_chunk(size_t ci) {
+  const Chunk &c = chunks[ci];
+  FillOut fo{d_f.p, d_corner.p, d_start.p, d_status.p};
+  TraceOut to{d_coords.p, d_alnoff.p, d_alnlen.p, d_qaln.p, d_taln.p, nullptr};
+  ChunkView cv{d_q.p, d_t.p, d_qoff.p, d_toff.p, uniform ? nullptr : d_order.p, c.first, c.count};
+  const DLayout dl = DLayout::make(d_rows_per_word(*this, c.m_max), c.m_max, c.n_max, numeric == ALNR_NUM_I16X2);
+  // symbol validation: one coalesced sweep; the per-pair scan only runs if it found something
+  if (uniform) {
+    const unsigned gq = (unsigned)std::min<uint64_t>(148 * 8, (c.q1 - c.q0) / 4096 + 1);
+    const unsigned gt = (unsigned)std::min<uint64_t>(148 * 8, (c.t1 - c.t0) / 4096 + 1);
+    any_symbol_out_of_range_kernel<<<gq, 256, 0, stream>>>(d_q.p + c.q0, c.q1 - c.q0, V, d_flags.p);
+    ALNR_LAUNCHED();
+    any_symbol_out_of_range_kernel<<<gt, 256, 0, stream>>>(d_t.p + c.t0, c.t1 - c.t0, V, d_flags.p);
+    ALNR_LAUNCHED();
+  }
+  validate_kernel<<<(c.count + 127) / 128, 128, 0, stream>>>(cv, V, d_status.p, d_flags.p);
+  ALNR_LAUNCHED();
+  int st = fill_mark(false);
+  if (st) return st;
+  if (numeric == ALNR_NUM_F64) st = launch_exact<double>(*this, c, cv, dl, fo, d_hcol_d.p, d_matd.p);
+  else if (numeric == ALNR_NUM_I32) st = launch_exact<int>(*this, c, cv, dl, fo, d_hcol_i.p, d_mati.p);
+  else st = strip_run_chunk(*this, c, cv, dl, fo);
+  if (st) return st;
+  st = fill_mark(true);
+  if (st) return st;
+  TraceArgs ta{cv, mode, V, d_D.p, dl, fo, to};
+  const uint32_t nmw = (c.n_max + c.m_max + 1 + 15) / 16;  // 2-bit move words per pair
+  if ((size_t)nmw * kTraceBlock * 4 <= 44 * 1024 && to.freq == nullptr) {
+    traceback_coop_kernel<<<(c.count + kTraceBlock - 1) / kTraceBlock, kTraceBlock,
+                            (size_t)nmw * kTraceBlock * 4, stream>>>(ta, nmw);
+  } else {
+    traceback_kernel<<<(c.count + 127) / 128, 128, 0, stream>>>(ta);
+  }
+  ALNR_LAUNCHED();
+  return ALNR_OK;
+}
+
+// Pipelined host->host call: chunk k's inputs are copied on `s_in` while chunk k-1 computes
+// on `stream` and chunk k-2's results drain on `s_out`.  Needs identity order (uniform
+// lengths) so that a chunk is a contiguous range of every input and output array.
+int alnr_batch_impl::stream_all(const alnr_batch *b, alnr_batch_out *out) {
+  ALNR_CUDA(cudaSetDevice(device));
+  if (count == 0) return ALNR_OK;
+  cudaStream_t s_in = nullptr, s_out = nullptr;
+  ALNR_CUDA(cudaStreamCreateWithFlags(&s_in, cudaStreamNonBlocking));
+  ALNR_CUDA(cudaStreamCreateWithFlags(&s_out, cudaStreamNonBlocking));
+  std::vector<cudaEvent_t> ev_in(chunks.size(), nullptr), ev_done(chunks.size(), nullptr);
+  int st = ALNR_OK;
+  auto fail = [&](cudaError_t e, const char *what) { st = cuda_fail(e, what, __FILE__, __LINE__); };
+  for (size_t i = 0; i < chunks.size() && !st; ++i) {
+    cudaError_t e = cudaEventCreateWithFlags(&ev_in[i], cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ev_done[i], cudaEventDisableTiming);
+    if (e != cudaSuccess) fail(e, "cudaEventCreate");
+  }
+  if (!st) {
+    cudaError_t e = cudaMemsetAsync(d_flags.p, 0, 4 * sizeof(int), stream);
+    if (e != cudaSuccess) fail(e, "memset flags");
+  }
+  rerun_total = 0;
+  for (size_t ci = 0; ci < chunks.size() && !st; ++ci) {
+    const Chunk &c = chunks[ci];
+    cudaError_t e = cudaMemcpyAsync(d_q.p + c.q0, b->q + c.q0, c.q1 - c.q0, cudaMemcpyHostToDevice, s_in);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_t.p + c.t0, b->t + c.t0, c.t1 - c.t0, cudaMemcpyHostToDevice, s_in);
+    if (e == cudaSuccess) e = cudaEventRecord(ev_in[ci], s_in);
+    if (e == cudaSuccess) e = cudaStreamWaitEvent(stream, ev_in[ci], 0);
+    if (e != cudaSuccess) { fail(e, "H2D chunk"); break; }
+    st = run_chunk(ci);
+    if (st) break;
+    e = cudaEventRecord(ev_done[ci], stream);
+    if (e == cudaSuccess) e = cudaStreamWaitEvent(s_out, ev_done[ci], 0);
+    auto cp = [&](void *dst, const void *src, size_t off, size_t bytes) {
+      if (dst && e == cudaSuccess)
+        e = cudaMemcpyAsync((char *)dst + off, (const char *)src + off, bytes, cudaMemcpyDeviceToHost, s_out);
+    };
+    const size_t f0 = c.first, fc = c.count;
+    cp(out->f, d_f.p, f0 * 8, fc * 8);
+    cp(out->corner, d_corner.p, f0 * 8, fc * 8);
+    cp(out->coords, d_coords.p, f0 * 32, fc * 32);
+    cp(out->aln_off, d_alnoff.p, f0 * 8, fc * 8);
+    cp(out->aln_len, d_alnlen.p, f0 * 4, fc * 4);
+    cp(out->status, d_status.p, f0 * 4, fc * 4);
+    const size_t a0 = c.q0 + c.t0 + f0, a1 = c.q1 + c.t1 + f0 + fc;  // alignment slots of the chunk
+    cp(out->q_aln, d_qaln.p, a0, a1 - a0);
+    cp(out->t_aln, d_taln.p, a0, a1 - a0);
+    if (e != cudaSuccess) fail(e, "D2H chunk");
+  }
+  cudaError_t e1 = cudaStreamSynchronize(s_in), e2 = cudaStreamSynchronize(stream), e3 = cudaStreamSynchronize(s_out);
+  if (!st && e1 != cudaSuccess) fail(e1, "sync s_in");
+  if (!st && e2 != cudaSuccess) fail(e2, "sync compute");
+  if (!st && e3 != cudaSuccess) fail(e3, "sync s_out");
+  for (size_t i = 0; i < chunks.size(); ++i) {
+    if (ev_in[i]) cudaEventDestroy(ev_in[i]);
+    if (ev_done[i]) cudaEventDestroy(ev_done[i]);
+  }
+  cudaStreamDestroy(s_in);
+  cudaStreamDestroy(s_out);
+  return st;
 }
 
 int alnr_batch_impl::download(alnr_batch_out *out) {

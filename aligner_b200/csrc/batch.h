@@ -11,6 +11,7 @@ namespace alnr {
 struct Chunk {
   uint32_t first, count;      // slots
   uint32_t m_max, n_max;      // chunk-wide maxima
+  uint64_t q0, q1, t0, t1;    // symbol ranges of the chunk (identity order only)
 };
 
 struct alnr_batch_impl {
@@ -48,6 +49,11 @@ struct alnr_batch_impl {
   ~alnr_batch_impl();
   int init(const alnr_params *p, const alnr_batch *b, bool want_mats);
   int run();                     // enqueue all kernels on `stream`
+  int run_chunk(size_t ci);      // validation + fill + traceback of one chunk on `stream`
+  // host buffers in -> host buffers out, chunks pipelined over three streams
+  int stream_all(const alnr_batch *b, alnr_batch_out *out);
+  bool resident = true;          // inputs were uploaded by init()
+  uint32_t max_chunk = 1u << 22;
   int download(alnr_batch_out *out);
   int classify();
   int plan_chunks(const uint64_t *q_off, const uint64_t *t_off);

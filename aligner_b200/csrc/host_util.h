@@ -36,25 +36,35 @@ inline int cuda_fail(cudaError_t e, const char *what, const char *file, int line
     if (_e != cudaSuccess) return ::alnr::cuda_fail(_e, "kernel launch", __FILE__, __LINE__); \
   } while (0)
 
-// RAII device buffer.
+// Caching device allocator: cudaMalloc/cudaFree cost milliseconds per GB and synchronise the
+// device, so buffers released by one call are kept per device and reused by the next
+// (alnr_release_cached_memory() returns them to the driver).  Thread-safe.
+cudaError_t pool_alloc(void **p, size_t bytes, size_t *granted);
+void pool_free(void *p, size_t granted);
+void pool_release_all();
+
+// RAII device buffer backed by the pool.
 template <typename T>
 struct DevBuf {
   T *p = nullptr;
   size_t n = 0;
+  size_t granted = 0;
   DevBuf() = default;
   DevBuf(const DevBuf &) = delete;
   DevBuf &operator=(const DevBuf &) = delete;
   ~DevBuf() { release(); }
   void release() {
-    if (p) cudaFree(p);
+    if (p) pool_free(p, granted);
     p = nullptr;
     n = 0;
+    granted = 0;
   }
   cudaError_t alloc(size_t count) {
     release();
     if (count == 0) count = 1;
-    cudaError_t e = cudaMalloc((void **)&p, count * sizeof(T));
-    if (e == cudaSuccess) n = count; else p = nullptr;
+    void *q = nullptr;
+    cudaError_t e = pool_alloc(&q, count * sizeof(T), &granted);
+    if (e == cudaSuccess) { p = (T *)q; n = count; } else { p = nullptr; granted = 0; }
     return e;
   }
 };

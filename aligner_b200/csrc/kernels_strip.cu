@@ -39,16 +39,6 @@ int strip_prepare(alnr_batch_impl &B) {
   const uint32_t nwq = (B.n_max + 15) / 16, nwt = (B.m_max + 15) / 16;
   const uint64_t groups = (B.count + 31) / 32;
   ALNR_CUDA(B.d_pack.alloc(groups * 32 * ((uint64_t)nwq + nwt)));
-  uint32_t *qpk = B.d_pack.p, *tpk = B.d_pack.p + groups * 32 * nwq;
-  const uint32_t *order = B.uniform ? nullptr : B.d_order.p;
-  uint64_t threads = groups * 32 * nwq;
-  pack2bit_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, B.stream>>>(B.d_q.p, B.d_qoff.p, order,
-                                                                          (uint32_t)B.count, nwq, qpk);
-  ALNR_LAUNCHED();
-  threads = groups * 32 * nwt;
-  pack2bit_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, B.stream>>>(B.d_t.p, B.d_toff.p, order,
-                                                                          (uint32_t)B.count, nwt, tpk);
-  ALNR_LAUNCHED();
   // speculation plumbing: two z buffers, two lists, counters (sized for the largest chunk)
   uint32_t cmax = 0;
   for (const Chunk &c : B.chunks) cmax = std::max(cmax, c.count);
@@ -93,6 +83,19 @@ int strip_run_chunk(alnr_batch_impl &B, const Chunk &c, const ChunkView &cv, con
   uint32_t *lists[2] = {B.d_rerun.p + base, B.d_rerun.p + base + cmax};
   uint32_t *zbuf[2] = {B.d_rerun.p + base + 2ull * cmax, B.d_rerun.p + base + 2ull * cmax + (uint64_t)cmax * nzw};
 
+  // pack this chunk's sequences (2 bits per symbol, coalesced layout)
+  {
+    uint32_t *qpk = B.d_pack.p, *tpk = B.d_pack.p + groups * 32 * nwq;
+    const uint64_t lg = (c.count + 31) / 32;
+    uint64_t threads = lg * 32 * nwq;
+    pack2bit_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, B.stream>>>(B.d_q.p, B.d_qoff.p, cv.order, c.first,
+                                                                            c.count, nwq, qpk);
+    ALNR_LAUNCHED();
+    threads = lg * 32 * nwt;
+    pack2bit_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, B.stream>>>(B.d_t.p, B.d_toff.p, cv.order, c.first,
+                                                                            c.count, nwt, tpk);
+    ALNR_LAUNCHED();
+  }
   const bool local = B.mode == ALNR_LOCAL;
   const bool stateful = local && B.del != B.ext;
   StripArgs a;

@@ -310,16 +310,18 @@ __global__ void __launch_bounds__(kStripBlock) fill_strip_kernel(StripArgs a) {
   if (!c.dupB) finish(bB, c.sB, c.bestB, lane_hi(c.corner), (c.mismatch >> 16) != 0);
 }
 
-// 2-bit packing of one sequence set into the coalesced [(group*nw + w)*32 + lane] layout.
+// 2-bit packing of the slots [first, first+count) of one sequence set into the coalesced
+// [(group*nw + w)*32 + lane] layout (group = batch slot / 32; first is a multiple of 32).
 __global__ void pack2bit_kernel(const uint8_t *seq, const uint64_t *off, const uint32_t *order,
-                                uint32_t count, uint32_t nw, uint32_t *out) {
+                                uint32_t first, uint32_t count, uint32_t nw, uint32_t *out) {
   const uint64_t gid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const uint32_t lane = gid & 31;
   const uint64_t rest = gid >> 5;
   const uint32_t w = (uint32_t)(rest % nw);
-  const uint64_t group = rest / nw;
-  const uint64_t slot = group * 32 + lane;
-  if (slot >= count) return;
+  const uint64_t lgroup = rest / nw;
+  const uint64_t local = lgroup * 32 + lane;
+  if (local >= count) return;
+  const uint64_t slot = first + local;
   const uint32_t pair = order ? order[slot] : (uint32_t)slot;
   const uint64_t b = off[pair], e = off[pair + 1];
   uint32_t word = 0;
@@ -327,7 +329,7 @@ __global__ void pack2bit_kernel(const uint8_t *seq, const uint64_t *off, const u
     const uint64_t i = b + (uint64_t)w * 16 + k;
     if (i < e) word |= (uint32_t)(seq[i] & 3u) << (2 * k);
   }
-  out[(group * nw + w) * 32 + lane] = word;
+  out[((slot >> 5) * nw + w) * 32 + lane] = word;
 }
 
 }  // namespace alnr

@@ -27,8 +27,12 @@ __global__ void any_symbol_out_of_range_kernel(const uint8_t *buf, uint64_t len,
   const uint64_t tid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
   bool bad = false;
-  const uint64_t nvec = len / 16;
-  const uint4 *v = reinterpret_cast<const uint4 *>(buf);
+  // unaligned head (chunk ranges start anywhere), 16-byte body, tail
+  uint64_t head = (16 - ((uintptr_t)buf & 15)) & 15;
+  if (head > len) head = len;
+  for (uint64_t i = tid; i < head; i += stride) bad |= buf[i] >= V;
+  const uint64_t nvec = (len - head) / 16;
+  const uint4 *v = reinterpret_cast<const uint4 *>(buf + head);
   for (uint64_t i = tid; i < nvec; i += stride) {
     uint4 w = v[i];
     uint32_t ws[4] = {w.x, w.y, w.z, w.w};
@@ -37,7 +41,7 @@ __global__ void any_symbol_out_of_range_kernel(const uint8_t *buf, uint64_t len,
 #pragma unroll
       for (int b = 0; b < 4; ++b) bad |= ((ws[k] >> (8 * b)) & 0xff) >= (uint32_t)V;
   }
-  for (uint64_t i = nvec * 16 + tid; i < len; i += stride) bad |= buf[i] >= V;
+  for (uint64_t i = head + nvec * 16 + tid; i < len; i += stride) bad |= buf[i] >= V;
   if (bad) *flag = 1;
 }
 

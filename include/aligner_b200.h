@@ -159,6 +159,9 @@ int alnr_measure_int_peak(int device, double *alu_ops_per_s, double *mixed_ops_p
 /* pinned host memory helpers for callers without a CUDA binding */
 void *alnr_host_alloc(uint64_t bytes);
 void alnr_host_free(void *p);
+/* Device buffers are cached between calls (cudaMalloc/cudaFree are slow and synchronising);
+ * this returns every cached buffer to the driver. */
+void alnr_release_cached_memory(void);
 
 #ifdef __cplusplus
 }
