@@ -2,6 +2,7 @@
 // and the per-chunk launch sequence (speculative pass, re-run passes, exact leftovers).
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 
 #include "kernels_exact.cuh"
 #include "kernels_strip.cuh"
@@ -50,7 +51,7 @@ int strip_prepare(alnr_batch_impl &B) {
 
 template <int R>
 static int launch_strip(alnr_batch_impl &B, const StripArgs &a, uint32_t duos, bool local, bool stateful) {
-  const size_t smem = (size_t)a.n * kStripBlock * 4;
+  const size_t smem = a.hglobal ? 0 : (size_t)a.n * kStripBlock * 4;
   const unsigned blocks = (duos + kStripBlock - 1) / kStripBlock;
   if (blocks == 0) return ALNR_OK;
 #define ALNR_STRIP_LAUNCH(L, S)                                                                   \
@@ -116,6 +117,8 @@ int strip_run_chunk(alnr_batch_impl &B, const Chunk &c, const ChunkView &cv, con
   a.D = B.d_D.p; a.dl = dl; a.fo = fo;
   a.list = nullptr; a.list_count = nullptr; a.z_in = nullptr; a.z_out = zbuf[0]; a.nzw = nzw;
   a.fail_list = lists[0]; a.fail_count = counters + 0;
+  static const bool hrow_global = getenv("ALNR_STRIP_HROW_SMEM") == nullptr;
+  a.hglobal = hrow_global ? (uint32_t *)B.d_hcol_i.p : nullptr;
   const uint32_t R = dl.rows_per_word;
   auto go = [&](const StripArgs &args, uint32_t duos) {
     return R == 15 ? launch_strip<15>(B, args, duos, local, stateful)

@@ -44,6 +44,7 @@ struct StripArgs {
   uint32_t nzw;
   uint32_t *fail_list;
   uint32_t *fail_count;
+  uint32_t *hglobal;           // strip boundary rows in global memory (nullptr: shared memory)
 };
 
 __device__ __forceinline__ uint32_t prmt_sx(uint32_t a, uint32_t b, uint32_t sel) {
@@ -72,7 +73,8 @@ struct Best {
 struct StripCtx {
   const uint32_t *qA, *qB, *tA, *tB;
   uint32_t *dA, *dB;      // D words of the two slots (contiguous layout), strip 0
-  uint32_t *hrow;         // smem: bottom row of the previous strip, hrow[(x-1) * kStripBlock]
+  uint32_t *hrow;         // bottom row of the previous strip, hrow[(x-1) * hstride] (smem or global)
+  uint32_t hstride;
   uint32_t sA, sB;
   bool dupB;
   Best bestA, bestB;
@@ -131,14 +133,17 @@ __device__ __forceinline__ void strip_sweep(const StripArgs &a, StripCtx &c, con
   uint32_t *dpA = c.dA + (size_t)strip * a.dl.ncols, *dpB = c.dB + (size_t)strip * a.dl.ncols;
   uint32_t a0 = 0, a1 = 0, a2 = 0, a3 = 0, b0 = 0, b1 = 0, b2 = 0, b3 = 0;  // 4 pending D words per pair
   uint32_t *hp = c.hrow;
+  const uint32_t hstride = c.hstride;
+  uint32_t hnext = *hp;  // one column ahead: hides the L2 latency when the row lives in global memory
 
 #pragma unroll 1
-  for (uint32_t xm1 = 0; xm1 < n; ++xm1, hp += kStripBlock) {
+  for (uint32_t xm1 = 0; xm1 < n; ++xm1, hp += hstride) {
     const uint32_t x = xm1 + 1;
     if ((xm1 & 15) == 0) { qwA = c.qA[(size_t)(xm1 >> 4) * 32]; qwB = c.qB[(size_t)(xm1 >> 4) * 32]; }
     const uint32_t Wa = swt[qwA & 3], Wb = swt[qwB & 3];
     qwA >>= 2; qwB >>= 2;
-    uint32_t hup = *hp;
+    uint32_t hup = hnext;
+    if (xm1 + 1 < n) hnext = hp[hstride];
     uint32_t diag = hdiag0;
     hdiag0 = hup;
     // penalty of the strip's first row
@@ -157,15 +162,16 @@ __device__ __forceinline__ void strip_sweep(const StripArgs &a, StripCtx &c, con
     } else {
       np = (!LOCAL && strip == 0 && x == 1) ? ndel2 : next2;  // simple/mod.rs:72: first cell pays del
     }
-    uint32_t accT = 0, accL = 0, accN = 0, cm = 0x80008000u;
+    uint32_t accG = 0, accU = 0, accN = 0, cm = 0x80008000u, mprev = 0x80008000u;
 #pragma unroll
     for (int r = 0; r < R; ++r) {
+      // max(top, left) = max(H_up, H_left) - penalty: one max + one add instead of two adds
       const uint32_t s = prmt_sx(Wa, Wb, sel[r]);
-      const uint32_t top = __vadd2(hup, np);
-      const uint32_t left = __vadd2(h[r], np);
-      const uint32_t mx = __vmaxs2(__viaddmax_s16x2(diag, s, top), left);
-      accT += __vminu2(mx ^ top, one2) << r;
-      accL += __vminu2(mx ^ left, one2) << r;
+      const uint32_t g = __vmaxs2(hup, h[r]);
+      const uint32_t gl = __vadd2(g, np);
+      const uint32_t mx = __viaddmax_s16x2(diag, s, gl);
+      accG += __vminu2(mx ^ gl, one2) << r;   // 1: neither gap move reaches the max -> Diagonal
+      accU += __vminu2(g ^ hup, one2) << r;   // 1: H_left > H_up -> Left beats Top (Top wins ties)
       if (LOCAL) {
         const uint32_t nz = __vminu2(mx, one2);
         accN += nz << r;
@@ -175,13 +181,21 @@ __device__ __forceinline__ void strip_sweep(const StripArgs &a, StripCtx &c, con
       diag = h[r];
       h[r] = mx;
       hup = mx;
-      if (LOCAL) { if (!LASTSTRIP || (uint32_t)r < rv) cm = __vmaxs2(cm, mx); }
+      if (LOCAL) {
+        // column maximum over the valid rows, two rows per 3-input max
+        if (!LASTSTRIP || (uint32_t)r < rv) {
+          if (r & 1) cm = __vimax3_s16x2(cm, mprev, mx); else mprev = mx;
+        }
+      }
     }
+    // an odd number of valid rows leaves the last one pending in mprev
+    if (LOCAL) { if (LASTSTRIP ? (rv & 1u) : (R & 1)) cm = __vmaxs2(cm, mprev); }
     if (!LASTSTRIP) *hp = h[R - 1];
-    // direction planes of this column (both pairs at once), then one word per pair
+    // direction planes of this column (both pairs at once), then one word per pair:
+    // Top = !G & !U, Left = !G & U, Diagonal = G, Beginning = Z  (enums.rs:18-46)
     uint32_t P0, P1;
-    if (LOCAL) { P0 = ~accN | (accT & ~accL); P1 = ~accN | (accT & accL); }
-    else { P0 = accT & ~accL; P1 = accT & accL; }
+    if (LOCAL) { P0 = ~accN | (~accG & accU); P1 = ~accN | accG; }
+    else { P0 = ~accG & accU; P1 = accG; }
     a0 = a1; a1 = a2; a2 = a3; a3 = __byte_perm(P0, P1, 0x5410);
     b0 = b1; b1 = b2; b2 = b3; b3 = __byte_perm(P0, P1, 0x7632);
     if ((xm1 & 3) == 3) {
@@ -272,7 +286,13 @@ __global__ void __launch_bounds__(kStripBlock) fill_strip_kernel(StripArgs a) {
   const uint32_t nstrips = (m + R - 1) / R;
   c.dA = a.D + a.dl.word(c.sA, 0, 0);
   c.dB = a.D + a.dl.word(c.sB, 0, 0);
-  c.hrow = smem_h + tid;
+  if (a.hglobal) {  // [(duo group * n + x-1) * 32 + lane]: coalesced, L2-resident
+    c.hrow = a.hglobal + ((size_t)(duo >> 5) * a.n) * 32 + (duo & 31);
+    c.hstride = 32;
+  } else {
+    c.hrow = smem_h + tid;
+    c.hstride = kStripBlock;
+  }
   c.bestA = Best{0, 0, 0, -1};
   c.bestB = Best{0, 0, 0, -1};
   c.mismatch = 0;
@@ -282,7 +302,7 @@ __global__ void __launch_bounds__(kStripBlock) fill_strip_kernel(StripArgs a) {
   for (uint32_t x = 1; x <= n; ++x) {
     int hv = 0;
     if (!LOCAL) hv = (x == n) ? -(int)(n + 1) * a.del : -(int)x * a.del;
-    c.hrow[(x - 1) * kStripBlock] = pack2(hv, hv);
+    c.hrow[(size_t)(x - 1) * c.hstride] = pack2(hv, hv);
   }
 
   for (uint32_t strip = 0; strip + 1 < nstrips; ++strip)
