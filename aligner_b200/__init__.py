@@ -10,11 +10,12 @@ from .aligners import (Alignment, AlignmentResult, Heuristics, SimpleGlobalAlign
                        SimpleLocalAligner)
 from .batch import BatchResult, DeviceBatch, PackedPairs, align_batch
 from .enums import DNA, Direction, Error, Protein
+from .heuristic import HeuristicAligner, heuristic_batch, matrix_search, transform_matrix
 from .matrices import dna_matrix, get_blosum62
 
 __all__ = [
     "AlignerError", "Alignment", "AlignmentResult", "BatchResult", "DNA", "DeviceBatch", "Direction",
-    "Error", "GLOBAL", "Heuristics", "LOCAL", "NUM_AUTO", "NUM_F64", "NUM_I16X2", "NUM_I32",
+    "Error", "GLOBAL", "HeuristicAligner", "Heuristics", "heuristic_batch", "matrix_search", "transform_matrix", "LOCAL", "NUM_AUTO", "NUM_F64", "NUM_I16X2", "NUM_I32",
     "PackedPairs", "Protein", "SimpleGlobalAligner", "SimpleLocalAligner", "align_batch",
     "dna_matrix", "get_blosum62",
 ]

@@ -47,6 +47,16 @@ class BatchOut(C.Structure):
                 ("aln_len", u32p), ("q_aln", u8p), ("t_aln", u8p), ("status", i32p)]
 
 
+class HeuristicItems(C.Structure):
+    _fields_ = [("pair_idx", u32p), ("mat_idx", u32p), ("count", C.c_uint64), ("matrices", f64p),
+                ("n_matrices", C.c_uint32), ("kd", C.c_double), ("r_squared", C.c_double),
+                ("frequencies", f64p)]
+
+
+class HeuristicOut(C.Structure):
+    _fields_ = [("f", f64p), ("passes", i32p), ("status", i32p), ("coords", u64p), ("matrices", f64p)]
+
+
 # every symbol include/aligner_b200.h declares: name -> (restype, argtypes)
 SIGNATURES = {
     "alnr_strerror": (C.c_char_p, [C.c_int]),
@@ -67,6 +77,11 @@ SIGNATURES = {
     "alnr_batch_numeric": (C.c_int, [C.c_void_p]),
     "alnr_batch_rerun_count": (C.c_uint64, [C.c_void_p]),
     "alnr_batch_destroy": (None, [C.c_void_p]),
+    "alnr_transform_matrix": (C.c_int, [f64p, C.c_int, C.c_int, C.c_double, C.c_double, f64p, f64p]),
+    "alnr_heuristic_batch": (C.c_int, [C.POINTER(Params), C.POINTER(Batch), C.POINTER(HeuristicItems),
+                                       C.POINTER(HeuristicOut)]),
+    "alnr_matrix_search": (C.c_int, [C.POINTER(Params), C.POINTER(Batch), f64p, C.c_uint32, C.c_double,
+                                     C.c_double, f64p, f64p, u32p, f64p, f64p, i32p]),
     "alnr_measure_int_peak": (C.c_int, [C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "alnr_host_alloc": (C.c_void_p, [C.c_uint64]),
     "alnr_host_free": (None, [C.c_void_p]),

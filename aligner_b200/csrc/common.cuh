@@ -67,6 +67,10 @@ struct ChunkView {
   const uint32_t *order;   // slot -> pair index (nullptr = identity), whole batch
   uint32_t first;          // first slot of this chunk in `order`
   uint32_t count;          // slots in this chunk
+  // Optional: result index ("pair") -> sequence index.  The heuristic search aligns the same
+  // sequence pair under many matrices, so several result slots share one pair of sequences.
+  const uint32_t *seqmap = nullptr;
+  __device__ __forceinline__ uint32_t seq(uint32_t pair) const { return seqmap ? seqmap[pair] : pair; }
 };
 
 // Per-pair results produced by the fill kernels and consumed by the traceback.

@@ -1,0 +1,252 @@
+// heur.cu — the heuristic matrix-search loop on the GPU:
+//   HeuristicAligner::perform_alignment   aligner-core/src/heuristic/mod.rs:36-78
+//   outer search over candidate matrices  aligner-web/src/bin/dispatcher/handlers.rs:193-251,
+//                                         aligner-web/src/bin/node/main.rs:61-74
+// One ITEM = (sequence pair, candidate matrix).  Per round every active item runs one FP64
+// local alignment with its own current matrix (fill_exact_kernel<double>, per-item matrices),
+// the traceback accumulates the item's V x V frequency matrix (alignment.rs:13-23), and an
+// update kernel either stops the item (f did not improve: heuristic/mod.rs:73-76) or derives its
+// next matrix with transform_matrix (mod.rs:64-72) and keeps it on the active list.
+#include <algorithm>
+#include <cfloat>
+#include <cmath>
+#include <vector>
+
+#include "host_util.h"
+#include "kernels_exact.cuh"
+#include "kernels_trace.cuh"
+#include "transform.cuh"
+
+namespace alnr {
+
+struct HeurState {
+  const uint32_t *pair_idx, *mat_idx;  // per item
+  const double *matrices;              // K * VV candidates
+  const double *freqs;                 // pairs * V
+  double kd, r2;
+  int V;
+  double *Tcur;      // items * VV: matrix of the NEXT / current pass
+  double *Tlast;     // items * VV: matrix that produced the pass being judged
+  double *freqm;     // items * VV: frequency matrix of the current pass
+  double *maxf, *fcur, *fout;
+  int32_t *status, *passes;
+  uint64_t *coords_cur, *coords_out;
+  const int32_t *pair_status;
+};
+
+static __global__ void heur_init_kernel(HeurState h, uint32_t items, uint32_t *list, uint32_t *count) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= items) return;
+  const int VV = h.V * h.V;
+  int st = h.pair_status[h.pair_idx[i]];
+  if (!st) st = transform_matrix_rc(h.matrices + (size_t)h.mat_idx[i] * VV, h.V, h.V, h.kd, h.r2,
+                                    h.freqs + (size_t)h.pair_idx[i] * h.V, h.Tcur + (size_t)i * VV);
+  h.status[i] = st;
+  h.maxf[i] = 0.0;  // heuristic/mod.rs:55
+  h.passes[i] = 0;
+  h.fout[i] = 0.0;
+  if (!st) list[atomicAdd(count, 1u)] = i;
+}
+
+// after fill + traceback of one round
+static __global__ void heur_update_kernel(HeurState h, const uint32_t *list, uint32_t n_active,
+                                          uint32_t *next, uint32_t *next_count) {
+  const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n_active) return;
+  const uint32_t i = list[k];
+  const int VV = h.V * h.V;
+  if (h.status[i] != 0) return;  // e.g. 11: no positive cell — the reference panics (simple/mod.rs:214)
+  h.passes[i] += 1;
+  const double f = h.fcur[i];
+  double *T = h.Tcur + (size_t)i * VV, *L = h.Tlast + (size_t)i * VV;
+  if (f > h.maxf[i]) {  // heuristic/mod.rs:64
+    h.maxf[i] = f;
+    const int st = transform_matrix_rc(h.freqm + (size_t)i * VV, h.V, h.V, h.kd, h.r2,
+                                       h.freqs + (size_t)h.pair_idx[i] * h.V, T);  // :66-72
+    if (st) { h.status[i] = st; return; }  // .unwrap() panic in the reference
+    next[atomicAdd(next_count, 1u)] = i;
+  } else {  // :73-76 — the LAST (non-improving) result and the matrix that produced it
+    h.fout[i] = f;
+    for (int j = 0; j < VV; ++j) L[j] = T[j];
+    for (int j = 0; j < 4; ++j) h.coords_out[4 * (size_t)i + j] = h.coords_cur[4 * (size_t)i + j];
+  }
+}
+
+}  // namespace alnr
+
+using namespace alnr;
+
+extern "C" int alnr_transform_matrix(const double *matrix, int rows, int cols, double kd,
+                                     double r_squared, const double *frequencies, double *out) {
+  if (!matrix || !frequencies || !out || rows < 1 || cols < 1) return ALNR_INVALID_ARGUMENT;
+  // host instance of the same routine the kernels run (aligner-helpers/src/matrices/mod.rs:19-68)
+  std::vector<double> tmp((size_t)rows * cols);
+  int st = transform_matrix_rc(matrix, rows, cols, kd, r_squared, frequencies, tmp.data());
+  if (st) return ALNR_WRONG_MATRIX;
+  std::copy(tmp.begin(), tmp.end(), out);
+  return ALNR_OK;
+}
+
+extern "C" int alnr_heuristic_batch(const alnr_params *p, const alnr_batch *b,
+                                    const alnr_heuristic_items *it, alnr_heuristic_out *out) {
+  if (!p || !b || !it || !out || !it->matrices || !it->frequencies) return ALNR_INVALID_ARGUMENT;
+  if (p->volume < 1 || p->volume > 32) return ALNR_MATRIX_SHAPE_ERROR;
+  const int V = p->volume, VV = V * V;
+  const uint64_t P = b->count, K = it->n_matrices;
+  const bool grid = it->pair_idx == nullptr;  // full grid: item = pair * K + k
+  const uint64_t items = grid ? P * K : it->count;
+  if (items == 0) return ALNR_OK;
+  if (items >= (1ull << 31) || P >= (1ull << 31)) return ALNR_INVALID_ARGUMENT;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+    (void)cudaGetLastError();
+    set_error_detail("no usable CUDA device (this library has no CPU fallback)");
+    return ALNR_CUDA_ERROR;
+  }
+  const int device = p->device < 0 ? 0 : p->device;
+  if (device >= ndev) return ALNR_INVALID_ARGUMENT;
+  ALNR_CUDA(cudaSetDevice(device));
+  double r2 = it->r_squared;
+  if (std::fabs(r2 - 0.0) < DBL_EPSILON) r2 = (double)VV;  // heuristic/mod.rs:48-50
+
+  uint32_t n_max = 0, m_max = 0;
+  for (uint64_t i = 0; i < P; ++i) {
+    n_max = std::max<uint32_t>(n_max, (uint32_t)(b->q_off[i + 1] - b->q_off[i]));
+    m_max = std::max<uint32_t>(m_max, (uint32_t)(b->t_off[i + 1] - b->t_off[i]));
+  }
+  const uint64_t q_total = b->q_off[P], t_total = b->t_off[P];
+  const DLayout dl0 = DLayout::make(16, std::max(m_max, 1u), std::max(n_max, 1u), false);
+  const uint64_t per_item = (uint64_t)dl0.nstrips * dl0.ncols * 4 + 8ull * (m_max + 1) + 3ull * VV * 8 + 128;
+  size_t free_b = 0, total_b = 0;
+  ALNR_CUDA(cudaMemGetInfo(&free_b, &total_b));
+  const uint64_t budget = std::max<uint64_t>(std::min<uint64_t>(free_b / 3, 16ull << 30), 64ull << 20);
+  uint64_t chunk = std::max<uint64_t>(budget / per_item / 32 * 32, 32);
+  chunk = std::min<uint64_t>(chunk, std::min<uint64_t>((items + 31) / 32 * 32, 1u << 20));
+
+  cudaStream_t stream;
+  ALNR_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+  struct StreamGuard { cudaStream_t s; ~StreamGuard() { cudaStreamSynchronize(s); cudaStreamDestroy(s); } } guard{stream};
+
+  DevBuf<uint8_t> d_q, d_t;
+  DevBuf<uint64_t> d_qoff, d_toff, d_cc, d_co;
+  DevBuf<uint32_t> d_pi, d_mi, d_lists, d_cnt, d_start, d_D;
+  DevBuf<int32_t> d_pst, d_st, d_passes;
+  DevBuf<int> d_flag;
+  DevBuf<double> d_mats, d_freqs, d_T, d_L, d_F, d_maxf, d_fcur, d_fout, d_corner, d_hcol;
+  ALNR_CUDA(d_q.alloc(q_total + 16)); ALNR_CUDA(d_t.alloc(t_total + 16));
+  ALNR_CUDA(d_qoff.alloc(P + 1)); ALNR_CUDA(d_toff.alloc(P + 1));
+  ALNR_CUDA(d_mats.alloc(K * VV)); ALNR_CUDA(d_freqs.alloc(P * V));
+  ALNR_CUDA(d_pst.alloc(P)); ALNR_CUDA(d_flag.alloc(4));
+  ALNR_CUDA(d_pi.alloc(chunk)); ALNR_CUDA(d_mi.alloc(chunk));
+  ALNR_CUDA(d_lists.alloc(2 * chunk)); ALNR_CUDA(d_cnt.alloc(64));
+  ALNR_CUDA(d_start.alloc(2 * chunk)); ALNR_CUDA(d_D.alloc(dl0.words_for(chunk)));
+  ALNR_CUDA(d_st.alloc(chunk)); ALNR_CUDA(d_passes.alloc(chunk));
+  ALNR_CUDA(d_T.alloc(chunk * VV)); ALNR_CUDA(d_L.alloc(chunk * VV)); ALNR_CUDA(d_F.alloc(chunk * VV));
+  ALNR_CUDA(d_maxf.alloc(chunk)); ALNR_CUDA(d_fcur.alloc(chunk)); ALNR_CUDA(d_fout.alloc(chunk));
+  ALNR_CUDA(d_corner.alloc(chunk)); ALNR_CUDA(d_hcol.alloc((chunk + 31) / 32 * 32 * ((uint64_t)m_max + 1)));
+  ALNR_CUDA(d_cc.alloc(chunk * 4)); ALNR_CUDA(d_co.alloc(chunk * 4));
+
+  auto h2d = [&](void *dst, const void *src, size_t bytes) {
+    return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, stream);
+  };
+  ALNR_CUDA(h2d(d_q.p, b->q, q_total)); ALNR_CUDA(h2d(d_t.p, b->t, t_total));
+  ALNR_CUDA(h2d(d_qoff.p, b->q_off, (P + 1) * 8)); ALNR_CUDA(h2d(d_toff.p, b->t_off, (P + 1) * 8));
+  ALNR_CUDA(h2d(d_mats.p, it->matrices, K * VV * 8)); ALNR_CUDA(h2d(d_freqs.p, it->frequencies, P * V * 8));
+  // per-pair validation (empty sequences, symbols outside the alphabet)
+  ALNR_CUDA(cudaMemsetAsync(d_flag.p, 0, 4 * sizeof(int), stream));
+  any_symbol_out_of_range_kernel<<<148 * 4, 256, 0, stream>>>(d_q.p, q_total, V, d_flag.p); ALNR_LAUNCHED();
+  any_symbol_out_of_range_kernel<<<148 * 4, 256, 0, stream>>>(d_t.p, t_total, V, d_flag.p); ALNR_LAUNCHED();
+  {
+    ChunkView cvp{d_q.p, d_t.p, d_qoff.p, d_toff.p, nullptr, 0, (uint32_t)P};
+    validate_kernel<<<(unsigned)((P + 127) / 128), 128, 0, stream>>>(cvp, V, d_pst.p, d_flag.p); ALNR_LAUNCHED();
+  }
+
+  std::vector<uint32_t> hpi(chunk), hmi(chunk);
+  for (uint64_t base = 0; base < items; base += chunk) {
+    const uint32_t cnt = (uint32_t)std::min<uint64_t>(chunk, items - base);
+    for (uint32_t i = 0; i < cnt; ++i) {
+      const uint64_t g = base + i;
+      hpi[i] = grid ? (uint32_t)(g / K) : it->pair_idx[g];
+      hmi[i] = grid ? (uint32_t)(g % K) : it->mat_idx[g];
+      if (hpi[i] >= P || hmi[i] >= K) return ALNR_INVALID_ARGUMENT;
+    }
+    ALNR_CUDA(h2d(d_pi.p, hpi.data(), cnt * 4)); ALNR_CUDA(h2d(d_mi.p, hmi.data(), cnt * 4));
+    ALNR_CUDA(cudaStreamSynchronize(stream));  // hpi/hmi are reused by the next chunk
+    HeurState hs{d_pi.p, d_mi.p, d_mats.p, d_freqs.p, it->kd, r2, V, d_T.p, d_L.p, d_F.p, d_maxf.p,
+                 d_fcur.p, d_fout.p, d_st.p, d_passes.p, d_cc.p, d_co.p, d_pst.p};
+    uint32_t *lists[2] = {d_lists.p, d_lists.p + chunk};
+    ALNR_CUDA(cudaMemsetAsync(d_cnt.p, 0, 64 * sizeof(uint32_t), stream));
+    ALNR_CUDA(cudaMemsetAsync(d_co.p, 0, (size_t)cnt * 32, stream));
+    heur_init_kernel<<<(cnt + 127) / 128, 128, 0, stream>>>(hs, cnt, lists[0], d_cnt.p); ALNR_LAUNCHED();
+    uint32_t n_active = 0;
+    ALNR_CUDA(cudaMemcpyAsync(&n_active, d_cnt.p, 4, cudaMemcpyDeviceToHost, stream));
+    ALNR_CUDA(cudaStreamSynchronize(stream));
+    for (int round = 0; n_active > 0; ++round) {
+      if (round >= 60) { set_error_detail("heuristic loop did not converge in 60 passes"); return ALNR_CALCULATION_ERROR; }
+      const uint32_t *cur = lists[round & 1];
+      uint32_t *nxt = lists[(round + 1) & 1];
+      uint32_t *cnt_next = d_cnt.p + 1 + round;
+      ChunkView cv{d_q.p, d_t.p, d_qoff.p, d_toff.p, cur, 0, n_active};
+      cv.seqmap = d_pi.p;
+      FillOut fo{d_fcur.p, d_corner.p, d_start.p, d_st.p};
+      ExactArgs<double> e;
+      e.cv = cv; e.mode = ALNR_LOCAL; e.V = V; e.del = p->del; e.ext = p->ext;
+      e.matrix = nullptr; e.hcol = d_hcol.p; e.hrows = m_max + 1; e.D = d_D.p; e.dl = dl0; e.fo = fo;
+      e.H_out = nullptr; e.D_out = nullptr; e.item_matrices = d_T.p;
+      fill_exact_kernel<double><<<(n_active + 127) / 128, 128, (size_t)VV * 8, stream>>>(e); ALNR_LAUNCHED();
+      TraceOut to{d_cc.p, nullptr, nullptr, nullptr, nullptr, d_F.p};
+      TraceArgs ta{cv, ALNR_LOCAL, V, d_D.p, dl0, fo, to};
+      traceback_kernel<<<(n_active + 127) / 128, 128, 0, stream>>>(ta); ALNR_LAUNCHED();
+      heur_update_kernel<<<(n_active + 127) / 128, 128, 0, stream>>>(hs, cur, n_active, nxt, cnt_next); ALNR_LAUNCHED();
+      ALNR_CUDA(cudaMemcpyAsync(&n_active, cnt_next, 4, cudaMemcpyDeviceToHost, stream));
+      ALNR_CUDA(cudaStreamSynchronize(stream));
+    }
+    auto d2h = [&](void *dst, const void *src, size_t bytes) -> cudaError_t {
+      if (!dst) return cudaSuccess;
+      return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, stream);
+    };
+    ALNR_CUDA(d2h(out->f ? out->f + base : nullptr, d_fout.p, (size_t)cnt * 8));
+    ALNR_CUDA(d2h(out->passes ? out->passes + base : nullptr, d_passes.p, (size_t)cnt * 4));
+    ALNR_CUDA(d2h(out->status ? out->status + base : nullptr, d_st.p, (size_t)cnt * 4));
+    ALNR_CUDA(d2h(out->coords ? out->coords + base * 4 : nullptr, d_co.p, (size_t)cnt * 32));
+    ALNR_CUDA(d2h(out->matrices ? out->matrices + base * VV : nullptr, d_L.p, (size_t)cnt * VV * 8));
+    ALNR_CUDA(cudaStreamSynchronize(stream));
+  }
+  return ALNR_OK;
+}
+
+// Outer search (dispatcher/handlers.rs:193-251 + node/main.rs:61-74 + the arg-best of
+// repository/queries.rs:74-80, taken as a MAXIMUM — the reference's ascending sort is a defect):
+// every pair under every candidate matrix, fitness[k] = sum over pairs of f(pair, k) added in
+// pair order (fixed, so the f64 sum is reproducible), best_k[pair] = first k with the largest f.
+extern "C" int alnr_matrix_search(const alnr_params *p, const alnr_batch *b, const double *matrices,
+                                  uint32_t n_matrices, double kd, double r_squared,
+                                  const double *frequencies, double *fitness, uint32_t *best_k,
+                                  double *best_f, double *f_grid, int32_t *status_grid) {
+  if (!b || !fitness || n_matrices == 0) return ALNR_INVALID_ARGUMENT;
+  const uint64_t P = b->count, K = n_matrices;
+  std::vector<double> fbuf;
+  std::vector<int32_t> sbuf;
+  double *fg = f_grid;
+  int32_t *sg = status_grid;
+  if (!fg) { fbuf.resize(P * K); fg = fbuf.data(); }
+  if (!sg) { sbuf.resize(P * K); sg = sbuf.data(); }
+  alnr_heuristic_items it{nullptr, nullptr, 0, matrices, n_matrices, kd, r_squared, frequencies};
+  alnr_heuristic_out out{fg, nullptr, sg, nullptr, nullptr};
+  int st = alnr_heuristic_batch(p, b, &it, &out);
+  if (st) return st;
+  for (uint64_t k = 0; k < K; ++k) fitness[k] = 0.0;
+  for (uint64_t i = 0; i < P; ++i) {
+    uint32_t bk = 0;
+    double bf = -INFINITY;
+    for (uint64_t k = 0; k < K; ++k) {
+      if (sg[i * K + k] != 0) continue;  // items on which the reference panics contribute nothing
+      const double f = fg[i * K + k];
+      fitness[k] = fitness[k] + f;
+      if (f > bf) { bf = f; bk = (uint32_t)k; }
+    }
+    if (best_k) best_k[i] = bk;
+    if (best_f) best_f[i] = bf;
+  }
+  return ALNR_OK;
+}

@@ -51,14 +51,15 @@ struct ExactArgs {
   uint8_t *D_out;    // optional, 1 byte per cell
   const uint32_t *list = nullptr;        // optional: chunk slots to process (strip leftovers)
   const uint32_t *list_count = nullptr;
+  const T *item_matrices = nullptr;      // optional: one V*V matrix per result index (heuristic search)
 };
 
 // grid: ceil(count/128) blocks of 128 threads; smem: V*V*sizeof(T)
 template <typename T>
 __global__ void __launch_bounds__(128) fill_exact_kernel(ExactArgs<T> a) {
   extern __shared__ unsigned char smem_raw[];
-  T *smat = reinterpret_cast<T *>(smem_raw);
-  for (int i = threadIdx.x; i < a.V * a.V; i += blockDim.x) smat[i] = a.matrix[i];
+  T *smat_s = reinterpret_cast<T *>(smem_raw);
+  if (!a.item_matrices) for (int i = threadIdx.x; i < a.V * a.V; i += blockDim.x) smat_s[i] = a.matrix[i];
   __syncthreads();
 
   const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -73,10 +74,12 @@ __global__ void __launch_bounds__(128) fill_exact_kernel(ExactArgs<T> a) {
   if (a.fo.status[pair] != 0 && !(a.list && a.fo.status[pair] == 11)) return;
   if (a.list) a.fo.status[pair] = 0;
 
-  const uint8_t *q = a.cv.q + a.cv.q_off[pair];
-  const uint8_t *t = a.cv.t + a.cv.t_off[pair];
-  const uint32_t n = (uint32_t)(a.cv.q_off[pair + 1] - a.cv.q_off[pair]);
-  const uint32_t m = (uint32_t)(a.cv.t_off[pair + 1] - a.cv.t_off[pair]);
+  const uint32_t sp = a.cv.seq(pair);
+  const uint8_t *q = a.cv.q + a.cv.q_off[sp];
+  const uint8_t *t = a.cv.t + a.cv.t_off[sp];
+  const uint32_t n = (uint32_t)(a.cv.q_off[sp + 1] - a.cv.q_off[sp]);
+  const uint32_t m = (uint32_t)(a.cv.t_off[sp + 1] - a.cv.t_off[sp]);
+  const T *smat = a.item_matrices ? a.item_matrices + (size_t)pair * a.V * a.V : smat_s;
   const bool glob = a.mode == 0;
   const uint32_t group = idx >> 5, lane = idx & 31;  // score-column scratch is per thread
   T *hc = a.hcol + (uint64_t)group * a.hrows * 32 + lane;  // hc[y*32]

@@ -332,7 +332,7 @@ __global__ void __launch_bounds__(kStripBlock) fill_strip_kernel(StripArgs a) {
 
 // 2-bit packing of the slots [first, first+count) of one sequence set into the coalesced
 // [(group*nw + w)*32 + lane] layout (group = batch slot / 32; first is a multiple of 32).
-__global__ void pack2bit_kernel(const uint8_t *seq, const uint64_t *off, const uint32_t *order,
+static __global__ void pack2bit_kernel(const uint8_t *seq, const uint64_t *off, const uint32_t *order,
                                 uint32_t first, uint32_t count, uint32_t nw, uint32_t *out) {
   const uint64_t gid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const uint32_t lane = gid & 31;

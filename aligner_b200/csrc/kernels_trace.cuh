@@ -7,12 +7,13 @@ namespace alnr {
 // One thread per pair: empty sequences and out-of-alphabet symbols become statuses
 // (the reference panics: simple/mod.rs:103-104 unwrap, matrix[[t,q]] bounds check).
 // The per-symbol scan only runs when the coalesced sweep below flagged the batch.
-__global__ void validate_kernel(ChunkView cv, int V, int32_t *status, const int *flag) {
+static __global__ void validate_kernel(ChunkView cv, int V, int32_t *status, const int *flag) {
   const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
   if (slot >= cv.count) return;
   const uint32_t pair = cv.order ? cv.order[cv.first + slot] : cv.first + slot;
-  const uint64_t q0 = cv.q_off[pair], q1 = cv.q_off[pair + 1];
-  const uint64_t t0 = cv.t_off[pair], t1 = cv.t_off[pair + 1];
+  const uint32_t sp = cv.seq(pair);
+  const uint64_t q0 = cv.q_off[sp], q1 = cv.q_off[sp + 1];
+  const uint64_t t0 = cv.t_off[sp], t1 = cv.t_off[sp + 1];
   int st = 0;
   if (q1 == q0 || t1 == t0) st = 10;  // ALNR_EMPTY_INPUT
   if (*flag) {
@@ -23,7 +24,7 @@ __global__ void validate_kernel(ChunkView cv, int V, int32_t *status, const int 
 }
 
 // Fast whole-buffer symbol check (coalesced 16-byte loads); flags[0] != 0 iff some byte >= V.
-__global__ void any_symbol_out_of_range_kernel(const uint8_t *buf, uint64_t len, int V, int *flag) {
+static __global__ void any_symbol_out_of_range_kernel(const uint8_t *buf, uint64_t len, int V, int *flag) {
   const uint64_t tid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
   bool bad = false;
@@ -59,13 +60,14 @@ struct TraceArgs {
 // (simple/mod.rs:99-130 global, :213-245 local).  The reference seeds the output with the
 // start pair BEFORE the walk and reverses at the end; writing backwards from the end of the
 // pair's slot yields the same string right-aligned with no reversal pass.
-__global__ void __launch_bounds__(128) traceback_kernel(TraceArgs a) {
+static __global__ void __launch_bounds__(128) traceback_kernel(TraceArgs a) {
   const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
   if (slot >= a.cv.count) return;
   const uint32_t pair = a.cv.order ? a.cv.order[a.cv.first + slot] : a.cv.first + slot;
-  const uint64_t qo = a.cv.q_off[pair], to = a.cv.t_off[pair];
-  const uint32_t n = (uint32_t)(a.cv.q_off[pair + 1] - qo);
-  const uint32_t m = (uint32_t)(a.cv.t_off[pair + 1] - to);
+  const uint32_t sp = a.cv.seq(pair);
+  const uint64_t qo = a.cv.q_off[sp], to = a.cv.t_off[sp];
+  const uint32_t n = (uint32_t)(a.cv.q_off[sp + 1] - qo);
+  const uint32_t m = (uint32_t)(a.cv.t_off[sp + 1] - to);
   const uint64_t slot_begin = qo + to + pair;
   const uint64_t slot_end = slot_begin + n + m + 1;
   double *freq = a.to.freq ? a.to.freq + (size_t)pair * a.V * a.V : nullptr;
@@ -122,7 +124,7 @@ __global__ void __launch_bounds__(128) traceback_kernel(TraceArgs a) {
 //           per store instead of one scattered byte per thread.
 constexpr int kTraceBlock = 128;
 
-__global__ void __launch_bounds__(kTraceBlock) traceback_coop_kernel(TraceArgs a, uint32_t nmw) {
+static __global__ void __launch_bounds__(kTraceBlock) traceback_coop_kernel(TraceArgs a, uint32_t nmw) {
   extern __shared__ uint32_t mv[];  // mv[w * kTraceBlock + tid]
   __shared__ uint32_t s_len[kTraceBlock], s_sy[kTraceBlock], s_sx[kTraceBlock];
   const uint32_t tid = threadIdx.x;

@@ -151,6 +151,47 @@ int alnr_batch_numeric(alnr_batch_handle *h);           /* domain selected for t
 uint64_t alnr_batch_rerun_count(alnr_batch_handle *h);  /* pairs whose speculation was redone */
 void alnr_batch_destroy(alnr_batch_handle *h);
 
+/* ---- heuristic matrix search ---------------------------------------------------------------
+ * transform_matrix (aligner-helpers/src/matrices/mod.rs:19-68): rows x cols matrix, frequencies
+ * [rows]; out may alias nothing.  Returns ALNR_WRONG_MATRIX on Roots::No. */
+int alnr_transform_matrix(const double *matrix, int rows, int cols, double kd, double r_squared,
+                          const double *frequencies, double *out);
+
+/* Items of a heuristic batch: item i aligns pair pair_idx[i] starting from candidate matrix
+ * mat_idx[i].  pair_idx == NULL means the full grid, item = pair * n_matrices + k. */
+typedef struct {
+  const uint32_t *pair_idx;
+  const uint32_t *mat_idx;
+  uint64_t count;            /* items (ignored for the full grid) */
+  const double *matrices;    /* n_matrices * V * V, each [t][q] */
+  uint32_t n_matrices;
+  double kd;                 /* Heuristics.kd          (lib.rs:21-25) */
+  double r_squared;          /* Heuristics.r_squared; 0 => V*V (heuristic/mod.rs:48-50) */
+  const double *frequencies; /* Heuristics.frequencies per PAIR: count_pairs * V */
+} alnr_heuristic_items;
+
+typedef struct {          /* caller-provided, any pointer may be NULL */
+  double *f;              /* [items] Alignment.f of the LAST pass (heuristic/mod.rs:73-76) */
+  int32_t *passes;        /* [items] local alignments run (>= 2 when status == 0) */
+  int32_t *status;        /* [items] */
+  uint64_t *coords;       /* [items*4] of the last pass */
+  double *matrices;       /* [items*V*V] AlignmentResult.matrix = Some(T): the matrix of the last pass */
+} alnr_heuristic_out;
+
+/* HeuristicAligner::perform_alignment (aligner-core/src/heuristic/mod.rs:36-78) over many
+ * (pair, matrix) items; p->matrix is ignored, p->mode must be ALNR_LOCAL. */
+int alnr_heuristic_batch(const alnr_params *p, const alnr_batch *b, const alnr_heuristic_items *items,
+                         alnr_heuristic_out *out);
+
+/* The outer search the web layer runs through Kafka + MariaDB (dispatcher/handlers.rs:193-251,
+ * node/main.rs:61-74): all pairs x all candidate matrices.  fitness[k] = sum_pairs f(pair, k)
+ * (added in pair order), best_k/best_f per pair (first maximum); f_grid/status_grid optional
+ * [pairs * n_matrices]. */
+int alnr_matrix_search(const alnr_params *p, const alnr_batch *b, const double *matrices,
+                       uint32_t n_matrices, double kd, double r_squared, const double *frequencies,
+                       double *fitness, uint32_t *best_k, double *best_f, double *f_grid,
+                       int32_t *status_grid);
+
 /* Roofline denominators measured on the device: arithmetic INT32 ops/s (an op = one
  * 32-bit add / max / logic op / multiply-add lane) of alu-pipe-only chains and of a 1:1
  * alu-pipe + fma-pipe mix over all SMs. */
