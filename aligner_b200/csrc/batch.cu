@@ -10,6 +10,7 @@
 #include "kernels_exact.cuh"
 #include "kernels_trace.cuh"
 #include "strip_launch.h"
+#include "wave_launch.h"
 
 namespace alnr {
 
@@ -124,12 +125,26 @@ int alnr_batch_impl::plan_chunks(const uint64_t *q_off, const uint64_t *t_off) {
     uint64_t c = std::min<uint64_t>(groups * 32, count - s);
     if (c < count - s) c = std::max<uint64_t>(c / 64 * 64, 32);  // keep duo-kernel warps whole
     if (c > max_chunk) c = max_chunk;
+    uint32_t m1, n1;
+    dims(s, m1, n1);
+    const bool wave = wave_eligible(*this, m1, n1);
+    if (wave) { c = 1; m = m1; n = n1; }
     Chunk ck{(uint32_t)s, (uint32_t)c, m, n, 0, 0, 0, 0};
+    if (wave) {
+      const uint64_t pidx = uniform ? s : order[s];
+      ck.wave = true; ck.wave_pair = (uint32_t)pidx; ck.q0 = q_off[pidx]; ck.t0 = t_off[pidx];
+      ck.q1 = q_off[pidx + 1]; ck.t1 = t_off[pidx + 1];
+    } else
     if (uniform) { ck.q0 = q_off[s]; ck.q1 = q_off[s + c]; ck.t0 = t_off[s]; ck.t1 = t_off[s + c]; }
     chunks.push_back(ck);
     s += c;
   }
   return ALNR_OK;
+}
+
+DLayout alnr_batch_impl::layout_for(const Chunk &c) const {
+  if (c.wave) return DLayout::make(16, c.m_max, c.n_max, true, 0);
+  return DLayout::make(d_rows_per_word(*this, c.m_max), c.m_max, c.n_max, numeric == ALNR_NUM_I16X2);
 }
 
 int alnr_batch_impl::init(const alnr_params *p, const alnr_batch *b, bool want_mats) {
@@ -207,7 +222,7 @@ int alnr_batch_impl::init(const alnr_params *p, const alnr_batch *b, bool want_m
 
   uint64_t dwords = 1, hcol = 1;
   for (const Chunk &c : chunks) {
-    const DLayout dl = DLayout::make(d_rows_per_word(*this, c.m_max), c.m_max, c.n_max, numeric == ALNR_NUM_I16X2);
+    const DLayout dl = layout_for(c);
     dwords = std::max<uint64_t>(dwords, dl.words_for(c.count));
     hcol = std::max<uint64_t>(hcol, (uint64_t)((c.count + 31) / 32) * 32 * ((uint64_t)std::max(c.m_max, c.n_max) + 1));
   }
@@ -261,9 +276,9 @@ int alnr_batch_impl::run_chunk(size_t ci) {
   FillOut fo{d_f.p, d_corner.p, d_start.p, d_status.p};
   TraceOut to{d_coords.p, d_alnoff.p, d_alnlen.p, d_qaln.p, d_taln.p, nullptr};
   ChunkView cv{d_q.p, d_t.p, d_qoff.p, d_toff.p, uniform ? nullptr : d_order.p, c.first, c.count};
-  const DLayout dl = DLayout::make(d_rows_per_word(*this, c.m_max), c.m_max, c.n_max, numeric == ALNR_NUM_I16X2);
+  const DLayout dl = layout_for(c);
   // symbol validation: one coalesced sweep; the per-pair scan only runs if it found something
-  if (uniform) {
+  if (uniform || c.wave) {
     const unsigned gq = (unsigned)std::min<uint64_t>(148 * 8, (c.q1 - c.q0) / 4096 + 1);
     const unsigned gt = (unsigned)std::min<uint64_t>(148 * 8, (c.t1 - c.t0) / 4096 + 1);
     any_symbol_out_of_range_kernel<<<gq, 256, 0, stream>>>(d_q.p + c.q0, c.q1 - c.q0, V, d_flags.p);
@@ -275,7 +290,8 @@ int alnr_batch_impl::run_chunk(size_t ci) {
   ALNR_LAUNCHED();
   int st = fill_mark(false);
   if (st) return st;
-  if (numeric == ALNR_NUM_F64) st = launch_exact<double>(*this, c, cv, dl, fo, d_hcol_d.p, d_matd.p);
+  if (c.wave) st = wave_run_pair(*this, c, dl, fo);
+  else if (numeric == ALNR_NUM_F64) st = launch_exact<double>(*this, c, cv, dl, fo, d_hcol_d.p, d_matd.p);
   else if (numeric == ALNR_NUM_I32) st = launch_exact<int>(*this, c, cv, dl, fo, d_hcol_i.p, d_mati.p);
   else st = strip_run_chunk(*this, c, cv, dl, fo);
   if (st) return st;

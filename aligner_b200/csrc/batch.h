@@ -12,6 +12,8 @@ struct Chunk {
   uint32_t first, count;      // slots
   uint32_t m_max, n_max;      // chunk-wide maxima
   uint64_t q0, q1, t0, t1;    // symbol ranges of the chunk (identity order only)
+  bool wave = false;          // one long pair: intra-pair wavefront kernel
+  uint32_t wave_pair = 0;     // its pair index; q0/t0 = its symbol offsets
 };
 
 struct alnr_batch_impl {
@@ -56,6 +58,7 @@ struct alnr_batch_impl {
   uint32_t max_chunk = 1u << 22;
   int download(alnr_batch_out *out);
   int classify();
+  DLayout layout_for(const Chunk &c) const;
   int plan_chunks(const uint64_t *q_off, const uint64_t *t_off);
 };
 

@@ -45,15 +45,17 @@ struct DLayout {
     return (((uint64_t)group * nstrips + strip) * ncols + xm1) * 32ull + lane;
   }
   __host__ __device__ inline uint64_t words_for(uint64_t slots) const {
+    if (contiguous) return slots * (uint64_t)nstrips * ncols + 4;
     return ((slots + 31) / 32) * (uint64_t)nstrips * ncols * 32ull;
   }
-  static inline DLayout make(uint32_t rows_per_word, uint32_t m_max, uint32_t n_max, bool contig) {
+  static inline DLayout make(uint32_t rows_per_word, uint32_t m_max, uint32_t n_max, bool contig,
+                             int planes_opt = -1) {
     DLayout d;
     d.rows_per_word = rows_per_word;
     d.nstrips = (m_max + rows_per_word - 1) / rows_per_word;
     d.ncols = contig ? (n_max + 3) / 4 * 4 : n_max;
     d.contiguous = contig ? 1u : 0u;
-    d.planes = contig ? 1u : 0u;
+    d.planes = planes_opt >= 0 ? (uint32_t)planes_opt : (contig ? 1u : 0u);
     return d;
   }
 };

@@ -1,0 +1,97 @@
+#!/usr/bin/env python
+"""Side benchmarks for the BASELINE configs that are not the bench.py headline (C1, C2, C4, C5).
+
+  python scripts/bench_configs.py [c4] [c4full] [c5] [c12]
+
+Prints one JSON line per measurement (GCUPS, device time through the C-ABI call incl. copies)."""
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in (ROOT, os.path.join(ROOT, "tests")):
+    sys.path.insert(0, p)
+
+import aligner_b200 as ab  # noqa: E402
+from aligner_b200 import _native as N  # noqa: E402
+from aligner_b200 import workloads as W  # noqa: E402
+
+
+def timed_pair(mode, q, t, d, e, M, symbols, reps=3):
+    cls = ab.SimpleGlobalAligner if mode == "global" else ab.SimpleLocalAligner
+    al = cls.from_seqs(q, t, symbols=symbols)
+    r = al.perform_alignment(d, e, M, want_matrices=False)  # warm-up
+    best = 1e9
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        r = al.perform_alignment(d, e, M, want_matrices=False)
+        best = min(best, time.perf_counter() - t0)
+    return r, best
+
+
+def emit(name, cells, secs, **kw):
+    print(json.dumps(dict(config=name, cells=cells, seconds=secs, gcups=cells / secs / 1e9, **kw)), flush=True)
+
+
+def c4(n, check):
+    q, t = W.dna_long_pair(n, seed=4)
+    M = ab.dna_matrix(5, -4)
+    r, secs = timed_pair("global", q, t, 8, 8, M, ab.DNA)
+    extra = {}
+    if check:
+        import oracle_lib as O
+        t0 = time.perf_counter()
+        ref = O.align_pair("global", q, t, 8.0, 8.0, M, lean=True)
+        cpu = time.perf_counter() - t0
+        ok = bool(r.corner_score == ref["corner"] and (r.alignment.query == ref["q_aln"]).all()
+                  and (r.alignment.target == ref["t_aln"]).all())
+        extra = dict(parity=ok, cpu_lean_oracle_seconds=cpu, cpu_gcups=len(q) * len(t) / cpu / 1e9)
+    emit("C4 global %dx%d DNA +5/-4 d=e=8 (wavefront + device traceback, e2e single-pair call)" % (len(q), len(t)),
+         float(len(q)) * len(t), secs, score=r.corner_score, aln_len=len(r.alignment.query), **extra)
+
+
+def c12():
+    ex = json.load(open(os.path.join(ROOT, "tests", "golden", "examples.json")))
+    book = [ab.Protein.str_to_vec(r["seq"]) for r in ex["book_example_1.fasta"]]
+    prot = [ab.Protein.str_to_vec(r["seq"]) for r in ex["protein.fasta"]]
+    gene = [ab.DNA.from_u8_vec(r["seq"].encode()) for r in ex["human_gene_example.fasta"]]
+    r, s = timed_pair("global", book[0], book[1], 8, 8, ab.get_blosum62(), ab.Protein, reps=20)
+    emit("C1 book example global BLOSUM62 d=e=8 (latency of one call)", 70.0, s, score=r.corner_score)
+    r, s = timed_pair("local", prot[0], prot[1], 11, 2, ab.get_blosum62(), ab.Protein, reps=10)
+    emit("C2 protein.fasta local BLOSUM62 d=11 e=2 (latency of one call)", 340.0 * 341, s, f=r.alignment.f)
+    r, s = timed_pair("global", gene[0], gene[1], 8, 8, ab.dna_matrix(), ab.DNA, reps=10)
+    emit("C4 file human_gene_example global d=e=8 (latency of one call)", 1231.0 * 1020, s, score=r.corner_score)
+
+
+def c5(P, K):
+    pairs = W.protein_pairs(0, P, 270, 330)
+    mats = W.candidate_matrices(K)
+    freqs = W.pair_frequencies(pairs, 24)
+    ab.matrix_search(pairs.__class__.from_lists(*zip(*[pairs.pair(i) for i in range(min(P, 4))])),
+                     mats[:2], 5, 5, -1.0, 576.0, freqs[:min(P, 4)])  # warm-up
+    t0 = time.perf_counter()
+    res = ab.heuristic_batch(pairs, mats, 5, 5, -1.0, 576.0, freqs, want_matrices=False)
+    secs = time.perf_counter() - t0
+    n = np.diff(pairs.q_off).astype(np.float64)
+    m = np.diff(pairs.t_off).astype(np.float64)
+    passes = res.passes.reshape(P, K).astype(np.float64)
+    cells = float((passes * (n * m)[:, None]).sum())
+    emit("C5 heuristic search %d pairs x %d matrices (~300 aa, FP64)" % (P, K), cells, secs,
+         items=P * K, mean_passes=float(passes.mean()), ok_items=int((res.status == 0).sum()))
+
+
+if __name__ == "__main__":
+    what = sys.argv[1:] or ["c12", "c4"]
+    if N.lib().alnr_device_count() < 1:
+        raise SystemExit("needs a GPU")
+    if "c12" in what:
+        c12()
+    if "c4" in what:
+        c4(20000, True)
+    if "c4full" in what:
+        c4(100000, "nocheck" not in what)
+    if "c5" in what:
+        c5(200, 50)

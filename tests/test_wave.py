@@ -1,0 +1,59 @@
+"""Intra-pair wavefront kernel (BASELINE config 4 shapes) against the lean oracle."""
+import numpy as np
+import pytest
+
+import oracle_lib as O
+
+import aligner_b200 as ab
+from aligner_b200 import _native as N
+from aligner_b200 import workloads as W
+
+pytestmark = pytest.mark.gpu
+
+
+def _long_pair(n, seed):
+    q, t = W.dna_long_pair(n, seed=seed)
+    return q, t
+
+
+@pytest.mark.parametrize("n,mode,d,e", [(4200, "global", 8, 8), (4200, "global", 10, 2), (4200, "local", 6, 6),
+                                        (9000, "global", 8, 8), (9000, "local", 7, 7)])
+def test_wavefront_vs_lean_oracle(n, mode, d, e):
+    q, t = _long_pair(n, seed=4 + n)
+    M = ab.dna_matrix(5, -4)
+    ref = O.align_pair(mode, q, t, float(d), float(e), M, lean=True)
+    assert ref["status"] == 0
+    cls = ab.SimpleGlobalAligner if mode == "global" else ab.SimpleLocalAligner
+    r = cls.from_seqs(q, t, symbols=ab.DNA).perform_alignment(d, e, M, want_matrices=False)
+    assert r.numeric == N.NUM_I32
+    assert r.alignment.f == ref["f"] and r.corner_score == ref["corner"]
+    assert r.alignment.coords == ref["coords"]
+    assert (r.alignment.query == ref["q_aln"]).all() and (r.alignment.target == ref["t_aln"]).all()
+
+
+def test_wavefront_rectangular_and_in_ragged_batch():
+    rng = np.random.default_rng(3)
+    big_q = rng.integers(0, 4, 7001).astype(np.uint8)
+    big_t = np.concatenate([big_q[:3000], rng.integers(0, 4, 333).astype(np.uint8), big_q[3000:5123]])
+    qs = [rng.integers(0, 4, 80).astype(np.uint8), big_q, rng.integers(0, 4, 33).astype(np.uint8)]
+    ts = [rng.integers(0, 4, 70).astype(np.uint8), big_t, rng.integers(0, 4, 90).astype(np.uint8)]
+    pairs = ab.PackedPairs.from_lists(qs, ts)
+    M = ab.dna_matrix(3, -2)
+    for mode in ("global", "local"):
+        res = ab.align_batch(N.GLOBAL if mode == "global" else N.LOCAL, pairs, M, 5, 5)
+        for i in range(3):
+            ref = O.align_pair(mode, qs[i], ts[i], 5.0, 5.0, M, lean=True)
+            assert res.status[i] == 0 and res.f[i] == ref["f"] and res.corner[i] == ref["corner"]
+            qa, ta = res.alignment(i)
+            assert (qa == ref["q_aln"]).all() and (ta == ref["t_aln"]).all()
+            assert tuple(int(v) for v in res.coords[i]) == ref["coords"][0] + ref["coords"][1]
+
+
+def test_wavefront_protein_matrix():
+    pairs = W.protein_pairs(0, 1, 4300, 4300)
+    q, t = pairs.pair(0)
+    M = ab.get_blosum62()
+    ref = O.align_pair("global", q, t, 11.0, 1.0, M, lean=True)
+    r = ab.SimpleGlobalAligner.from_seqs(q, t).perform_alignment(11, 1, M, want_matrices=False)
+    assert r.corner_score == ref["corner"]
+    assert (r.alignment.query == ref["q_aln"]).all() and (r.alignment.target == ref["t_aln"]).all()
