@@ -65,7 +65,7 @@ __device__ __forceinline__ unsigned long long wave_key(int v, uint32_t y, uint32
          (unsigned long long)(0xFFFFFu - x);
 }
 
-template <int R>
+template <int R, bool LOCAL>
 __global__ void __launch_bounds__(128) fill_wave_kernel(WaveArgs a) {
   extern __shared__ int wsm[];
   int *smat = wsm;                                    // V*V
@@ -74,6 +74,7 @@ __global__ void __launch_bounds__(128) fill_wave_kernel(WaveArgs a) {
   const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   uint8_t *sq = sq_all + warp * a.TW;
   constexpr uint32_t TH = 32 * R;
+  const uint32_t n = a.n, m = a.m;
 
   // tiles (i, j) with i + j == diag
   const uint32_t i_lo = a.diag >= a.tile_cols ? a.diag - a.tile_cols + 1 : 0;
@@ -82,82 +83,88 @@ __global__ void __launch_bounds__(128) fill_wave_kernel(WaveArgs a) {
   const bool have = ti <= i_hi;
   const uint32_t tj = have ? a.diag - ti : 0;
   const uint32_t y0 = ti * TH, x0 = tj * a.TW;
-  const uint32_t TWv = have ? min(a.TW, a.n - x0) : 0;
+  const uint32_t TWv = have ? min(a.TW, n - x0) : 0;
   if (have) for (uint32_t k = lane; k < TWv; k += 32) sq[k] = a.q[x0 + k];
   __syncthreads();
   if (!have) return;
 
   const uint32_t yl0 = y0 + lane * R;  // rows yl0+1 .. yl0+R (1-based)
-  int trow[R], h[R];
+  const int *srow[R];                  // smat row of each target symbol
+  int h[R];
+  bool rvalid[R];
 #pragma unroll
   for (int r = 0; r < R; ++r) {
     const uint32_t y = yl0 + r + 1;
-    trow[r] = (y <= a.m ? (int)a.t[y - 1] : 0) * a.V;
-    h[r] = y <= a.m ? a.colbuf[y] : 0;  // H[y][x0]
+    rvalid[r] = y <= m;
+    srow[r] = smat + (rvalid[r] ? (int)a.t[y - 1] : 0) * a.V;
+    h[r] = rvalid[r] ? a.colbuf[y] : 0;  // H[y][x0]
   }
-  int diag0 = (lane == 0) ? a.corner[ti] : a.colbuf[min(yl0, a.m)];  // H[yl0][x0]
-  int bottom = 0;
-  int rowchunk = 0;
+  int diag0 = (lane == 0) ? a.corner[ti] : a.colbuf[min(yl0, m)];  // H[yl0][x0]
+  int bottom = 0, rowchunk = 0;
   int best_v = 0;
   uint32_t best_y = 0, best_x = 0;
   const uint32_t steps = TWv + 31;
-  const bool glob = !a.local;
+  const int ext = a.ext;
+  // the one cell that pays `del` in global mode: (1, 1)  (simple/mod.rs:72,88-92)
+  const bool first_cell_here = !LOCAL && ti == 0 && tj == 0 && lane == 0;
   // byte address of this lane's rows inside the D word of (strip, column): 16 rows per word
-  uint8_t *dbase = a.Dbytes + ((uint64_t)(yl0 >> 4) * a.ncols) * 4 + ((yl0 & 15) >> 2);
+  uint8_t *dp = a.Dbytes + ((uint64_t)(yl0 >> 4) * a.ncols + x0) * 4 + ((yl0 & 15) >> 2) - 4 * (int64_t)lane;
+  int *rowout = a.rowbuf + x0 + 1 - (int)lane;
+  const bool store_d = yl0 < m;
+  int up_last = 0;
 
-  for (uint32_t s = 0; s < steps; ++s) {
+  for (uint32_t s = 0; s < steps; ++s, dp += 4) {
     if ((s & 31) == 0) {  // next 32 top-boundary values, one coalesced load
       const uint32_t xx = x0 + s + lane + 1;
-      rowchunk = xx <= a.n ? a.rowbuf[xx] : 0;
+      rowchunk = xx <= n ? a.rowbuf[xx] : 0;
     }
     int up = __shfl_up_sync(0xffffffffu, bottom, 1);
     const int top0 = __shfl_sync(0xffffffffu, rowchunk, s & 31);
     if (lane == 0) up = top0;
-    const int c = (int)s - (int)lane;
-    if (c >= 0 && c < (int)TWv) {
-      const uint32_t x = x0 + c + 1;
+    const uint32_t c = s - lane;  // wraps for s < lane
+    if (c < TWv) {
       const int qs = sq[c];
       int diag = diag0;
       diag0 = up;
+      up_last = up;
       int hup = up;
       uint32_t bits = 0;
 #pragma unroll
       for (int r = 0; r < R; ++r) {
-        const uint32_t y = yl0 + r + 1;
-        const int pen = (glob && x == 1 && y == 1) ? a.del : a.ext;  // simple/mod.rs:72,88-92
-        const int sc = smat[trow[r] + qs];
+        const int pen = (r == 0 && first_cell_here && c == 0) ? a.del : ext;
+        const int sc = srow[r][qs];
         const int top = hup - pen, left = h[r] - pen, dg = diag + sc;
         const int mx = max(max(top, left), dg);
-        uint32_t code;
-        if (!glob && mx == 0) code = DIR_BEGINNING;  // enums.rs:37
-        else if (mx == top) code = DIR_TOP;          // enums.rs:21/:39
-        else if (mx == left) code = DIR_LEFT;        // enums.rs:23/:41
-        else code = DIR_DIAGONAL;
+        uint32_t code = (mx == left) ? DIR_LEFT : DIR_DIAGONAL;  // enums.rs:23/:41
+        code = (mx == top) ? DIR_TOP : code;                     // enums.rs:21/:39
+        if (LOCAL) code = (mx == 0) ? DIR_BEGINNING : code;      // enums.rs:37
         bits |= code << (2 * r);
         diag = h[r];
         h[r] = mx;
         hup = mx;
-        if (!glob && y <= a.m && (mx > best_v || (mx == best_v && y < best_y))) {
-          best_v = mx; best_y = y; best_x = x;
+        if (LOCAL) {
+          if (mx >= best_v && rvalid[r]) {  // rare: first maximum in row-major order
+            const uint32_t y = yl0 + r + 1;
+            if (mx > best_v || y < best_y) { best_v = mx; best_y = y; best_x = x0 + c + 1; }
+          }
         }
-        if (y == a.m && x == a.n) *a.corner_out = mx;
       }
       bottom = hup;
-      if (yl0 < a.m) {
-        uint8_t *dp = dbase + (uint64_t)(x - 1) * 4;
+      if (store_d) {
         if (R == 4) *dp = (uint8_t)bits; else *reinterpret_cast<uint16_t *>(dp) = (uint16_t)bits;
       }
-      if (lane == 31) a.rowbuf[x] = hup;               // bottom row of the tile, for the tile below
-      if (lane == 0 && c == (int)TWv - 1) a.corner[ti] = up;  // H[y0][x0+TWv] for the tile to the right
+      if (lane == 31) rowout[s] = hup;  // bottom row of the tile, for the tile below
     }
   }
-  // right edge of the tile, for the tile to the right
+  if (lane == 0) a.corner[ti] = up_last;  // H[y0][x0+TWv] for the tile to the right
+  // right edge of the tile, for the tile to the right; H[m][n] from the last tile column
 #pragma unroll
   for (int r = 0; r < R; ++r) {
     const uint32_t y = yl0 + r + 1;
-    if (y <= a.m) a.colbuf[y] = h[r];
+    if (rvalid[r]) a.colbuf[y] = h[r];
+    if (y == m && x0 + TWv == n) *a.corner_out = h[r];
   }
-  if (!glob) {
+  if (LOCAL) {
     unsigned long long key = best_v > 0 ? wave_key(best_v, best_y, best_x) : 0ull;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {

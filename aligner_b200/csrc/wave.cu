@@ -23,7 +23,7 @@ bool wave_eligible(const alnr_batch_impl &B, uint32_t m, uint32_t n) {
 
 int wave_run_pair(alnr_batch_impl &B, const Chunk &c, const DLayout &dl, const FillOut &fo) {
   static const int R = std::getenv("ALNR_WAVE_R8") ? 8 : 4;
-  static const uint32_t TWenv = std::getenv("ALNR_WAVE_TW") ? (uint32_t)std::atoi(std::getenv("ALNR_WAVE_TW")) : 256;
+  static const uint32_t TWenv = std::getenv("ALNR_WAVE_TW") ? (uint32_t)std::atoi(std::getenv("ALNR_WAVE_TW")) : 128;
   const uint32_t TH = 32 * R, TW = std::max(32u, TWenv / 32 * 32);
   WaveArgs a;
   a.q = B.d_q.p + c.q0; a.t = B.d_t.p + c.t0;
@@ -46,8 +46,14 @@ int wave_run_pair(alnr_batch_impl &B, const Chunk &c, const DLayout &dl, const F
     a.diag = d;
     const uint32_t i_lo = d >= a.tile_cols ? d - a.tile_cols + 1 : 0, i_hi = std::min(d, a.tile_rows - 1);
     const uint32_t tiles = i_hi - i_lo + 1;
-    if (R == 8) fill_wave_kernel<8><<<(tiles + 3) / 4, 128, smem, B.stream>>>(a);
-    else fill_wave_kernel<4><<<(tiles + 3) / 4, 128, smem, B.stream>>>(a);
+    const unsigned grid = (tiles + 3) / 4;
+    if (a.local) {
+      if (R == 8) fill_wave_kernel<8, true><<<grid, 128, smem, B.stream>>>(a);
+      else fill_wave_kernel<4, true><<<grid, 128, smem, B.stream>>>(a);
+    } else {
+      if (R == 8) fill_wave_kernel<8, false><<<grid, 128, smem, B.stream>>>(a);
+      else fill_wave_kernel<4, false><<<grid, 128, smem, B.stream>>>(a);
+    }
     ALNR_LAUNCHED();
   }
   wave_finish_kernel<<<1, 1, 0, B.stream>>>(a, fo, c.wave_pair);

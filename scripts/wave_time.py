@@ -1,0 +1,11 @@
+import sys, os, time
+sys.path.insert(0, "/root/repo")
+import numpy as np, aligner_b200 as ab
+from aligner_b200 import _native as N, workloads as W
+q, t = W.dna_long_pair(100000, seed=4)
+pairs = ab.PackedPairs.from_lists([q], [t])
+db = ab.DeviceBatch(N.GLOBAL, pairs, ab.dna_matrix(), 8, 8)
+db.run_timed(1)
+for _ in range(2):
+    ms, fill = db.run_timed(1)
+    print("total ms %.2f fill ms %.2f -> fill GCUPS %.1f" % (ms, fill, len(q)*len(t)/fill/1e6))
