@@ -4,12 +4,15 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <numeric>
+#include <type_traits>
 
 #include "kernels_exact.cuh"
 #include "kernels_trace.cuh"
 #include "strip_launch.h"
+#include "warp_args.h"
 #include "wave_launch.h"
 
 namespace alnr {
@@ -118,9 +121,8 @@ int alnr_batch_impl::plan_chunks(const uint64_t *q_off, const uint64_t *t_off) {
     dims(s, m, n);
     if (!uniform) n = nsuf[s];
     m = std::max(m, 1u); n = std::max(n, 1u);
-    const uint32_t rpw = d_rows_per_word(*this, m);
-    const uint64_t nstrips = (m + rpw - 1) / rpw;
-    const uint64_t per_group = (nstrips * ((n + 3) / 4 * 4) * 4 + ((uint64_t)m + 1) * num_sz + (uint64_t)(n + 1) * 4) * 32;
+    const DLayout pl = layout_dims(m, n, false);
+    const uint64_t per_group = pl.words_for(32) * 4 + (((uint64_t)std::max(m, n) + 1) * num_sz + (uint64_t)(n + 1) * 4) * 32;
     uint64_t groups = std::max<uint64_t>(budget / per_group, 1);
     uint64_t c = std::min<uint64_t>(groups * 32, count - s);
     if (c < count - s) c = std::max<uint64_t>(c / 64 * 64, 32);  // keep duo-kernel warps whole
@@ -142,10 +144,22 @@ int alnr_batch_impl::plan_chunks(const uint64_t *q_off, const uint64_t *t_off) {
   return ALNR_OK;
 }
 
-DLayout alnr_batch_impl::layout_for(const Chunk &c) const {
-  if (c.wave) return DLayout::make(16, c.m_max, c.n_max, true, 0);
-  return DLayout::make(d_rows_per_word(*this, c.m_max), c.m_max, c.n_max, numeric == ALNR_NUM_I16X2);
+// One warp per pair pays off once a lane has real work (>= 24 target rows) or the batch is too
+// small to fill the GPU with one thread per pair; tiny pairs in huge batches stay per-thread.
+bool alnr_batch_impl::use_warp(uint32_t m) const {
+  if (numeric == ALNR_NUM_I16X2) return false;
+  static const bool off = getenv("ALNR_NO_WARP_KERNEL") != nullptr;
+  if (off) return false;
+  return want_matrices || m >= 24 || count <= 4096;
 }
+
+DLayout alnr_batch_impl::layout_dims(uint32_t m, uint32_t n, bool wave) const {
+  if (wave) return DLayout::make(16, m, n, true, 0);
+  if (use_warp(m)) return DLayout::make_skewed(want_matrices ? 8 : warp_pick_rows(m), m, n);
+  return DLayout::make(d_rows_per_word(*this, m), m, n, numeric == ALNR_NUM_I16X2);
+}
+
+DLayout alnr_batch_impl::layout_for(const Chunk &c) const { return layout_dims(c.m_max, c.n_max, c.wave); }
 
 int alnr_batch_impl::init(const alnr_params *p, const alnr_batch *b, bool want_mats) {
   if (!p || !b || !p->matrix) return ALNR_INVALID_ARGUMENT;
@@ -236,6 +250,10 @@ int alnr_batch_impl::init(const alnr_params *p, const alnr_batch *b, bool want_m
   if (numeric == ALNR_NUM_I16X2) {
     st = strip_prepare(*this);
     if (st) return st;
+  } else if (mode == ALNR_LOCAL && del != ext) {
+    uint32_t cmax = 0;
+    for (const Chunk &c : chunks) cmax = std::max(cmax, c.count);
+    ALNR_CUDA(d_wz.alloc(8 + (uint64_t)cmax * (1 + 2ull * ((n_max + 31) / 32))));
   }
   return ALNR_OK;
 }
@@ -249,6 +267,38 @@ static int launch_exact(alnr_batch_impl &B, const Chunk &c, const ChunkView &cv,
   a.H_out = B.d_Hout.p; a.D_out = B.d_Dout.p;
   const uint32_t blocks = (c.count + 127) / 128;
   fill_exact_kernel<T><<<blocks, 128, (size_t)B.V * B.V * sizeof(T), B.stream>>>(a);
+  ALNR_LAUNCHED();
+  return ALNR_OK;
+}
+
+template <typename T>
+static int launch_warp(alnr_batch_impl &B, const Chunk &c, const ChunkView &cv, const DLayout &dl,
+                       const FillOut &fo, T *hcol, const T *mat) {
+  WarpArgs<T> a;
+  a.cv = cv; a.V = B.V; a.del = (T)B.del; a.ext = (T)B.ext;
+  const bool local = B.mode == ALNR_LOCAL;
+  a.stateful = local && B.del != B.ext;
+  a.matrix = mat; a.item_matrices = nullptr;
+  a.D = B.d_D.p; a.dl = dl; a.fo = fo;
+  a.rowbuf = hcol; a.rowbuf_stride = c.n_max + 1;
+  a.nzw = (B.n_max + 31) / 32;
+  uint32_t *counters = B.d_wz.p;
+  a.fail_count = counters; a.fail_list = counters ? counters + 8 : nullptr;
+  a.zbuf = counters ? counters + 8 + c.count : nullptr;
+  a.H_out = B.d_Hout.p; a.D_out = B.d_Dout.p;
+  const bool mats = B.want_matrices && B.count == 1;
+  if (a.stateful) ALNR_CUDA(cudaMemsetAsync(counters, 0, 8 * sizeof(uint32_t), B.stream));
+  int st;
+  if constexpr (std::is_same<T, int>::value) st = warp_launch_i32(B.stream, a, local, mats);
+  else st = warp_launch_f64(B.stream, a, local, mats);
+  if (st || !a.stateful) return st;
+  // pairs whose speculation did not settle: exact column-major kernel over the fail list
+  ExactArgs<T> e;
+  e.cv = cv; e.mode = B.mode; e.V = B.V; e.del = (T)B.del; e.ext = (T)B.ext;
+  e.matrix = mat; e.hcol = hcol; e.hrows = c.m_max + 1; e.D = B.d_D.p; e.dl = dl; e.fo = fo;
+  e.H_out = mats ? B.d_Hout.p : nullptr; e.D_out = mats ? B.d_Dout.p : nullptr;
+  e.list = a.fail_list; e.list_count = a.fail_count;
+  fill_exact_kernel<T><<<(c.count + 127) / 128, 128, (size_t)B.V * B.V * sizeof(T), B.stream>>>(e);
   ALNR_LAUNCHED();
   return ALNR_OK;
 }
@@ -291,6 +341,8 @@ int alnr_batch_impl::run_chunk(size_t ci) {
   int st = fill_mark(false);
   if (st) return st;
   if (c.wave) st = wave_run_pair(*this, c, dl, fo);
+  else if (numeric == ALNR_NUM_F64 && dl.skewed) st = launch_warp<double>(*this, c, cv, dl, fo, d_hcol_d.p, d_matd.p);
+  else if (numeric == ALNR_NUM_I32 && dl.skewed) st = launch_warp<int>(*this, c, cv, dl, fo, d_hcol_i.p, d_mati.p);
   else if (numeric == ALNR_NUM_F64) st = launch_exact<double>(*this, c, cv, dl, fo, d_hcol_d.p, d_matd.p);
   else if (numeric == ALNR_NUM_I32) st = launch_exact<int>(*this, c, cv, dl, fo, d_hcol_i.p, d_mati.p);
   else st = strip_run_chunk(*this, c, cv, dl, fo);

@@ -40,6 +40,7 @@ struct alnr_batch_impl {
   DevBuf<double> d_f, d_corner, d_matd, d_Hout, d_hcol_d;
   DevBuf<int> d_mati, d_hcol_i;
   DevBuf<uint32_t> d_pack;      // packed sequences for the strip kernel
+  DevBuf<uint32_t> d_wz;        // warp kernel: [8 counters][fail list][z bits 2*nzw per slot]
   uint64_t rerun_total = 0;
   bool profile = false;                 // record events around every fill launch
   std::vector<cudaEvent_t> fill_events; // pairs (begin, end), filled when profile is set
@@ -59,6 +60,8 @@ struct alnr_batch_impl {
   int download(alnr_batch_out *out);
   int classify();
   DLayout layout_for(const Chunk &c) const;
+  DLayout layout_dims(uint32_t m, uint32_t n, bool wave) const;
+  bool use_warp(uint32_t m) const;  // warp-per-pair kernel instead of one pair per thread
   int plan_chunks(const uint64_t *q_off, const uint64_t *t_off);
 };
 

@@ -33,6 +33,11 @@ struct DLayout {
   // Bit format inside a word.  0: code of row r at bits [2r, 2r+1].  1 ("planes", strip
   // kernel): bit r = code bit 0, bit 16+r = code bit 1 — the kernel builds whole bit-planes.
   uint32_t planes;
+  // Address map 3, "skewed" (warp-per-pair kernel, kernels_warp.cuh): strip = band * 32 + lane,
+  // lane l works l columns behind lane 0, so the words a warp emits in one step are
+  //   slot * nstrips * (ncols + 31) + ((band * (ncols + 31) + (x-1) + lane) * 32 + lane)
+  // -> one 128-byte line per step.  rows_per_word = rows per lane.
+  uint32_t skewed;
   __host__ __device__ inline uint32_t put(uint32_t code, uint32_t r) const {
     return planes ? (((code & 1u) << r) | ((code >> 1) << (16 + r))) : (code << (2 * r));
   }
@@ -40,11 +45,16 @@ struct DLayout {
     return planes ? (((w >> r) & 1u) | (((w >> (16 + r)) & 1u) << 1)) : ((w >> (2 * r)) & 3u);
   }
   __host__ __device__ inline uint64_t word(uint32_t slot, uint32_t strip, uint32_t xm1) const {
+    if (skewed) {
+      const uint32_t band = strip >> 5, lane = strip & 31;
+      return (uint64_t)slot * nstrips * (ncols + 31) + (((uint64_t)band * (ncols + 31) + xm1 + lane) * 32ull + lane);
+    }
     if (contiguous) return ((uint64_t)slot * nstrips + strip) * ncols + xm1;
     uint32_t group = slot >> 5, lane = slot & 31;
     return (((uint64_t)group * nstrips + strip) * ncols + xm1) * 32ull + lane;
   }
   __host__ __device__ inline uint64_t words_for(uint64_t slots) const {
+    if (skewed) return slots * (uint64_t)nstrips * (ncols + 31);
     if (contiguous) return slots * (uint64_t)nstrips * ncols + 4;
     return ((slots + 31) / 32) * (uint64_t)nstrips * ncols * 32ull;
   }
@@ -56,6 +66,18 @@ struct DLayout {
     d.ncols = contig ? (n_max + 3) / 4 * 4 : n_max;
     d.contiguous = contig ? 1u : 0u;
     d.planes = planes_opt >= 0 ? (uint32_t)planes_opt : (contig ? 1u : 0u);
+    d.skewed = 0;
+    return d;
+  }
+  // warp-per-pair layout: R rows per lane, bands of 32 * R rows
+  static inline DLayout make_skewed(uint32_t R, uint32_t m_max, uint32_t n_max) {
+    DLayout d;
+    d.rows_per_word = R;
+    d.nstrips = (m_max + 32 * R - 1) / (32 * R) * 32;
+    d.ncols = n_max;
+    d.contiguous = 0;
+    d.planes = 0;
+    d.skewed = 1;
     return d;
   }
 };

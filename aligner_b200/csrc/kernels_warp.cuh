@@ -1,0 +1,247 @@
+// kernels_warp.cuh — intra-pair fill with ONE WARP PER PAIR (or per (pair, matrix) item).
+//
+// Serves everything between the short-read strip kernel and the 10^5-scale wavefront kernel:
+// single-pair calls (BASELINE configs 1, 2 and the config-4 file), protein / ragged batches in
+// exact INT32, and the FP64 heuristic matrix search (config 5), where every item has its own
+// non-integral matrix (the warp stages it in shared memory; one thread per item would have to
+// look 4.6 KB tables up in L2).
+//
+// Lane l owns R consecutive target rows in registers and works l columns behind lane l-1, so the
+// bottom cell of lane l-1 arrives by one __shfl_up per column (skewed systolic sweep, 31 bubble
+// steps per band).  Targets longer than 32*R rows are cut into bands; a band's bottom row
+// passes to the next through an L2-resident row buffer.  The words of 2-bit directions a warp
+// emits in one step are consecutive in the "skewed" D layout (common.cuh): 128 bytes per store.
+//
+// The recurrence is the reference's, literally (simple/mod.rs:74-97 global, :187-210 local;
+// enums.rs:18-46): top/left pay the carried `penalty`, ties resolve Top > Left > Diagonal with
+// |max - cand| < EPSILON, Beginning iff max == 0, penalty <- ext unless the cell just computed
+// is Beginning.  Inside a column the penalty follows the cell above, across lanes it follows the
+// value handed up by the shuffle (Beginning <=> value == 0 for interior cells).  The only
+// cross-column dependency — penalty(1, x) = del iff H[m][x-1] == 0 (local mode, del != ext) — is
+// speculated exactly like the strip kernel: assume a bit vector z, observe the true bits on
+// row m, repeat the pass with the observed bits until they agree (each pass extends the verified
+// prefix); pairs that do not settle within kWarpPasses go to the exact column-major kernel.
+#pragma once
+#include "common.cuh"
+#include "kernels_exact.cuh"
+#include "warp_args.h"
+
+namespace alnr {
+
+__device__ __forceinline__ int shfl_up_t(int v) { return __shfl_up_sync(0xffffffffu, v, 1); }
+__device__ __forceinline__ double shfl_up_t(double v) { return __shfl_up_sync(0xffffffffu, v, 1); }
+
+// grid: ceil(count / kWarpsPerBlock); smem: V*V*sizeof(T) * (item_matrices ? kWarpsPerBlock : 1)
+template <typename T, int R, bool LOCAL, bool MATS>
+__global__ void __launch_bounds__(kWarpsPerBlock * 32) fill_warp_kernel(WarpArgs<T> a) {
+  extern __shared__ unsigned char smem_raw[];
+  T *smem = reinterpret_cast<T *>(smem_raw);
+  const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int V = a.V, VV = V * V;
+  const uint32_t slot = blockIdx.x * kWarpsPerBlock + warp;
+  bool have = slot < a.cv.count;
+  uint32_t pair = 0;
+  if (have) {
+    pair = a.cv.order ? a.cv.order[a.cv.first + slot] : a.cv.first + slot;
+    if (a.fo.status[pair] != 0) have = false;  // rejected by validation
+  }
+  const T *smat;
+  if (a.item_matrices) {
+    T *mine = smem + (size_t)warp * VV;
+    if (have) for (int i = lane; i < VV; i += 32) mine[i] = a.item_matrices[(size_t)pair * VV + i];
+    __syncwarp();
+    smat = mine;
+  } else {
+    for (int i = threadIdx.x; i < VV; i += blockDim.x) smem[i] = a.matrix[i];
+    __syncthreads();
+    smat = smem;
+  }
+  if (!have) return;
+
+  const uint32_t sp = a.cv.seq(pair);
+  const uint8_t *q = a.cv.q + a.cv.q_off[sp];
+  const uint8_t *t = a.cv.t + a.cv.t_off[sp];
+  const uint32_t n = (uint32_t)(a.cv.q_off[sp + 1] - a.cv.q_off[sp]);
+  const uint32_t m = (uint32_t)(a.cv.t_off[sp + 1] - a.cv.t_off[sp]);
+  constexpr uint32_t BH = 32 * R;  // rows per band
+  const uint32_t nbands = (m + BH - 1) / BH;
+  const uint32_t m_lane = ((m - 1) % BH) / R, m_r = (m - 1) % R;  // where row m lives (last band)
+  const T del = a.del, ext = a.ext;
+  const bool stateful = LOCAL && a.stateful;
+  T *rowbuf = a.rowbuf + (size_t)slot * a.rowbuf_stride;
+  uint32_t *Dslot = a.D + (uint64_t)slot * a.dl.nstrips * (a.dl.ncols + 31);
+  const uint64_t band_words = (uint64_t)(a.dl.ncols + 31) * 32;
+  const size_t W = (size_t)n + 1;
+  uint32_t *zb0 = stateful ? a.zbuf + (size_t)slot * 2 * a.nzw : nullptr;
+  const uint32_t *zin = nullptr;
+  uint32_t *zout = zb0;
+
+  // row 0 and column 0 of the optional full matrices (simple/mod.rs:59-70; zeros/Beginning local)
+  if (MATS) {
+    for (uint32_t x = lane; x <= n; x += 32) {
+      T v = T(0);
+      if (!LOCAL && x > 0) v = (x == n) ? -(T(n) + T(1)) * del : -T(x) * del;
+      a.H_out[x] = (double)v;
+      a.D_out[x] = LOCAL ? DIR_BEGINNING : (x == 0 ? DIR_BEGINNING : DIR_LEFT);
+    }
+    for (uint32_t y = 1 + lane; y <= m; y += 32) {
+      T v = T(0);
+      if (!LOCAL) v = (y == m) ? -(T(m) + T(1)) * del : -T(y) * del;
+      a.H_out[y * W] = (double)v;
+      a.D_out[y * W] = LOCAL ? DIR_BEGINNING : DIR_TOP;
+    }
+  }
+
+  T best = T(0), corner = T(0);
+  uint32_t by = 0, bx = 0;
+  bool settled = true;
+  for (int pass = 0;; ++pass) {
+    best = T(0); by = 0; bx = 0;
+    bool mism = false;
+    for (uint32_t band = 0; band < nbands; ++band) {
+      const uint32_t yb = band * BH + lane * R;  // this lane's rows: yb+1 .. yb+R (1-based)
+      const bool last_band = band + 1 == nbands;
+      uint32_t toff[R];
+      T h[R];
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        const uint32_t y = yb + r + 1;
+        const bool valid = y <= m;
+        toff[r] = valid ? (uint32_t)t[y - 1] * V : 0u;
+        T v = T(0);
+        if (!LOCAL && valid) v = (y == m) ? -(T(m) + T(1)) * del : -T(y) * del;  // :64-67, :70
+        h[r] = v;
+      }
+      T dprev = (LOCAL || yb == 0) ? T(0) : -T(yb) * del;  // H[yb][0]
+      T bottom = T(0);
+      uint32_t zw = 0, zacc = 0;
+      uint32_t qn = q[0];
+      uint32_t *dp = Dslot + band * band_words + lane;
+      const bool store_d = yb < m;
+      const bool obs_lane = last_band && lane == m_lane;
+      const bool top_lane = band == 0 && lane == 0;
+      const uint32_t steps = n + 31;
+      for (uint32_t s = 0; s < steps; ++s, dp += 32) {
+        T up = shfl_up_t(bottom);
+        const uint32_t c = s - lane;  // 0-based column; wraps for s < lane
+        if (c < n) {
+          const uint32_t x = c + 1;
+          if (lane == 0) {
+            if (band == 0) { up = T(0); if (!LOCAL) up = (x == n) ? -(T(n) + T(1)) * del : -T(x) * del; }  // :59-62, :69
+            else up = rowbuf[x];
+          }
+          const uint32_t qs = qn;
+          if (x < n) qn = q[x];
+          T diag = dprev;
+          dprev = up;
+          T hup = up;
+          // penalty of the lane's first row (simple/mod.rs:72,88-92 / :185,201-205)
+          T pen = ext;
+          if (!LOCAL) {
+            if (top_lane && c == 0) pen = del;           // the very first cell pays del
+          } else if (top_lane) {
+            bool z = c == 0;                              // initial penalty = del
+            if (stateful && c > 0) {
+              if (((c - 1) & 31) == 0) zw = zin ? zin[(c - 1) >> 5] : 0u;
+              z = (zw >> ((c - 1) & 31)) & 1u;            // assumed: H[m][x-1] == 0
+            }
+            pen = z ? del : ext;
+          } else {
+            pen = Num<T>::is_zero(up) ? del : ext;        // cell above is Beginning iff it is 0
+          }
+          uint32_t bits = 0;
+#pragma unroll
+          for (int r = 0; r < R; ++r) {
+            const T sc = smat[toff[r] + qs];
+            const T top = nsub(hup, pen), lft = nsub(h[r], pen), dg = nadd(diag, sc);
+            const T mx = Num<T>::max3(top, lft, dg);
+            uint32_t d = Num<T>::same(mx, lft) ? DIR_LEFT : DIR_DIAGONAL;  // enums.rs:23/:41
+            d = Num<T>::same(mx, top) ? DIR_TOP : d;                       // enums.rs:21/:39
+            if (LOCAL) {
+              const bool zero = Num<T>::is_zero(mx);                       // enums.rs:37
+              d = zero ? DIR_BEGINNING : d;
+              pen = zero ? del : ext;
+            } else {
+              pen = ext;
+            }
+            bits |= d << (2 * r);
+            diag = h[r];
+            h[r] = mx;
+            hup = mx;
+            if (LOCAL) {
+              if (mx >= best) {  // rare: first maximum in row-major order (simple/mod.rs:212)
+                const uint32_t y = yb + r + 1;
+                if (y <= m && (mx > best || (mx == best && y < by))) { best = mx; by = y; bx = x; }
+              }
+            }
+            if (MATS) {
+              const uint32_t y = yb + r + 1;
+              if (y <= m) { a.H_out[y * W + x] = (double)mx; a.D_out[y * W + x] = (uint8_t)d; }
+            }
+          }
+          bottom = hup;
+          if (store_d) *dp = bits;
+          if (lane == 31 && !last_band) rowbuf[x] = hup;
+          if (obs_lane && (stateful || x == n)) {
+            T hm = h[0];
+#pragma unroll
+            for (int r = 1; r < R; ++r) if ((uint32_t)r == m_r) hm = h[r];
+            if (x == n) corner = hm;
+            if (stateful) {
+              // observe z[x-1] = (H[m][x] == 0): it sets the penalty of cell (1, x+1)
+              zacc |= (Num<T>::is_zero(hm) ? 1u : 0u) << (c & 31);
+              if ((c & 31) == 31 || x == n) {
+                const uint32_t w = c >> 5;
+                const uint32_t assumed = zin ? zin[w] : 0u;
+                // bits at column index >= n-1 never feed a penalty (there is no column n+1)
+                const uint32_t nb = (n - 1) - (w << 5);
+                const uint32_t vmask = (n - 1 <= (w << 5)) ? 0u : (nb >= 32 ? 0xffffffffu : ((1u << nb) - 1u));
+                if ((zacc ^ assumed) & vmask) mism = true;
+                zout[w] = zacc;
+                zacc = 0;
+              }
+            }
+          }
+        }
+      }
+      __syncwarp();  // rowbuf / z words written by one lane are read by another
+    }
+    if (!stateful) break;
+    if (!__any_sync(0xffffffffu, mism)) break;
+    if (pass + 1 == kWarpPasses) { settled = false; break; }
+    zin = zout;
+    zout = (zout == zb0) ? zb0 + a.nzw : zb0;
+  }
+  if (!settled) {
+    if (lane == 0) a.fail_list[atomicAdd(a.fail_count, 1u)] = slot;
+    return;
+  }
+
+  // ---- per-pair results -------------------------------------------------------------------
+  corner = __shfl_sync(0xffffffffu, corner, m_lane);
+  if (LOCAL) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const T ov = __shfl_xor_sync(0xffffffffu, best, o);
+      const uint32_t oy = __shfl_xor_sync(0xffffffffu, by, o), ox = __shfl_xor_sync(0xffffffffu, bx, o);
+      // larger value, then smaller y, then smaller x; (0, 0) = "no positive cell" loses to any cell
+      const bool take = ov > best || (ov == best && oy != 0 && (by == 0 || oy < by || (oy == by && ox < bx)));
+      if (take) { best = ov; by = oy; bx = ox; }
+    }
+  }
+  if (lane == 0) {
+    a.fo.corner[pair] = (double)corner;
+    if (LOCAL) {
+      a.fo.f[pair] = (double)best;  // simple/mod.rs:247
+      a.fo.start[2 * (size_t)pair] = by;
+      a.fo.start[2 * (size_t)pair + 1] = bx;
+      if (by == 0 || bx == 0) a.fo.status[pair] = 11;  // ALNR_NO_POSITIVE_CELL (simple/mod.rs:214)
+    } else {
+      a.fo.f[pair] = 0.0;  // simple/mod.rs:139
+      a.fo.start[2 * (size_t)pair] = m;
+      a.fo.start[2 * (size_t)pair + 1] = n;
+    }
+  }
+}
+
+}  // namespace alnr

@@ -1,0 +1,45 @@
+// warp_args.h — argument block and host entry points of the warp-per-pair fill kernel
+// (kernels_warp.cuh; instantiated in warp_i32.cu and warp_f64.cu).
+#pragma once
+#include "common.cuh"
+
+namespace alnr {
+
+constexpr int kWarpsPerBlock = 4;
+constexpr int kWarpPasses = 6;
+
+template <typename T>
+struct WarpArgs {
+  ChunkView cv;
+  int V;
+  T del, ext;
+  int stateful;            // local mode with del != ext
+  const T *matrix;         // V*V shared by all items (device) ...
+  const T *item_matrices;  // ... or one V*V matrix per result index (heuristic search)
+  uint32_t *D;
+  DLayout dl;              // skewed, rows_per_word == R
+  FillOut fo;
+  T *rowbuf;               // band boundary rows, [slot * rowbuf_stride + x]
+  uint32_t rowbuf_stride;
+  uint32_t *zbuf;          // [slot][2][nzw] assumed / observed bits (stateful only)
+  uint32_t nzw;
+  uint32_t *fail_list;     // slots whose speculation did not settle
+  uint32_t *fail_count;
+  double *H_out;           // optional, single-pair calls: (m+1)*(n+1) row-major
+  uint8_t *D_out;
+};
+
+// Rows per lane for targets of up to m_max rows: the smallest even R <= 16 with 32 * R >= m_max
+// (one band), else 16 (several bands).
+inline uint32_t warp_pick_rows(uint32_t m_max) {
+  uint32_t r = (m_max + 31) / 32;
+  r = (r + 1) / 2 * 2;
+  return r < 2 ? 2 : (r > 16 ? 16 : r);
+}
+
+// Enqueue the warp-per-pair fill of a.cv.count slots on `stream`; a.dl.rows_per_word selects R.
+// mats: also write a.H_out / a.D_out (single pair; R must be 8).
+int warp_launch_i32(cudaStream_t stream, const WarpArgs<int> &a, bool local, bool mats);
+int warp_launch_f64(cudaStream_t stream, const WarpArgs<double> &a, bool local, bool mats);
+
+}  // namespace alnr

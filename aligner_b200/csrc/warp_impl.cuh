@@ -1,0 +1,36 @@
+// warp_impl.cuh — launcher template shared by warp_i32.cu / warp_f64.cu.
+#pragma once
+#include "host_util.h"
+#include "kernels_warp.cuh"
+
+namespace alnr {
+
+template <typename T, int R, bool LOCAL, bool MATS>
+static int warp_launch_one(cudaStream_t stream, const WarpArgs<T> &a) {
+  const unsigned blocks = (a.cv.count + kWarpsPerBlock - 1) / kWarpsPerBlock;
+  if (blocks == 0) return ALNR_OK;
+  const size_t smem = (size_t)a.V * a.V * sizeof(T) * (a.item_matrices ? kWarpsPerBlock : 1);
+  fill_warp_kernel<T, R, LOCAL, MATS><<<blocks, kWarpsPerBlock * 32, smem, stream>>>(a);
+  ALNR_LAUNCHED();
+  return ALNR_OK;
+}
+
+template <typename T>
+static int warp_launch_any(cudaStream_t stream, const WarpArgs<T> &a, bool local, bool mats) {
+  if (mats) {
+    if (a.dl.rows_per_word != 8) return ALNR_INVALID_ARGUMENT;
+    return local ? warp_launch_one<T, 8, true, true>(stream, a) : warp_launch_one<T, 8, false, true>(stream, a);
+  }
+#define ALNR_WARP_CASE(RR)                                                        \
+  case RR:                                                                        \
+    return local ? warp_launch_one<T, RR, true, false>(stream, a)                 \
+                 : warp_launch_one<T, RR, false, false>(stream, a);
+  switch (a.dl.rows_per_word) {
+    ALNR_WARP_CASE(2) ALNR_WARP_CASE(4) ALNR_WARP_CASE(6) ALNR_WARP_CASE(8)
+    ALNR_WARP_CASE(10) ALNR_WARP_CASE(12) ALNR_WARP_CASE(14) ALNR_WARP_CASE(16)
+    default: return ALNR_INVALID_ARGUMENT;
+  }
+#undef ALNR_WARP_CASE
+}
+
+}  // namespace alnr
