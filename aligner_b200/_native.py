@@ -83,6 +83,7 @@ SIGNATURES = {
     "alnr_matrix_search": (C.c_int, [C.POINTER(Params), C.POINTER(Batch), f64p, C.c_uint32, C.c_double,
                                      C.c_double, f64p, f64p, u32p, f64p, f64p, i32p]),
     "alnr_measure_int_peak": (C.c_int, [C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
+    "alnr_measure_fp64_peak": (C.c_int, [C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "alnr_host_alloc": (C.c_void_p, [C.c_uint64]),
     "alnr_host_free": (None, [C.c_void_p]),
     "alnr_release_cached_memory": (None, []),

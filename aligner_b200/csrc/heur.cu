@@ -16,6 +16,7 @@
 #include "kernels_exact.cuh"
 #include "kernels_trace.cuh"
 #include "transform.cuh"
+#include "warp_args.h"
 
 namespace alnr {
 
@@ -115,8 +116,12 @@ extern "C" int alnr_heuristic_batch(const alnr_params *p, const alnr_batch *b,
     m_max = std::max<uint32_t>(m_max, (uint32_t)(b->t_off[i + 1] - b->t_off[i]));
   }
   const uint64_t q_total = b->q_off[P], t_total = b->t_off[P];
-  const DLayout dl0 = DLayout::make(16, std::max(m_max, 1u), std::max(n_max, 1u), false);
-  const uint64_t per_item = (uint64_t)dl0.nstrips * dl0.ncols * 4 + 8ull * (m_max + 1) + 3ull * VV * 8 + 128;
+  // one warp per item (kernels_warp.cuh): the item's own matrix sits in shared memory
+  const DLayout dl0 = DLayout::make_skewed(warp_pick_rows(std::max(m_max, 1u)), std::max(m_max, 1u), std::max(n_max, 1u));
+  const bool stateful = p->del != p->ext;
+  const uint32_t nzw = (n_max + 31) / 32;
+  const uint64_t row_words = (uint64_t)std::max(m_max, n_max) + 1;  // band rows / exact-kernel column
+  const uint64_t per_item = dl0.words_for(1) * 4 + 8ull * row_words + 3ull * VV * 8 + 128 + (stateful ? 8ull * nzw + 4 : 0);
   size_t free_b = 0, total_b = 0;
   ALNR_CUDA(cudaMemGetInfo(&free_b, &total_b));
   const uint64_t budget = std::max<uint64_t>(std::min<uint64_t>(free_b / 3, 16ull << 30), 64ull << 20);
@@ -129,7 +134,7 @@ extern "C" int alnr_heuristic_batch(const alnr_params *p, const alnr_batch *b,
 
   DevBuf<uint8_t> d_q, d_t;
   DevBuf<uint64_t> d_qoff, d_toff, d_cc, d_co;
-  DevBuf<uint32_t> d_pi, d_mi, d_lists, d_cnt, d_start, d_D;
+  DevBuf<uint32_t> d_pi, d_mi, d_lists, d_cnt, d_start, d_D, d_wz;
   DevBuf<int32_t> d_pst, d_st, d_passes;
   DevBuf<int> d_flag;
   DevBuf<double> d_mats, d_freqs, d_T, d_L, d_F, d_maxf, d_fcur, d_fout, d_corner, d_hcol;
@@ -143,7 +148,8 @@ extern "C" int alnr_heuristic_batch(const alnr_params *p, const alnr_batch *b,
   ALNR_CUDA(d_st.alloc(chunk)); ALNR_CUDA(d_passes.alloc(chunk));
   ALNR_CUDA(d_T.alloc(chunk * VV)); ALNR_CUDA(d_L.alloc(chunk * VV)); ALNR_CUDA(d_F.alloc(chunk * VV));
   ALNR_CUDA(d_maxf.alloc(chunk)); ALNR_CUDA(d_fcur.alloc(chunk)); ALNR_CUDA(d_fout.alloc(chunk));
-  ALNR_CUDA(d_corner.alloc(chunk)); ALNR_CUDA(d_hcol.alloc((chunk + 31) / 32 * 32 * ((uint64_t)m_max + 1)));
+  ALNR_CUDA(d_corner.alloc(chunk)); ALNR_CUDA(d_hcol.alloc((chunk + 31) / 32 * 32 * row_words));
+  if (stateful) ALNR_CUDA(d_wz.alloc(8 + chunk * (1 + 2ull * nzw)));
   ALNR_CUDA(d_cc.alloc(chunk * 4)); ALNR_CUDA(d_co.alloc(chunk * 4));
 
   auto h2d = [&](void *dst, const void *src, size_t bytes) {
@@ -189,11 +195,23 @@ extern "C" int alnr_heuristic_batch(const alnr_params *p, const alnr_batch *b,
       ChunkView cv{d_q.p, d_t.p, d_qoff.p, d_toff.p, cur, 0, n_active};
       cv.seqmap = d_pi.p;
       FillOut fo{d_fcur.p, d_corner.p, d_start.p, d_st.p};
-      ExactArgs<double> e;
-      e.cv = cv; e.mode = ALNR_LOCAL; e.V = V; e.del = p->del; e.ext = p->ext;
-      e.matrix = nullptr; e.hcol = d_hcol.p; e.hrows = m_max + 1; e.D = d_D.p; e.dl = dl0; e.fo = fo;
-      e.H_out = nullptr; e.D_out = nullptr; e.item_matrices = d_T.p;
-      fill_exact_kernel<double><<<(n_active + 127) / 128, 128, (size_t)VV * 8, stream>>>(e); ALNR_LAUNCHED();
+      WarpArgs<double> w;
+      w.cv = cv; w.V = V; w.del = p->del; w.ext = p->ext; w.stateful = stateful;
+      w.matrix = nullptr; w.item_matrices = d_T.p; w.D = d_D.p; w.dl = dl0; w.fo = fo;
+      w.rowbuf = d_hcol.p; w.rowbuf_stride = n_max + 1;
+      w.nzw = nzw; w.fail_count = d_wz.p; w.fail_list = stateful ? d_wz.p + 8 : nullptr;
+      w.zbuf = stateful ? d_wz.p + 8 + chunk : nullptr;
+      w.H_out = nullptr; w.D_out = nullptr;
+      if (stateful) ALNR_CUDA(cudaMemsetAsync(d_wz.p, 0, 8 * sizeof(uint32_t), stream));
+      { int wst = warp_launch_f64(stream, w, true, false); if (wst) return wst; }
+      if (stateful) {  // items whose speculation did not settle: exact column-major kernel
+        ExactArgs<double> e;
+        e.cv = cv; e.mode = ALNR_LOCAL; e.V = V; e.del = p->del; e.ext = p->ext;
+        e.matrix = nullptr; e.hcol = d_hcol.p; e.hrows = m_max + 1; e.D = d_D.p; e.dl = dl0; e.fo = fo;
+        e.H_out = nullptr; e.D_out = nullptr; e.item_matrices = d_T.p;
+        e.list = w.fail_list; e.list_count = w.fail_count;
+        fill_exact_kernel<double><<<(n_active + 127) / 128, 128, (size_t)VV * 8, stream>>>(e); ALNR_LAUNCHED();
+      }
       TraceOut to{d_cc.p, nullptr, nullptr, nullptr, nullptr, d_F.p};
       TraceArgs ta{cv, ALNR_LOCAL, V, d_D.p, dl0, fo, to};
       traceback_kernel<<<(n_active + 127) / 128, 128, 0, stream>>>(ta); ALNR_LAUNCHED();

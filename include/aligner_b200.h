@@ -196,6 +196,9 @@ int alnr_matrix_search(const alnr_params *p, const alnr_batch *b, const double *
  * 32-bit add / max / logic op / multiply-add lane) of alu-pipe-only chains and of a 1:1
  * alu-pipe + fma-pipe mix over all SMs. */
 int alnr_measure_int_peak(int device, double *alu_ops_per_s, double *mixed_ops_per_s);
+/* FP64 denominators for the heuristic matrix search (non-integral matrices force doubles):
+ * ops/s of independent DADD chains, and of DADD + fmax chains (an op = one f64 add or max). */
+int alnr_measure_fp64_peak(int device, double *add_ops_per_s, double *addmax_ops_per_s);
 
 /* pinned host memory helpers for callers without a CUDA binding */
 void *alnr_host_alloc(uint64_t bytes);

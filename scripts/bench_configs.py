@@ -95,3 +95,13 @@ if __name__ == "__main__":
         c4(100000, "nocheck" not in what)
     if "c5" in what:
         c5(200, 50)
+    if "c5big" in what:
+        c5(2000, 100)
+    if "peaks" in what:
+        import ctypes as C
+        a, b = C.c_double(), C.c_double()
+        N.lib().alnr_measure_int_peak(0, C.byref(a), C.byref(b))
+        c, d = C.c_double(), C.c_double()
+        N.lib().alnr_measure_fp64_peak(0, C.byref(c), C.byref(d))
+        print(json.dumps(dict(int_alu_tops=a.value / 1e12, int_mixed_tops=b.value / 1e12,
+                              f64_add_tops=c.value / 1e12, f64_addmax_tops=d.value / 1e12)), flush=True)
