@@ -1,4 +1,6 @@
 // api.cu — the extern "C" boundary declared in include/aligner_b200.h.
+#include <chrono>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <new>
@@ -116,11 +118,20 @@ int alnr_align_batch(const alnr_params *p, const alnr_batch *b, alnr_batch_out *
   alnr_batch_impl &B = hh->impl;
   // uniform batches stream chunk by chunk (copies overlap compute); init() finds out which
   B.resident = false;
-  B.max_chunk = 1u << 20;
+  B.ramp = true;
+  B.max_chunk = 600000;  // ~3 waves of the strip kernel: short pipeline fill / drain
+  static const bool timing = std::getenv("ALNR_TIMING") != nullptr;
+  const auto t0 = std::chrono::steady_clock::now();
   int st = B.init(p, b, false);
+  const auto t1 = std::chrono::steady_clock::now();
   if (!st) {
     if (B.uniform) {
       st = B.stream_all(b, out);
+      if (timing)
+        std::fprintf(stderr, "[alnr] align_batch: init %.1f ms, stream_all %.1f ms, %zu chunks\n",
+                     std::chrono::duration<double, std::milli>(t1 - t0).count(),
+                     std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t1).count(),
+                     B.chunks.size());
     } else {
       cudaError_t e = cudaSuccess;
       if (B.count) {

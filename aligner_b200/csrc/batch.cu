@@ -4,9 +4,11 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <numeric>
+#include <thread>
 #include <type_traits>
 
 #include "kernels_exact.cuh"
@@ -27,6 +29,9 @@ alnr_batch_impl::~alnr_batch_impl() {
   if (ev1) cudaEventDestroy(ev1);
   if (ev2) cudaEventDestroy(ev2);
   for (cudaEvent_t e : fill_events) cudaEventDestroy(e);
+  for (cudaEvent_t e : ev_p1) cudaEventDestroy(e);
+  for (cudaEvent_t e : ev_p2) cudaEventDestroy(e);
+  if (stream2) cudaStreamDestroy(stream2);
   if (stream) cudaStreamDestroy(stream);
 }
 
@@ -75,6 +80,13 @@ int alnr_batch_impl::classify() {
   return ALNR_INVALID_ARGUMENT;
 }
 
+static const uint64_t kStripWavePairs = 148ull * 10 * 128;
+
+static __global__ void uniform_offsets_kernel(uint64_t *qo, uint64_t *to, uint64_t n_off, uint64_t n, uint64_t m) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n_off) { qo[i] = i * n; to[i] = i * m; }
+}
+
 static uint64_t scratch_budget_bytes() {
   size_t free_b = 0, total_b = 0;
   if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) return 1ull << 30;
@@ -113,7 +125,7 @@ int alnr_batch_impl::plan_chunks(const uint64_t *q_off, const uint64_t *t_off) {
     uint32_t mx = 0;
     for (uint64_t s = count; s-- > 0;) { uint32_t m, n; dims(s, m, n); mx = std::max(mx, n); nsuf[s] = mx; }
   }
-  const uint64_t budget = scratch_budget_bytes();
+  const uint64_t budget = scratch_budget_bytes() / 2;  // two parity copies of the chunk scratch
   const size_t num_sz = numeric == ALNR_NUM_F64 ? 8 : 4;
   uint64_t s = 0;
   while (s < count) {
@@ -127,6 +139,16 @@ int alnr_batch_impl::plan_chunks(const uint64_t *q_off, const uint64_t *t_off) {
     uint64_t c = std::min<uint64_t>(groups * 32, count - s);
     if (c < count - s) c = std::max<uint64_t>(c / 64 * 64, 32);  // keep duo-kernel warps whole
     if (c > max_chunk) c = max_chunk;
+    // whole waves of the strip kernel (148 SMs x 10 resident blocks x 128 pairs): kernels of one
+    // stream run back to back, so a partly filled last wave is idle time in every chunk
+    if (numeric == ALNR_NUM_I16X2 && c < count - s && c >= kStripWavePairs) c = c / kStripWavePairs * kStripWavePairs;
+    if (ramp && numeric == ALNR_NUM_I16X2 && count > 4 * kStripWavePairs) {
+      // streaming call: a one-wave first chunk starts the compute after ~1 ms of copies, a
+      // one-wave last chunk leaves only ~2 ms of device->host copies behind the last kernel
+      const uint64_t rem = count - s;
+      if (s == 0) c = std::min<uint64_t>(c, kStripWavePairs);
+      else if (rem <= c && rem > kStripWavePairs + kStripWavePairs / 2) c = (rem - kStripWavePairs) / 64 * 64;
+    }
     uint32_t m1, n1;
     dims(s, m1, n1);
     const bool wave = wave_eligible(*this, m1, n1);
@@ -161,6 +183,13 @@ DLayout alnr_batch_impl::layout_dims(uint32_t m, uint32_t n, bool wave) const {
 
 DLayout alnr_batch_impl::layout_for(const Chunk &c) const { return layout_dims(c.m_max, c.n_max, c.wave); }
 
+// Compact alignment output: identity pair order (uniform batch, so a chunk is a contiguous
+// region of q_aln / t_aln) and move strings short enough for the two-phase traceback.
+bool alnr_batch_impl::chunk_compact(const Chunk &c) const {
+  const uint32_t nmw = (c.n_max + c.m_max + 1 + 15) / 16;
+  return uniform && !c.wave && nmw <= 256 && c.count >= 32;
+}
+
 int alnr_batch_impl::init(const alnr_params *p, const alnr_batch *b, bool want_mats) {
   if (!p || !b || !p->matrix) return ALNR_INVALID_ARGUMENT;
   if (p->mode != ALNR_GLOBAL && p->mode != ALNR_LOCAL) return ALNR_INVALID_ARGUMENT;
@@ -180,6 +209,7 @@ int alnr_batch_impl::init(const alnr_params *p, const alnr_batch *b, bool want_m
   }
   ALNR_CUDA(cudaSetDevice(device));
   ALNR_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+  ALNR_CUDA(cudaStreamCreateWithFlags(&stream2, cudaStreamNonBlocking));
   ALNR_CUDA(cudaEventCreate(&ev0));
   ALNR_CUDA(cudaEventCreate(&ev1));
   ALNR_CUDA(cudaEventCreate(&ev2));
@@ -188,13 +218,38 @@ int alnr_batch_impl::init(const alnr_params *p, const alnr_batch *b, bool want_m
   t_total = count ? b->t_off[count] : 0;
   n_max = m_max = 0;
   uniform = true;
-  for (uint64_t i = 0; i < count; ++i) {
-    if (b->q_off[i + 1] < b->q_off[i] || b->t_off[i + 1] < b->t_off[i]) return ALNR_INVALID_ARGUMENT;
-    uint64_t n = b->q_off[i + 1] - b->q_off[i], m = b->t_off[i + 1] - b->t_off[i];
-    if (n >= (1ull << 31) || m >= (1ull << 31)) return ALNR_INVALID_ARGUMENT;
-    if (i && (n != b->q_off[1] - b->q_off[0] || m != b->t_off[1] - b->t_off[0])) uniform = false;
-    n_max = std::max<uint32_t>(n_max, (uint32_t)n);
-    m_max = std::max<uint32_t>(m_max, (uint32_t)m);
+  {
+    // offsets sweep (monotone, < 2^31 per sequence, uniform or ragged): 10^7 pairs are 160 MB of
+    // offsets, so it runs on a few host threads
+    const unsigned nt = count >= (1u << 20) ? 8u : 1u;
+    struct Part { uint32_t n_max = 0, m_max = 0; bool uniform = true, bad = false; };
+    std::vector<Part> parts(nt);
+    const uint64_t n0 = count ? b->q_off[1] - b->q_off[0] : 0, m0 = count ? b->t_off[1] - b->t_off[0] : 0;
+    auto sweep = [&](unsigned k) {
+      Part &pt = parts[k];
+      const uint64_t lo = count * k / nt, hi = count * (k + 1) / nt;
+      uint64_t nmx = 0, mmx = 0, diff = 0, neg = 0;
+      for (uint64_t i = lo; i < hi; ++i) {
+        const uint64_t n = b->q_off[i + 1] - b->q_off[i], m = b->t_off[i + 1] - b->t_off[i];
+        neg |= (n | m) >> 31;  // covers offsets that go backwards (the difference wraps)
+        diff |= (n ^ n0) | (m ^ m0);
+        nmx = n > nmx ? n : nmx;
+        mmx = m > mmx ? m : mmx;
+      }
+      pt.bad = neg != 0; pt.uniform = diff == 0; pt.n_max = (uint32_t)nmx; pt.m_max = (uint32_t)mmx;
+    };
+    if (nt == 1) sweep(0);
+    else {
+      std::vector<std::thread> th;
+      for (unsigned k = 0; k < nt; ++k) th.emplace_back(sweep, k);
+      for (auto &t : th) t.join();
+    }
+    for (const Part &pt : parts) {
+      if (pt.bad) return ALNR_INVALID_ARGUMENT;
+      uniform = uniform && pt.uniform;
+      n_max = std::max(n_max, pt.n_max);
+      m_max = std::max(m_max, pt.m_max);
+    }
   }
   int st = classify();
   if (st) return st;
@@ -208,8 +263,16 @@ int alnr_batch_impl::init(const alnr_params *p, const alnr_batch *b, bool want_m
       ALNR_CUDA(cudaMemcpyAsync(d_q.p, b->q, q_total, cudaMemcpyHostToDevice, stream));
       ALNR_CUDA(cudaMemcpyAsync(d_t.p, b->t, t_total, cudaMemcpyHostToDevice, stream));
     }
-    ALNR_CUDA(cudaMemcpyAsync(d_qoff.p, b->q_off, (count + 1) * 8, cudaMemcpyHostToDevice, stream));
-    ALNR_CUDA(cudaMemcpyAsync(d_toff.p, b->t_off, (count + 1) * 8, cudaMemcpyHostToDevice, stream));
+    if (uniform && count >= 4096 && b->q_off[0] == 0 && b->t_off[0] == 0) {
+      // equal lengths: the offsets are i * n and i * m — written on the device instead of
+      // copying 16 bytes per pair over PCIe
+      uniform_offsets_kernel<<<(unsigned)((count + 1 + 255) / 256), 256, 0, stream>>>(
+          d_qoff.p, d_toff.p, count + 1, b->q_off[1], b->t_off[1]);
+      ALNR_LAUNCHED();
+    } else {
+      ALNR_CUDA(cudaMemcpyAsync(d_qoff.p, b->q_off, (count + 1) * 8, cudaMemcpyHostToDevice, stream));
+      ALNR_CUDA(cudaMemcpyAsync(d_toff.p, b->t_off, (count + 1) * 8, cudaMemcpyHostToDevice, stream));
+    }
   }
   ALNR_CUDA(d_matd.alloc((size_t)V * V));
   ALNR_CUDA(d_mati.alloc((size_t)V * V));
@@ -233,6 +296,17 @@ int alnr_batch_impl::init(const alnr_params *p, const alnr_batch *b, bool want_m
   ALNR_CUDA(d_taln.alloc(q_total + t_total + count));
   ALNR_CUDA(d_flags.alloc(4));
   ALNR_CUDA(d_rerun.alloc(count + 1));
+  {
+    uint32_t cmax = 0;
+    for (const Chunk &c : chunks) cmax = std::max(cmax, c.count);
+    ALNR_CUDA(d_desc.alloc((size_t)cmax / (kScanBlock * kScanItems) + 4));
+    ALNR_CUDA(d_ctotal.alloc(chunks.size() + 1));
+    uint64_t mwords = 1;
+    for (const Chunk &c : chunks)
+      if (chunk_compact(c))
+        mwords = std::max<uint64_t>(mwords, (uint64_t)((c.count + 31) / 32 * 32) * ((c.n_max + c.m_max + 1 + 15) / 16));
+    ALNR_CUDA(d_moves.alloc(mwords));
+  }
 
   uint64_t dwords = 1, hcol = 1;
   for (const Chunk &c : chunks) {
@@ -240,9 +314,18 @@ int alnr_batch_impl::init(const alnr_params *p, const alnr_batch *b, bool want_m
     dwords = std::max<uint64_t>(dwords, dl.words_for(c.count));
     hcol = std::max<uint64_t>(hcol, (uint64_t)((c.count + 31) / 32) * 32 * ((uint64_t)std::max(c.m_max, c.n_max) + 1));
   }
-  ALNR_CUDA(d_D.alloc(dwords));
-  if (numeric == ALNR_NUM_F64) ALNR_CUDA(d_hcol_d.alloc(hcol));
-  else ALNR_CUDA(d_hcol_i.alloc(hcol));
+  const size_t copies = chunks.size() > 1 ? 2 : 1;
+  d_words = (dwords + 3) / 4 * 4; hcol_elems = (hcol + 3) / 4 * 4;
+  ALNR_CUDA(d_D.alloc(d_words * copies));
+  if (numeric == ALNR_NUM_F64) ALNR_CUDA(d_hcol_d.alloc(hcol_elems * copies));
+  else ALNR_CUDA(d_hcol_i.alloc(hcol_elems * copies));
+  for (size_t i = 0; i < chunks.size(); ++i) {
+    cudaEvent_t e1, e2;
+    ALNR_CUDA(cudaEventCreateWithFlags(&e1, cudaEventDisableTiming));
+    ev_p1.push_back(e1);
+    ALNR_CUDA(cudaEventCreateWithFlags(&e2, cudaEventDisableTiming));
+    ev_p2.push_back(e2);
+  }
   if (want_matrices && count == 1) {
     ALNR_CUDA(d_Hout.alloc(((size_t)m_max + 1) * ((size_t)n_max + 1)));
     ALNR_CUDA(d_Dout.alloc(((size_t)m_max + 1) * ((size_t)n_max + 1)));
@@ -263,7 +346,7 @@ static int launch_exact(alnr_batch_impl &B, const Chunk &c, const ChunkView &cv,
                         const FillOut &fo, T *hcol, const T *mat) {
   ExactArgs<T> a;
   a.cv = cv; a.mode = B.mode; a.V = B.V; a.del = (T)B.del; a.ext = (T)B.ext;
-  a.matrix = mat; a.hcol = hcol; a.hrows = c.m_max + 1; a.D = B.d_D.p; a.dl = dl; a.fo = fo;
+  a.matrix = mat; a.hcol = hcol; a.hrows = c.m_max + 1; a.D = B.Dp(); a.dl = dl; a.fo = fo;
   a.H_out = B.d_Hout.p; a.D_out = B.d_Dout.p;
   const uint32_t blocks = (c.count + 127) / 128;
   fill_exact_kernel<T><<<blocks, 128, (size_t)B.V * B.V * sizeof(T), B.stream>>>(a);
@@ -279,7 +362,7 @@ static int launch_warp(alnr_batch_impl &B, const Chunk &c, const ChunkView &cv, 
   const bool local = B.mode == ALNR_LOCAL;
   a.stateful = local && B.del != B.ext;
   a.matrix = mat; a.item_matrices = nullptr;
-  a.D = B.d_D.p; a.dl = dl; a.fo = fo;
+  a.D = B.Dp(); a.dl = dl; a.fo = fo;
   a.rowbuf = hcol; a.rowbuf_stride = c.n_max + 1;
   a.nzw = (B.n_max + 31) / 32;
   uint32_t *counters = B.d_wz.p;
@@ -295,7 +378,7 @@ static int launch_warp(alnr_batch_impl &B, const Chunk &c, const ChunkView &cv, 
   // pairs whose speculation did not settle: exact column-major kernel over the fail list
   ExactArgs<T> e;
   e.cv = cv; e.mode = B.mode; e.V = B.V; e.del = (T)B.del; e.ext = (T)B.ext;
-  e.matrix = mat; e.hcol = hcol; e.hrows = c.m_max + 1; e.D = B.d_D.p; e.dl = dl; e.fo = fo;
+  e.matrix = mat; e.hcol = hcol; e.hrows = c.m_max + 1; e.D = B.Dp(); e.dl = dl; e.fo = fo;
   e.H_out = mats ? B.d_Hout.p : nullptr; e.D_out = mats ? B.d_Dout.p : nullptr;
   e.list = a.fail_list; e.list_count = a.fail_count;
   fill_exact_kernel<T><<<(c.count + 127) / 128, 128, (size_t)B.V * B.V * sizeof(T), B.stream>>>(e);
@@ -321,10 +404,34 @@ int alnr_batch_impl::run() {
   return ALNR_OK;
 }
 
+// Phase 1 on `stream`, phase 2 on the second stream (on `stream` too when profiling the fill
+// or when the batch is a single chunk).  Chunk k+2 reuses chunk k's parity copy of the scratch,
+// so its phase 1 waits for phase 2 of chunk k; `stream` also waits for the LAST phase 2 so that
+// the caller only ever has to synchronise `stream`.
 int alnr_batch_impl::run_chunk(size_t ci) {
+  static const bool serial_env = getenv("ALNR_SERIAL_PHASES") != nullptr;
+  const bool overlap = chunks.size() > 1 && !profile && !serial_env;
+  s2 = overlap ? stream2 : stream;
+  par = chunks.size() > 1 ? (int)(ci & 1) : 0;
+  if (overlap && ci >= 2) ALNR_CUDA(cudaStreamWaitEvent(stream, ev_p2[ci - 2], 0));
+  int st = phase1(ci);
+  if (st) return st;
+  if (overlap) {
+    ALNR_CUDA(cudaEventRecord(ev_p1[ci], stream));
+    ALNR_CUDA(cudaStreamWaitEvent(stream2, ev_p1[ci], 0));
+  }
+  st = phase2(ci);
+  if (st) return st;
+  if (overlap) {
+    ALNR_CUDA(cudaEventRecord(ev_p2[ci], stream2));
+    if (ci + 1 == chunks.size()) ALNR_CUDA(cudaStreamWaitEvent(stream, ev_p2[ci], 0));
+  }
+  return ALNR_OK;
+}
+
+int alnr_batch_impl::phase1(size_t ci) {
   const Chunk &c = chunks[ci];
   FillOut fo{d_f.p, d_corner.p, d_start.p, d_status.p};
-  TraceOut to{d_coords.p, d_alnoff.p, d_alnlen.p, d_qaln.p, d_taln.p, nullptr};
   ChunkView cv{d_q.p, d_t.p, d_qoff.p, d_toff.p, uniform ? nullptr : d_order.p, c.first, c.count};
   const DLayout dl = layout_for(c);
   // symbol validation: one coalesced sweep; the per-pair scan only runs if it found something
@@ -341,21 +448,48 @@ int alnr_batch_impl::run_chunk(size_t ci) {
   int st = fill_mark(false);
   if (st) return st;
   if (c.wave) st = wave_run_pair(*this, c, dl, fo);
-  else if (numeric == ALNR_NUM_F64 && dl.skewed) st = launch_warp<double>(*this, c, cv, dl, fo, d_hcol_d.p, d_matd.p);
-  else if (numeric == ALNR_NUM_I32 && dl.skewed) st = launch_warp<int>(*this, c, cv, dl, fo, d_hcol_i.p, d_mati.p);
-  else if (numeric == ALNR_NUM_F64) st = launch_exact<double>(*this, c, cv, dl, fo, d_hcol_d.p, d_matd.p);
-  else if (numeric == ALNR_NUM_I32) st = launch_exact<int>(*this, c, cv, dl, fo, d_hcol_i.p, d_mati.p);
-  else st = strip_run_chunk(*this, c, cv, dl, fo);
+  else if (numeric == ALNR_NUM_F64 && dl.skewed) st = launch_warp<double>(*this, c, cv, dl, fo, hcol_d(), d_matd.p);
+  else if (numeric == ALNR_NUM_I32 && dl.skewed) st = launch_warp<int>(*this, c, cv, dl, fo, hcol_i(), d_mati.p);
+  else if (numeric == ALNR_NUM_F64) st = launch_exact<double>(*this, c, cv, dl, fo, hcol_d(), d_matd.p);
+  else if (numeric == ALNR_NUM_I32) st = launch_exact<int>(*this, c, cv, dl, fo, hcol_i(), d_mati.p);
+  else st = strip_main_pass(*this, c, cv, dl, fo);
   if (st) return st;
-  st = fill_mark(true);
-  if (st) return st;
-  TraceArgs ta{cv, mode, V, d_D.p, dl, fo, to};
+  if (numeric != ALNR_NUM_I16X2 || !(mode == ALNR_LOCAL && del != ext)) st = fill_mark(true);
+  return st;
+}
+
+int alnr_batch_impl::phase2(size_t ci) {
+  const Chunk &c = chunks[ci];
+  FillOut fo{d_f.p, d_corner.p, d_start.p, d_status.p};
+  TraceOut to{d_coords.p, d_alnoff.p, d_alnlen.p, d_qaln.p, d_taln.p, nullptr};
+  ChunkView cv{d_q.p, d_t.p, d_qoff.p, d_toff.p, uniform ? nullptr : d_order.p, c.first, c.count};
+  const DLayout dl = layout_for(c);
+  if (numeric == ALNR_NUM_I16X2 && !c.wave && mode == ALNR_LOCAL && del != ext) {
+    int st = strip_rerun_passes(*this, c, cv, dl, fo);  // on s2
+    if (st) return st;
+    st = fill_mark(true);  // only recorded when profiling, i.e. when s2 == stream
+    if (st) return st;
+  }
+  TraceArgs ta{cv, mode, V, Dp(), dl, fo, to};
   const uint32_t nmw = (c.n_max + c.m_max + 1 + 15) / 16;  // 2-bit move words per pair
-  if ((size_t)nmw * kTraceBlock * 4 <= 44 * 1024 && to.freq == nullptr) {
+  if (chunk_compact(c)) {
+    // alignments of the chunk back to back from the start of its region (kernels_trace.cuh A/S/B)
+    const uint32_t stride = (c.count + 31) / 32 * 32;
+    const uint32_t tiles = (c.count + kScanBlock * kScanItems - 1) / (kScanBlock * kScanItems);
+    trace_moves_kernel<<<(c.count + 127) / 128, 128, 0, s2>>>(ta, d_moves.p, stride);
+    ALNR_LAUNCHED();
+    ALNR_CUDA(cudaMemsetAsync(d_desc.p, 0, ((size_t)tiles + 1) * 8, s2));
+    scan_lengths_kernel<<<tiles, kScanBlock, 0, s2>>>(d_alnlen.p, d_alnoff.p, c.first, c.count,
+                                                      c.q0 + c.t0 + c.first,
+                                                      reinterpret_cast<unsigned long long *>(d_desc.p),
+                                                      d_ctotal.p + ci);
+    ALNR_LAUNCHED();
+    trace_expand_kernel<<<(c.count + 127) / 128, 128, 0, s2>>>(ta, d_moves.p, stride);
+  } else if ((size_t)nmw * kTraceBlock * 4 <= 44 * 1024 && to.freq == nullptr) {
     traceback_coop_kernel<<<(c.count + kTraceBlock - 1) / kTraceBlock, kTraceBlock,
-                            (size_t)nmw * kTraceBlock * 4, stream>>>(ta, nmw);
+                            (size_t)nmw * kTraceBlock * 4, s2>>>(ta, nmw);
   } else {
-    traceback_kernel<<<(c.count + 127) / 128, 128, 0, stream>>>(ta);
+    traceback_kernel<<<(c.count + 127) / 128, 128, 0, s2>>>(ta);
   }
   ALNR_LAUNCHED();
   return ALNR_OK;
@@ -383,43 +517,103 @@ int alnr_batch_impl::stream_all(const alnr_batch *b, alnr_batch_out *out) {
     if (e != cudaSuccess) fail(e, "memset flags");
   }
   rerun_total = 0;
-  for (size_t ci = 0; ci < chunks.size() && !st; ++ci) {
+  // ALNR_TIMING: per-chunk timeline (H2D end, compute begin/end, D2H end) relative to the first copy
+  static const bool trace = getenv("ALNR_TIMING") != nullptr;
+  std::vector<cudaEvent_t> tev;
+  auto mark = [&](cudaStream_t sx) {
+    if (!trace) return;
+    cudaEvent_t e;
+    cudaEventCreate(&e);
+    cudaEventRecord(e, sx);
+    tev.push_back(e);
+  };
+  mark(s_in);
+  // chunk totals of the compact alignment output come back through pinned memory; the host waits
+  // for chunk k's total only after chunk k+1 has been enqueued, so the device never idles
+  uint64_t *h_tot = nullptr;
+  if (!st) {
+    cudaError_t e = cudaMallocHost(&h_tot, (chunks.size() + 1) * sizeof(uint64_t));
+    if (e != cudaSuccess) fail(e, "cudaMallocHost totals");
+  }
+  auto drain = [&](size_t ci) {  // device -> host copies of chunk ci on s_out
     const Chunk &c = chunks[ci];
-    cudaError_t e = cudaMemcpyAsync(d_q.p + c.q0, b->q + c.q0, c.q1 - c.q0, cudaMemcpyHostToDevice, s_in);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(d_t.p + c.t0, b->t + c.t0, c.t1 - c.t0, cudaMemcpyHostToDevice, s_in);
-    if (e == cudaSuccess) e = cudaEventRecord(ev_in[ci], s_in);
-    if (e == cudaSuccess) e = cudaStreamWaitEvent(stream, ev_in[ci], 0);
-    if (e != cudaSuccess) { fail(e, "H2D chunk"); break; }
-    st = run_chunk(ci);
-    if (st) break;
-    e = cudaEventRecord(ev_done[ci], stream);
-    if (e == cudaSuccess) e = cudaStreamWaitEvent(s_out, ev_done[ci], 0);
+    cudaError_t e = cudaSuccess;
+    const size_t f0 = c.first, fc = c.count;
+    const size_t a0 = c.q0 + c.t0 + f0;  // first byte of the chunk's alignment region
+    size_t abytes = (c.q1 + c.t1 + f0 + fc) - a0;
+    if (chunk_compact(c)) {
+      e = cudaEventSynchronize(ev_done[ci]);  // h_tot[ci] was copied before ev_done was recorded
+      if (e == cudaSuccess) abytes = (size_t)h_tot[ci];
+    }
     auto cp = [&](void *dst, const void *src, size_t off, size_t bytes) {
-      if (dst && e == cudaSuccess)
+      if (dst && bytes && e == cudaSuccess)
         e = cudaMemcpyAsync((char *)dst + off, (const char *)src + off, bytes, cudaMemcpyDeviceToHost, s_out);
     };
-    const size_t f0 = c.first, fc = c.count;
     cp(out->f, d_f.p, f0 * 8, fc * 8);
     cp(out->corner, d_corner.p, f0 * 8, fc * 8);
     cp(out->coords, d_coords.p, f0 * 32, fc * 32);
     cp(out->aln_off, d_alnoff.p, f0 * 8, fc * 8);
     cp(out->aln_len, d_alnlen.p, f0 * 4, fc * 4);
     cp(out->status, d_status.p, f0 * 4, fc * 4);
-    const size_t a0 = c.q0 + c.t0 + f0, a1 = c.q1 + c.t1 + f0 + fc;  // alignment slots of the chunk
-    cp(out->q_aln, d_qaln.p, a0, a1 - a0);
-    cp(out->t_aln, d_taln.p, a0, a1 - a0);
+    cp(out->q_aln, d_qaln.p, a0, abytes);
+    cp(out->t_aln, d_taln.p, a0, abytes);
     if (e != cudaSuccess) fail(e, "D2H chunk");
+    mark(s_out);
+  };
+  // every chunk has its own region of d_q / d_t, so all host->device copies are queued up front
+  // (they run back to back on the copy engine) and each chunk's compute waits for its own event
+  for (size_t ci = 0; ci < chunks.size() && !st; ++ci) {
+    const Chunk &c = chunks[ci];
+    cudaError_t e = cudaMemcpyAsync(d_q.p + c.q0, b->q + c.q0, c.q1 - c.q0, cudaMemcpyHostToDevice, s_in);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_t.p + c.t0, b->t + c.t0, c.t1 - c.t0, cudaMemcpyHostToDevice, s_in);
+    if (e == cudaSuccess) e = cudaEventRecord(ev_in[ci], s_in);
+    if (e != cudaSuccess) fail(e, "H2D chunk");
   }
+  for (size_t ci = 0; ci < chunks.size() && !st; ++ci) {
+    const Chunk &c = chunks[ci];
+    cudaError_t e = cudaStreamWaitEvent(stream, ev_in[ci], 0);
+    if (e != cudaSuccess) { fail(e, "H2D wait"); break; }
+    mark(stream);
+    st = run_chunk(ci);
+    if (st) break;
+    mark(s2);
+    // s2 = the stream phase 2 of this chunk ran on: its results are complete there
+    if (chunk_compact(c))
+      e = cudaMemcpyAsync(h_tot + ci, d_ctotal.p + ci, sizeof(uint64_t), cudaMemcpyDeviceToHost, s2);
+    if (e == cudaSuccess) e = cudaEventRecord(ev_done[ci], s2);
+    if (e == cudaSuccess) e = cudaStreamWaitEvent(s_out, ev_done[ci], 0);
+    if (e != cudaSuccess) { fail(e, "chunk events"); break; }
+    if (ci > 0) drain(ci - 1);
+  }
+  if (!st && !chunks.empty()) drain(chunks.size() - 1);
   cudaError_t e1 = cudaStreamSynchronize(s_in), e2 = cudaStreamSynchronize(stream), e3 = cudaStreamSynchronize(s_out);
+  if (e2 == cudaSuccess) e2 = cudaStreamSynchronize(stream2);
   if (!st && e1 != cudaSuccess) fail(e1, "sync s_in");
   if (!st && e2 != cudaSuccess) fail(e2, "sync compute");
   if (!st && e3 != cudaSuccess) fail(e3, "sync s_out");
+  if (trace && !st && tev.size() == 1 + 3 * chunks.size()) {
+    // order of marks: [0] start, then per chunk ci: compute begin, compute end; the D2H end
+    // of chunk ci-1 is recorded inside iteration ci (after its compute-end mark), the last one at the end
+    auto ms = [&](size_t k) { float t = 0; cudaEventElapsedTime(&t, tev[0], tev[k]); return t; };
+    std::vector<size_t> c0(chunks.size()), c1(chunks.size()), d2h(chunks.size());
+    size_t k = 1;
+    for (size_t ci = 0; ci < chunks.size(); ++ci) {
+      c0[ci] = k++; c1[ci] = k++;
+      if (ci > 0) d2h[ci - 1] = k++;
+    }
+    d2h[chunks.size() - 1] = k++;
+    for (size_t ci = 0; ci < chunks.size(); ++ci)
+      std::fprintf(stderr, "[alnr] chunk %2zu: compute %7.2f -> %7.2f  d2h_end %7.2f ms\n", ci,
+                   ms(c0[ci]), ms(c1[ci]), ms(d2h[ci]));
+  }
+  for (cudaEvent_t e : tev) cudaEventDestroy(e);
   for (size_t i = 0; i < chunks.size(); ++i) {
     if (ev_in[i]) cudaEventDestroy(ev_in[i]);
     if (ev_done[i]) cudaEventDestroy(ev_done[i]);
   }
   cudaStreamDestroy(s_in);
   cudaStreamDestroy(s_out);
+  if (h_tot) cudaFreeHost(h_tot);
   return st;
 }
 

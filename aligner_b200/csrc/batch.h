@@ -30,10 +30,27 @@ struct alnr_batch_impl {
   std::vector<Chunk> chunks;
 
   // device state
-  cudaStream_t stream = nullptr;
+  cudaStream_t stream = nullptr;    // phase 1 of every chunk: validation, packing, main fill pass
+  // Phase 2 of a chunk (speculation re-runs, exact leftovers, traceback) runs on a second stream
+  // so that its thin launches overlap the next chunk's main pass; the D / row / list scratch is
+  // double-buffered by chunk parity.  `stream` waits for the last phase 2 at the end of run(), so
+  // synchronising `stream` still means "everything is done".
+  cudaStream_t stream2 = nullptr;
+  cudaStream_t s2 = nullptr;        // stream phase 2 is enqueued on right now (stream2, or stream when serial)
+  std::vector<cudaEvent_t> ev_p1, ev_p2;  // per chunk: phase 1 done, phase 2 done
+  int par = 0;                      // parity of the chunk being enqueued
+  uint64_t d_words = 0, hcol_elems = 0, rerun_words = 0;  // size of ONE parity copy
+  uint32_t *Dp() const { return d_D.p + (size_t)par * d_words; }
+  int *hcol_i() const { return d_hcol_i.p ? d_hcol_i.p + (size_t)par * hcol_elems : nullptr; }
+  double *hcol_d() const { return d_hcol_d.p ? d_hcol_d.p + (size_t)par * hcol_elems : nullptr; }
+  int phase1(size_t ci);            // on `stream`
+  int phase2(size_t ci);            // on `s2`
   cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr;
   DevBuf<uint8_t> d_q, d_t, d_qaln, d_taln, d_Dout;
   DevBuf<uint64_t> d_qoff, d_toff, d_coords, d_alnoff;
+  DevBuf<uint64_t> d_desc;      // compact traceback: [ticket][one scan descriptor per tile]
+  DevBuf<uint32_t> d_moves;     // compact traceback: 2-bit move strings, [word][slot]
+  DevBuf<uint64_t> d_ctotal;    // compact traceback: alignment bytes used by each chunk
   DevBuf<uint32_t> d_order, d_start, d_alnlen, d_D, d_rerun;
   DevBuf<int32_t> d_status;
   DevBuf<int> d_flags;
@@ -52,15 +69,17 @@ struct alnr_batch_impl {
   ~alnr_batch_impl();
   int init(const alnr_params *p, const alnr_batch *b, bool want_mats);
   int run();                     // enqueue all kernels on `stream`
-  int run_chunk(size_t ci);      // validation + fill + traceback of one chunk on `stream`
+  int run_chunk(size_t ci);      // phase 1 + phase 2 of one chunk with the cross-stream dependencies
   // host buffers in -> host buffers out, chunks pipelined over three streams
   int stream_all(const alnr_batch *b, alnr_batch_out *out);
   bool resident = true;          // inputs were uploaded by init()
   uint32_t max_chunk = 1u << 22;
+  bool ramp = false;             // streaming: short first and last chunks
   int download(alnr_batch_out *out);
   int classify();
   DLayout layout_for(const Chunk &c) const;
   DLayout layout_dims(uint32_t m, uint32_t n, bool wave) const;
+  bool chunk_compact(const Chunk &c) const;  // alignments of the chunk are written back to back
   bool use_warp(uint32_t m) const;  // warp-per-pair kernel instead of one pair per thread
   int plan_chunks(const uint64_t *q_off, const uint64_t *t_off);
 };

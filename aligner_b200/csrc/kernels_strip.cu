@@ -44,13 +44,15 @@ int strip_prepare(alnr_batch_impl &B) {
   uint32_t cmax = 0;
   for (const Chunk &c : B.chunks) cmax = std::max(cmax, c.count);
   const uint32_t nzw = (B.n_max + 31) / 32;
-  // layout of d_rerun: [counters 8 per chunk][list0 cmax][list1 cmax][z0 cmax*nzw][z1 cmax*nzw]
-  ALNR_CUDA(B.d_rerun.alloc(8 * B.chunks.size() + 2ull * cmax + 2ull * cmax * nzw));
+  // layout of d_rerun: [counters 8 per chunk] then one block per chunk parity:
+  // [list0 cmax][list1 cmax][z0 cmax*nzw][z1 cmax*nzw]
+  B.rerun_words = 2ull * cmax + 2ull * cmax * nzw;
+  ALNR_CUDA(B.d_rerun.alloc(8 * B.chunks.size() + (B.chunks.size() > 1 ? 2 : 1) * B.rerun_words));
   return ALNR_OK;
 }
 
 template <int R>
-static int launch_strip(alnr_batch_impl &B, const StripArgs &a, uint32_t duos, bool local, bool stateful) {
+static int launch_strip(alnr_batch_impl &B, cudaStream_t stream, const StripArgs &a, uint32_t duos, bool local, bool stateful) {
   const size_t smem = a.hglobal ? 0 : (size_t)a.n * kStripBlock * 4;
   const unsigned blocks = (duos + kStripBlock - 1) / kStripBlock;
   if (blocks == 0) return ALNR_OK;
@@ -62,7 +64,7 @@ static int launch_strip(alnr_batch_impl &B, const StripArgs &a, uint32_t duos, b
                                      cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));   \
       attr_done = true;                                                                           \
     }                                                                                             \
-    fill_strip_kernel<R, L, S><<<blocks, kStripBlock, smem, B.stream>>>(a);                       \
+    fill_strip_kernel<R, L, S><<<blocks, kStripBlock, smem, stream>>>(a);                       \
   } while (0)
   if (!local) ALNR_STRIP_LAUNCH(false, false);
   else if (stateful) ALNR_STRIP_LAUNCH(true, true);
@@ -72,37 +74,32 @@ static int launch_strip(alnr_batch_impl &B, const StripArgs &a, uint32_t duos, b
   return ALNR_OK;
 }
 
-int strip_run_chunk(alnr_batch_impl &B, const Chunk &c, const ChunkView &cv, const DLayout &dl,
-                    const FillOut &fo) {
-  const uint32_t nwq = (B.n_max + 15) / 16, nwt = (B.m_max + 15) / 16;
+namespace {
+struct StripPlan {
+  StripArgs a;
+  uint32_t *counters, *lists[2], *zbuf[2];
+  bool local, stateful;
+  uint32_t R;
+};
+
+StripPlan strip_plan(alnr_batch_impl &B, const Chunk &c, const ChunkView &cv, const DLayout &dl, const FillOut &fo) {
+  StripPlan P;
+  const uint32_t nwq = (B.n_max + 15) / 16;
   const uint64_t groups = (B.count + 31) / 32;
   uint32_t cmax = 0;
   for (const Chunk &k : B.chunks) cmax = std::max(cmax, k.count);
   const uint32_t nzw = (B.n_max + 31) / 32;
-  const size_t ci = &c - B.chunks.data(), base = 8 * B.chunks.size();
-  uint32_t *counters = B.d_rerun.p + 8 * ci;
-  uint32_t *lists[2] = {B.d_rerun.p + base, B.d_rerun.p + base + cmax};
-  uint32_t *zbuf[2] = {B.d_rerun.p + base + 2ull * cmax, B.d_rerun.p + base + 2ull * cmax + (uint64_t)cmax * nzw};
-
-  // pack this chunk's sequences (2 bits per symbol, coalesced layout)
-  {
-    uint32_t *qpk = B.d_pack.p, *tpk = B.d_pack.p + groups * 32 * nwq;
-    const uint64_t lg = (c.count + 31) / 32;
-    uint64_t threads = lg * 32 * nwq;
-    pack2bit_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, B.stream>>>(B.d_q.p, B.d_qoff.p, cv.order, c.first,
-                                                                            c.count, nwq, qpk);
-    ALNR_LAUNCHED();
-    threads = lg * 32 * nwt;
-    pack2bit_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, B.stream>>>(B.d_t.p, B.d_toff.p, cv.order, c.first,
-                                                                            c.count, nwt, tpk);
-    ALNR_LAUNCHED();
-  }
-  const bool local = B.mode == ALNR_LOCAL;
-  const bool stateful = local && B.del != B.ext;
-  StripArgs a;
+  const size_t ci = &c - B.chunks.data();
+  uint32_t *base = B.d_rerun.p + 8 * B.chunks.size() + (size_t)B.par * B.rerun_words;
+  P.counters = B.d_rerun.p + 8 * ci;
+  P.lists[0] = base; P.lists[1] = base + cmax;
+  P.zbuf[0] = base + 2ull * cmax; P.zbuf[1] = base + 2ull * cmax + (uint64_t)cmax * nzw;
+  P.local = B.mode == ALNR_LOCAL;
+  P.stateful = P.local && B.del != B.ext;
+  StripArgs &a = P.a;
   a.qpk = B.d_pack.p;
   a.tpk = B.d_pack.p + groups * 32 * nwq;
-  a.nwq = nwq; a.nwt = nwt; a.n = B.n_max; a.m = B.m_max;
+  a.nwq = nwq; a.nwt = (B.m_max + 15) / 16; a.n = B.n_max; a.m = B.m_max;
   a.first = c.first; a.count = c.count;
   a.order = cv.order;
   for (int qs = 0; qs < 4; ++qs) {
@@ -114,38 +111,63 @@ int strip_run_chunk(alnr_batch_impl &B, const Chunk &c, const ChunkView &cv, con
     a.wtab[qs] = w;
   }
   a.del = (int)B.del; a.ext = (int)B.ext;
-  a.D = B.d_D.p; a.dl = dl; a.fo = fo;
-  a.list = nullptr; a.list_count = nullptr; a.z_in = nullptr; a.z_out = zbuf[0]; a.nzw = nzw;
-  a.fail_list = lists[0]; a.fail_count = counters + 0;
+  a.D = B.Dp(); a.dl = dl; a.fo = fo;
+  a.list = nullptr; a.list_count = nullptr; a.z_in = nullptr; a.z_out = P.zbuf[0]; a.nzw = nzw;
+  a.fail_list = P.lists[0]; a.fail_count = P.counters + 0;
   static const bool hrow_global = getenv("ALNR_STRIP_HROW_SMEM") == nullptr;
-  a.hglobal = hrow_global ? (uint32_t *)B.d_hcol_i.p : nullptr;
-  const uint32_t R = dl.rows_per_word;
-  auto go = [&](const StripArgs &args, uint32_t duos) {
-    return R == 15 ? launch_strip<15>(B, args, duos, local, stateful)
-                   : launch_strip<16>(B, args, duos, local, stateful);
-  };
-  if (stateful) ALNR_CUDA(cudaMemsetAsync(counters, 0, 8 * sizeof(uint32_t), B.stream));
-  int st = go(a, (c.count + 63) / 64 * 32);
-  if (st || !stateful) return st;
+  a.hglobal = hrow_global ? (uint32_t *)B.hcol_i() : nullptr;
+  P.R = dl.rows_per_word;
+  return P;
+}
+}  // namespace
 
+int strip_main_pass(alnr_batch_impl &B, const Chunk &c, const ChunkView &cv, const DLayout &dl,
+                    const FillOut &fo) {
+  StripPlan P = strip_plan(B, c, cv, dl, fo);
+  cudaStream_t stream = B.stream;
+  // pack this chunk's sequences (2 bits per symbol, coalesced layout)
+  {
+    const uint64_t lg = (c.count + 31) / 32;
+    uint64_t threads = lg * 32 * P.a.nwq;
+    pack2bit_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, stream>>>(
+        B.d_q.p, B.d_qoff.p, cv.order, c.first, c.count, P.a.nwq, const_cast<uint32_t *>(P.a.qpk));
+    ALNR_LAUNCHED();
+    threads = lg * 32 * P.a.nwt;
+    pack2bit_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, stream>>>(
+        B.d_t.p, B.d_toff.p, cv.order, c.first, c.count, P.a.nwt, const_cast<uint32_t *>(P.a.tpk));
+    ALNR_LAUNCHED();
+  }
+  if (P.stateful) ALNR_CUDA(cudaMemsetAsync(P.counters, 0, 8 * sizeof(uint32_t), stream));
+  const uint32_t duos = (c.count + 63) / 64 * 32;
+  return P.R == 15 ? launch_strip<15>(B, stream, P.a, duos, P.local, P.stateful)
+                   : launch_strip<16>(B, stream, P.a, duos, P.local, P.stateful);
+}
+
+int strip_rerun_passes(alnr_batch_impl &B, const Chunk &c, const ChunkView &cv, const DLayout &dl,
+                       const FillOut &fo) {
+  StripPlan P = strip_plan(B, c, cv, dl, fo);
+  cudaStream_t stream = B.s2;
   // re-run passes over the (device-side) fail list; grids are sized for the worst case and
   // exit at once past the list length, so no host synchronisation is needed.
   for (int pass = 0; pass < kRedoPasses; ++pass) {
-    StripArgs r = a;
-    r.list = lists[pass & 1]; r.list_count = counters + pass;
-    r.z_in = zbuf[pass & 1]; r.z_out = zbuf[(pass + 1) & 1];
-    r.fail_list = lists[(pass + 1) & 1]; r.fail_count = counters + pass + 1;
-    // expected fail fraction shrinks quickly; cap the grid at the full chunk anyway
-    st = go(r, (c.count + 1) / 2);
+    StripArgs r = P.a;
+    r.list = P.lists[pass & 1]; r.list_count = P.counters + pass;
+    r.z_in = P.zbuf[pass & 1]; r.z_out = P.zbuf[(pass + 1) & 1];
+    r.fail_list = P.lists[(pass + 1) & 1]; r.fail_count = P.counters + pass + 1;
+    // the fail fraction shrinks quickly: size each grid for a generous bound, the kernel exits
+    // past the list length (a list longer than the grid would be wrong, so bound by the chunk)
+    const uint32_t duos = (c.count + 1) / 2;
+    int st = P.R == 15 ? launch_strip<15>(B, stream, r, duos, true, true)
+                       : launch_strip<16>(B, stream, r, duos, true, true);
     if (st) return st;
   }
   // leftovers: exact column-major kernel over the last list
   ExactArgs<int> e;
   e.cv = cv; e.mode = B.mode; e.V = B.V; e.del = (int)B.del; e.ext = (int)B.ext;
-  e.matrix = B.d_mati.p; e.hcol = B.d_hcol_i.p; e.hrows = c.m_max + 1; e.D = B.d_D.p; e.dl = dl; e.fo = fo;
+  e.matrix = B.d_mati.p; e.hcol = B.hcol_i(); e.hrows = c.m_max + 1; e.D = B.Dp(); e.dl = dl; e.fo = fo;
   e.H_out = nullptr; e.D_out = nullptr;
-  e.list = lists[kRedoPasses & 1]; e.list_count = counters + kRedoPasses;
-  fill_exact_kernel<int><<<(c.count + 127) / 128, 128, (size_t)B.V * B.V * sizeof(int), B.stream>>>(e);
+  e.list = P.lists[kRedoPasses & 1]; e.list_count = P.counters + kRedoPasses;
+  fill_exact_kernel<int><<<(c.count + 127) / 128, 128, (size_t)B.V * B.V * sizeof(int), stream>>>(e);
   ALNR_LAUNCHED();
   return ALNR_OK;
 }

@@ -213,3 +213,170 @@ static __global__ void __launch_bounds__(kTraceBlock) traceback_coop_kernel(Trac
 }
 
 }  // namespace alnr
+
+namespace alnr {
+
+// ---- compact output for batches of equal-length short pairs (identity pair order) -----------
+// Three launches: (A) one thread per pair chases the directions and stores its 2-bit move string
+// in global memory, (S) a single-pass chained scan turns the alignment lengths into offsets —
+// alignment i starts at base + sum of aln_len of the chunk's earlier pairs — and (B) each warp
+// expands 32 move strings into the packed output.  The chunk's alignments are back to back, so
+// the device->host copy moves only the bytes that exist.
+
+// (A) mvg[w * stride + slot]; writes aln_len (0 for rejected pairs) and coords.
+static __global__ void __launch_bounds__(128) trace_moves_kernel(TraceArgs a, uint32_t *mvg, uint32_t stride) {
+  const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+  if (slot >= a.cv.count) return;
+  const uint32_t pair = a.cv.first + slot;
+  const bool glob = a.mode == 0;
+  const uint32_t rpw = a.dl.rows_per_word;
+  if (a.fo.status[pair] != 0) {
+    a.to.aln_len[pair] = 0;
+    if (a.to.coords) for (int k = 0; k < 4; ++k) a.to.coords[4 * (size_t)pair + k] = 0;
+    return;
+  }
+  const uint32_t n = (uint32_t)(a.cv.q_off[pair + 1] - a.cv.q_off[pair]);
+  const uint32_t m = (uint32_t)(a.cv.t_off[pair + 1] - a.cv.t_off[pair]);
+  const uint32_t sy = a.fo.start[2 * (size_t)pair], sx = a.fo.start[2 * (size_t)pair + 1];
+  uint32_t cy = sy, cx = sx, acc = 0, K = 0;
+  uint32_t *mv = mvg + slot;
+  for (;;) {
+    int d;
+    if (cy == 0 || cx == 0) {
+      if (!glob || (cy == 0 && cx == 0)) d = DIR_BEGINNING;
+      else d = (cy == 0) ? DIR_LEFT : DIR_TOP;
+    } else {
+      const uint32_t w = a.D[a.dl.word(slot, (cy - 1) / rpw, cx - 1)];
+      d = a.dl.get(w, (cy - 1) % rpw);
+    }
+    if (d == DIR_BEGINNING) break;
+    acc |= (uint32_t)d << (2 * (K & 15));
+    ++K;
+    if ((K & 15) == 0) { mv[(size_t)((K >> 4) - 1) * stride] = acc; acc = 0; }
+    if (d != DIR_LEFT) --cy;
+    if (d != DIR_TOP) --cx;
+  }
+  if (K & 15) mv[(size_t)(K >> 4) * stride] = acc;
+  a.to.aln_len[pair] = K + 1;
+  if (a.to.coords) {
+    uint64_t *c = a.to.coords + 4 * (size_t)pair;
+    if (glob) { c[0] = 1; c[1] = n; c[2] = 1; c[3] = m; }
+    else { c[0] = cx + 1; c[1] = sx + 1; c[2] = cy + 1; c[3] = sy + 1; }
+  }
+}
+
+// (S) aln_off[first + i] = base + sum_{j<i} aln_len[first + j]; *total = sum of all.
+// Single pass: tiles of 1024 pairs are taken in arrival order (ticket), every tile publishes a
+// 64-bit descriptor (flag 1 = its own sum, 2 = inclusive prefix; low 62 bits = value) and warp 0
+// looks back 32 descriptors at a time.  desc[0] is the ticket, desc[1..] the tiles; all zeroed.
+constexpr int kScanBlock = 256, kScanItems = 4;
+
+static __global__ void __launch_bounds__(kScanBlock) scan_lengths_kernel(const uint32_t *len, uint64_t *off,
+                                                                         uint32_t first, uint32_t count, uint64_t base,
+                                                                         unsigned long long *descbuf, uint64_t *total) {
+  __shared__ uint32_t s_wsum[kScanBlock / 32], s_tile;
+  __shared__ unsigned long long s_excl;
+  const uint32_t tid = threadIdx.x, lane = tid & 31;
+  if (tid == 0) s_tile = atomicAdd(reinterpret_cast<uint32_t *>(descbuf), 1u);
+  __syncthreads();
+  const uint32_t tile = s_tile;
+  volatile unsigned long long *desc = descbuf + 1;
+  const uint32_t i0 = (tile * kScanBlock + tid) * kScanItems;
+  uint32_t v[kScanItems], tsum = 0;
+#pragma unroll
+  for (int k = 0; k < kScanItems; ++k) { v[k] = (i0 + k < count) ? len[first + i0 + k] : 0u; tsum += v[k]; }
+  uint32_t inc = tsum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t u = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= (uint32_t)o) inc += u;
+  }
+  if (lane == 31) s_wsum[tid >> 5] = inc;
+  __syncthreads();
+  uint32_t woff = 0, T = 0;
+#pragma unroll
+  for (int w = 0; w < kScanBlock / 32; ++w) { if ((uint32_t)w < (tid >> 5)) woff += s_wsum[w]; T += s_wsum[w]; }
+  if (tid < 32) {
+    const unsigned long long vmask = (1ull << 62) - 1;
+    unsigned long long excl = 0;
+    if (tile > 0) {
+      if (tid == 0) desc[tile] = (1ull << 62) | T;
+      int hi = (int)tile - 1;
+      for (;;) {
+        const int j = hi - (int)tid;
+        unsigned long long d = 2ull << 62;  // before tile 0: an empty inclusive prefix
+        if (j >= 0) { do { d = desc[j]; } while ((d >> 62) == 0); }
+        const uint32_t pfx = __ballot_sync(0xffffffffu, (d >> 62) == 2);
+        const int stop = pfx ? __ffs(pfx) - 1 : 31;
+        unsigned long long s = ((int)tid <= stop) ? (d & vmask) : 0ull;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        excl += s;
+        if (pfx) break;
+        hi -= 32;
+      }
+    }
+    if (tid == 0) {
+      desc[tile] = (2ull << 62) | (excl + T);
+      s_excl = excl;
+      if (tile + 1 == gridDim.x) *total = excl + T;
+    }
+  }
+  __syncthreads();
+  uint64_t o = base + s_excl + woff + (inc - tsum);
+#pragma unroll
+  for (int k = 0; k < kScanItems; ++k) {
+    if (i0 + k < count) off[first + i0 + k] = o;
+    o += v[k];
+  }
+}
+
+// (B) each warp expands the move strings of 32 consecutive pairs: 32 moves at a time, symbol
+// positions by ballot/popc prefix counts, 32 consecutive output bytes per store.  The reference
+// seeds the string with the start pair and reverses it (simple/mod.rs:102-105,:129-130): move i
+// lands at aln_off + aln_len - 2 - i, the seed at aln_off + aln_len - 1.
+static __global__ void __launch_bounds__(128) trace_expand_kernel(TraceArgs a, const uint32_t *mvg, uint32_t stride) {
+  const uint32_t lane = threadIdx.x & 31;
+  const uint32_t wslot = (blockIdx.x * blockDim.x + threadIdx.x) & ~31u;  // first slot of this warp
+  if (wslot >= a.cv.count) return;
+  const uint32_t ltmask = (1u << lane) - 1u;
+  // lane l preloads pair wslot + l
+  uint32_t my_len = 0, my_sy = 0, my_sx = 0;
+  uint64_t my_off = 0;
+  if (wslot + lane < a.cv.count) {
+    const uint32_t pair = a.cv.first + wslot + lane;
+    my_len = a.to.aln_len[pair];
+    my_off = a.to.aln_off[pair];
+    my_sy = a.fo.start[2 * (size_t)pair];
+    my_sx = a.fo.start[2 * (size_t)pair + 1];
+  }
+  for (uint32_t pi = 0; pi < 32; ++pi) {
+    const uint32_t L = __shfl_sync(0xffffffffu, my_len, pi);
+    const uint64_t dst = __shfl_sync(0xffffffffu, my_off, pi);
+    uint32_t cy = __shfl_sync(0xffffffffu, my_sy, pi), cx = __shfl_sync(0xffffffffu, my_sx, pi);
+    if (L == 0) continue;
+    const uint32_t Kp = L - 1;
+    const uint32_t pair = a.cv.first + wslot + pi;
+    const uint8_t *q = a.cv.q + a.cv.q_off[pair], *t = a.cv.t + a.cv.t_off[pair];
+    const uint32_t *mv = mvg + wslot + pi;
+    const uint64_t end = dst + L;
+    if (lane == 0) { a.to.q_aln[end - 1] = q[cx - 1]; a.to.t_aln[end - 1] = t[cy - 1]; }
+    for (uint32_t b0 = 0; b0 < Kp; b0 += 32) {
+      const uint32_t i = b0 + lane;
+      const bool valid = i < Kp;
+      const uint32_t code = valid ? (mv[(size_t)(i >> 4) * stride] >> (2 * (i & 15))) & 3u : 3u;
+      const bool cq = valid && code != DIR_TOP, ct = valid && code != DIR_LEFT;
+      const uint32_t bq = __ballot_sync(0xffffffffu, cq), bt = __ballot_sync(0xffffffffu, ct);
+      if (valid) {
+        const uint32_t xi = cx - __popc(bq & ltmask), yi = cy - __popc(bt & ltmask);
+        const uint64_t pos = end - 2 - i;
+        a.to.q_aln[pos] = cq ? q[xi - 1] : (uint8_t)kBlank;
+        a.to.t_aln[pos] = ct ? t[yi - 1] : (uint8_t)kBlank;
+      }
+      cx -= __popc(bq);
+      cy -= __popc(bt);
+    }
+  }
+}
+
+}  // namespace alnr

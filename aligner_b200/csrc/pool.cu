@@ -33,9 +33,10 @@ cudaError_t pool_alloc(void **p, size_t bytes, size_t *granted) {
   {
     std::lock_guard<std::mutex> g(P.mu);
     auto &fb = P.free_blocks[dev];
+    // best fit: an exact-size block if there is one (repeated calls of one shape then always hit),
+    // else the smallest larger block unless it is wastefully large
     auto it = fb.lower_bound(need);
-    // reuse a cached block unless it is wastefully large
-    if (it != fb.end() && it->first <= need + need / 2 + (8u << 20)) {
+    if (it != fb.end() && it->first <= need + need / 4 + (8u << 20)) {
       *p = it->second;
       *granted = it->first;
       fb.erase(it);

@@ -10,9 +10,13 @@ bool strip_eligible(const alnr_batch_impl &B, double value_bound);
 uint32_t d_rows_per_word(const alnr_batch_impl &B, uint32_t m);
 // one-time per-batch preparation (packed sequences, profile table).
 int strip_prepare(alnr_batch_impl &B);
-// enqueue the fill of one chunk (+ exact re-runs of pairs whose speculation failed).
-int strip_run_chunk(alnr_batch_impl &B, const Chunk &c, const ChunkView &cv, const DLayout &dl,
+// phase 1 (B.stream): pack the chunk's sequences and run the speculative main pass.
+int strip_main_pass(alnr_batch_impl &B, const Chunk &c, const ChunkView &cv, const DLayout &dl,
                     const FillOut &fo);
+// phase 2 (B.s2; local mode with del != ext only): re-run passes over the fail list and the exact
+// column-major kernel for pairs that never settle.
+int strip_rerun_passes(alnr_batch_impl &B, const Chunk &c, const ChunkView &cv, const DLayout &dl,
+                       const FillOut &fo);
 
 // diagnostic: pairs on the re-run list after pass 0..3, summed over chunks (synchronises).
 int strip_fail_counts(alnr_batch_impl &B, uint64_t out[4]);

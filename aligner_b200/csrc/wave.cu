@@ -31,11 +31,11 @@ int wave_run_pair(alnr_batch_impl &B, const Chunk &c, const DLayout &dl, const F
   a.del = (int)B.del; a.ext = (int)B.ext; a.local = B.mode == ALNR_LOCAL;
   a.TW = TW;
   a.tile_rows = (a.m + TH - 1) / TH; a.tile_cols = (a.n + TW - 1) / TW;
-  int *base = B.d_hcol_i.p;
+  int *base = B.hcol_i();
   a.rowbuf = base; a.colbuf = base + (a.n + 1); a.corner = a.colbuf + (a.m + 1);
   a.corner_out = a.corner + a.tile_rows;
   a.best = reinterpret_cast<unsigned long long *>(base + (((size_t)(a.n + 1) + (a.m + 1) + a.tile_rows + 1 + 1) / 2 * 2));
-  a.Dbytes = reinterpret_cast<uint8_t *>(B.d_D.p);
+  a.Dbytes = reinterpret_cast<uint8_t *>(B.Dp());
   a.ncols = dl.ncols;
   a.diag = 0;
   const uint32_t mx = std::max(std::max(a.n, a.m) + 1, a.tile_rows);

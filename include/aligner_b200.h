@@ -118,10 +118,12 @@ typedef struct {
 } alnr_batch;
 
 /* Caller-provided output arrays (host memory; pinned memory makes copies faster).
- * Any pointer may be NULL to skip that output.  Alignment i is written into the slot
- * [slot_off(i), slot_off(i) + n_i + m_i + 1) of q_aln / t_aln with
- * slot_off(i) = q_off[i] + t_off[i] + i, RIGHT-aligned: it starts at aln_off[i] and has
- * aln_len[i] symbols.  q_aln/t_aln therefore need q_off[count] + t_off[count] + count bytes. */
+ * Any pointer may be NULL to skip that output.  Alignment i occupies
+ * [aln_off[i], aln_off[i] + aln_len[i]) of q_aln / t_aln; aln_off is authoritative.  q_aln/t_aln
+ * need q_off[count] + t_off[count] + count bytes (the reference's worst case, n_i + m_i + 1 per
+ * pair); bytes outside the alignments are unspecified.  Batches of equal-length short pairs are
+ * written back to back per chunk (only the bytes that exist cross PCIe); other batches put
+ * alignment i right-aligned into its own slot starting at q_off[i] + t_off[i] + i. */
 typedef struct {
   double *f;           /* [count] */
   double *corner;      /* [count] */
