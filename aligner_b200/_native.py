@@ -19,6 +19,7 @@ STATUS_NAMES = {
 }
 GLOBAL, LOCAL = 0, 1
 NUM_AUTO, NUM_I16X2, NUM_I32, NUM_F64 = 0, 1, 2, 3
+FITNESS_BLOCK = 256
 
 u8p = C.POINTER(C.c_uint8)
 u32p = C.POINTER(C.c_uint32)
@@ -82,6 +83,8 @@ SIGNATURES = {
                                        C.POINTER(HeuristicOut)]),
     "alnr_matrix_search": (C.c_int, [C.POINTER(Params), C.POINTER(Batch), f64p, C.c_uint32, C.c_double,
                                      C.c_double, f64p, f64p, u32p, f64p, f64p, i32p]),
+    "alnr_fitness_block_sums": (C.c_int, [f64p, i32p, C.c_uint64, C.c_uint32, f64p]),
+    "alnr_fitness_from_blocks": (C.c_int, [f64p, C.c_uint64, C.c_uint32, f64p]),
     "alnr_measure_int_peak": (C.c_int, [C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "alnr_measure_fp64_peak": (C.c_int, [C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "alnr_host_alloc": (C.c_void_p, [C.c_uint64]),

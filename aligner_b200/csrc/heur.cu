@@ -233,10 +233,43 @@ extern "C" int alnr_heuristic_batch(const alnr_params *p, const alnr_batch *b,
   return ALNR_OK;
 }
 
+// Fitness reduction in a FIXED order so that the f64 sums do not depend on how many GPUs shared
+// the pairs: pairs are cut into blocks of ALNR_FITNESS_BLOCK consecutive pairs (global pair
+// index), block_sums[b][k] adds f(pair, k) over the block in pair order, and fitness[k] adds the
+// blocks in block order.  A shard that starts on a block boundary produces its blocks exactly;
+// the ranks exchange them (every block has one owner, so an all-reduce that adds zeros is exact).
+extern "C" int alnr_fitness_block_sums(const double *f_grid, const int32_t *status_grid, uint64_t n_pairs,
+                                       uint32_t n_matrices, double *block_sums) {
+  if (!f_grid || !block_sums || n_matrices == 0) return ALNR_INVALID_ARGUMENT;
+  const uint64_t K = n_matrices, nb = (n_pairs + ALNR_FITNESS_BLOCK - 1) / ALNR_FITNESS_BLOCK;
+  for (uint64_t b = 0; b < nb; ++b) {
+    double *out = block_sums + b * K;
+    for (uint64_t k = 0; k < K; ++k) out[k] = 0.0;
+    const uint64_t lo = b * ALNR_FITNESS_BLOCK, hi = std::min<uint64_t>(lo + ALNR_FITNESS_BLOCK, n_pairs);
+    for (uint64_t i = lo; i < hi; ++i)
+      for (uint64_t k = 0; k < K; ++k) {
+        if (status_grid && status_grid[i * K + k] != 0) continue;  // items on which the reference panics
+        out[k] = out[k] + f_grid[i * K + k];
+      }
+  }
+  return ALNR_OK;
+}
+
+extern "C" int alnr_fitness_from_blocks(const double *block_sums, uint64_t n_blocks, uint32_t n_matrices,
+                                        double *fitness) {
+  if (!block_sums || !fitness) return ALNR_INVALID_ARGUMENT;
+  for (uint64_t k = 0; k < n_matrices; ++k) {
+    double acc = 0.0;
+    for (uint64_t b = 0; b < n_blocks; ++b) acc = acc + block_sums[b * n_matrices + k];
+    fitness[k] = acc;
+  }
+  return ALNR_OK;
+}
+
 // Outer search (dispatcher/handlers.rs:193-251 + node/main.rs:61-74 + the arg-best of
 // repository/queries.rs:74-80, taken as a MAXIMUM — the reference's ascending sort is a defect):
-// every pair under every candidate matrix, fitness[k] = sum over pairs of f(pair, k) added in
-// pair order (fixed, so the f64 sum is reproducible), best_k[pair] = first k with the largest f.
+// every pair under every candidate matrix, fitness[k] = sum over pairs of f(pair, k) in the fixed
+// blocked order above, best_k[pair] = first k with the largest f.
 extern "C" int alnr_matrix_search(const alnr_params *p, const alnr_batch *b, const double *matrices,
                                   uint32_t n_matrices, double kd, double r_squared,
                                   const double *frequencies, double *fitness, uint32_t *best_k,
@@ -253,14 +286,19 @@ extern "C" int alnr_matrix_search(const alnr_params *p, const alnr_batch *b, con
   alnr_heuristic_out out{fg, nullptr, sg, nullptr, nullptr};
   int st = alnr_heuristic_batch(p, b, &it, &out);
   if (st) return st;
-  for (uint64_t k = 0; k < K; ++k) fitness[k] = 0.0;
+  // fitness in the fixed blocked order (see alnr_fitness_block_sums): identical for 1 or N GPUs
+  const uint64_t nb = (P + ALNR_FITNESS_BLOCK - 1) / ALNR_FITNESS_BLOCK;
+  std::vector<double> bs(nb * K);
+  st = alnr_fitness_block_sums(fg, sg, P, n_matrices, bs.data());
+  if (st) return st;
+  st = alnr_fitness_from_blocks(bs.data(), nb, n_matrices, fitness);
+  if (st) return st;
   for (uint64_t i = 0; i < P; ++i) {
     uint32_t bk = 0;
     double bf = -INFINITY;
     for (uint64_t k = 0; k < K; ++k) {
-      if (sg[i * K + k] != 0) continue;  // items on which the reference panics contribute nothing
+      if (sg[i * K + k] != 0) continue;
       const double f = fg[i * K + k];
-      fitness[k] = fitness[k] + f;
       if (f > bf) { bf = f; bk = (uint32_t)k; }
     }
     if (best_k) best_k[i] = bk;

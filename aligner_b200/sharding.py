@@ -1,0 +1,144 @@
+"""Multi-GPU layer: one process per GPU, independent shards, no data-path collective.
+
+The reference spreads its work as one stateless job per (pair, matrix) item over Kafka workers
+(aligner-web/src/bin/node/main.rs:61-74; dispatcher/handlers.rs:193-251).  Here every rank takes a
+contiguous range of pair indices; batched alignment needs only a final gather of the results,
+and the matrix search needs ONE reduction, of the fitness vector (``torch.distributed`` over NCCL
+on GPUs, gloo in the CPU tests).  The reduction is made in a fixed blocked order
+(``alnr_fitness_block_sums``) so the f64 sums are bit-identical for every number of GPUs.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _native as N
+from .batch import PackedPairs, align_batch
+from .heuristic import heuristic_batch
+
+BLOCK = N.FITNESS_BLOCK
+
+
+def shard_bounds(weights, world, align=1):
+    """Cut ``len(weights)`` consecutive items into ``world`` contiguous ranges of nearly equal total
+    weight (balanced by sum of m*n); every boundary is a multiple of ``align``.
+    Returns world+1 boundaries."""
+    w = np.asarray(weights, dtype=np.float64)
+    count = len(w)
+    cum = np.concatenate([[0.0], np.cumsum(w)])
+    bounds = [0]
+    for r in range(1, world):
+        target = cum[-1] * r / world
+        i = int(np.searchsorted(cum, target, side="left"))
+        i = int(round(i / align)) * align
+        bounds.append(max(min(i, count // align * align), bounds[-1]))
+    bounds.append(count)
+    return bounds
+
+
+def shard_range(count, rank, world, weights=None, align=1):
+    """[lo, hi) of rank ``rank``."""
+    b = shard_bounds(np.ones(count) if weights is None else weights, world, align)
+    return b[rank], b[rank + 1]
+
+
+def slice_pairs(pairs, lo, hi):
+    """Pairs [lo, hi) of a PackedPairs as a new PackedPairs (views, offsets rebased)."""
+    q0, q1 = int(pairs.q_off[lo]), int(pairs.q_off[hi])
+    t0, t1 = int(pairs.t_off[lo]), int(pairs.t_off[hi])
+    return PackedPairs(pairs.q[q0:q1], pairs.q_off[lo:hi + 1] - np.uint64(q0),
+                       pairs.t[t0:t1], pairs.t_off[lo:hi + 1] - np.uint64(t0))
+
+
+def _dist():
+    import torch.distributed as dist
+    return dist if dist.is_available() and dist.is_initialized() else None
+
+
+def _rank_world():
+    d = _dist()
+    return (d.get_rank(), d.get_world_size()) if d else (0, 1)
+
+
+def fitness_block_sums(f_grid, status_grid=None):
+    """alnr_fitness_block_sums: [ceil(P/BLOCK), K] partial sums of a local f grid (pure host math)."""
+    f = np.ascontiguousarray(f_grid, dtype=np.float64)
+    P, K = f.shape
+    st = None if status_grid is None else np.ascontiguousarray(status_grid, dtype=np.int32)
+    out = np.zeros(((P + BLOCK - 1) // BLOCK, K), dtype=np.float64)
+    N.check(N.lib().alnr_fitness_block_sums(f.ctypes.data_as(N.f64p),
+                                            st.ctypes.data_as(N.i32p) if st is not None else N.i32p(),
+                                            P, K, out.ctypes.data_as(N.f64p)))
+    return out
+
+
+def fitness_from_blocks(block_sums):
+    b = np.ascontiguousarray(block_sums, dtype=np.float64)
+    out = np.zeros(b.shape[1], dtype=np.float64)
+    N.check(N.lib().alnr_fitness_from_blocks(b.ctypes.data_as(N.f64p), b.shape[0], b.shape[1],
+                                             out.ctypes.data_as(N.f64p)))
+    return out
+
+
+def reduce_fitness(local_blocks, first_block, total_blocks, device=None):
+    """The one collective of the search: every rank contributes the blocks it owns to a zero
+    [total_blocks, K] tensor, one all-reduce(SUM) (each block has a single owner, so adding the
+    other ranks' zeros is exact), then every rank adds the blocks in block order."""
+    import torch
+    K = local_blocks.shape[1]
+    full = np.zeros((total_blocks, K), dtype=np.float64)
+    full[first_block:first_block + local_blocks.shape[0]] = local_blocks
+    d = _dist()
+    if d is not None and d.get_world_size() > 1:
+        t = torch.from_numpy(full)
+        if device is not None:
+            t = t.to(device)
+        d.all_reduce(t, op=d.ReduceOp.SUM)
+        full = t.cpu().numpy()
+    return fitness_from_blocks(full)
+
+
+def matrix_search_sharded(pairs, matrices, del_, ext, kd, r_squared, frequencies, device=-1,
+                          collective_device=None):
+    """C5 on N ranks: shard the PAIRS on fitness-block boundaries (balanced by sum of n*m), every
+    rank runs the heuristic loop for its pairs under all K candidate matrices on its own GPU, the
+    fitness vector is reduced across ranks.  Returns (fitness[K] identical on every rank,
+    (lo, hi), best_k[lo:hi], best_f[lo:hi], f_grid[lo:hi], status[lo:hi])."""
+    rank, world = _rank_world()
+    mats = np.ascontiguousarray(matrices, dtype=np.float64)
+    K = mats.shape[0]
+    P = pairs.count
+    cells = np.diff(pairs.q_off).astype(np.float64) * np.diff(pairs.t_off).astype(np.float64)
+    lo, hi = shard_range(P, rank, world, cells, align=BLOCK)
+    total_blocks = (P + BLOCK - 1) // BLOCK
+    if hi > lo:
+        res = heuristic_batch(slice_pairs(pairs, lo, hi), mats, del_, ext, kd, r_squared,
+                              np.ascontiguousarray(frequencies[lo:hi]), want_matrices=False, device=device)
+        f = res.f.reshape(hi - lo, K)
+        st = res.status.reshape(hi - lo, K)
+        blocks = fitness_block_sums(f, st)
+    else:
+        f = np.zeros((0, K))
+        st = np.zeros((0, K), dtype=np.int32)
+        blocks = np.zeros((0, K))
+    fitness = reduce_fitness(blocks, lo // BLOCK, total_blocks, collective_device)
+    masked = np.where(st == 0, f, -np.inf)
+    best_k = masked.argmax(axis=1).astype(np.uint32) if hi > lo else np.zeros(0, dtype=np.uint32)
+    best_f = masked.max(axis=1) if hi > lo else np.zeros(0)
+    return fitness, (lo, hi), best_k, best_f, f, st
+
+
+def align_batch_sharded(mode, pairs, matrix, del_, ext, device=-1, gather=True):
+    """C3 on N ranks: this rank aligns its contiguous range of pairs (balanced by sum of n*m) on its
+    own GPU; no collective on the data path.  With ``gather`` rank 0 receives every rank's
+    (lo, hi, BatchResult) in rank order (``gather_object``), the other ranks get their own only."""
+    rank, world = _rank_world()
+    cells = np.diff(pairs.q_off).astype(np.float64) * np.diff(pairs.t_off).astype(np.float64)
+    lo, hi = shard_range(pairs.count, rank, world, cells)
+    res = align_batch(mode, slice_pairs(pairs, lo, hi), matrix, del_, ext, device=device)
+    mine = (lo, hi, res)
+    d = _dist()
+    if not gather or d is None or world == 1:
+        return [mine]
+    out = [None] * world if rank == 0 else None
+    d.gather_object(mine, out, dst=0)
+    return out if rank == 0 else [mine]

@@ -187,12 +187,24 @@ int alnr_heuristic_batch(const alnr_params *p, const alnr_batch *b, const alnr_h
 
 /* The outer search the web layer runs through Kafka + MariaDB (dispatcher/handlers.rs:193-251,
  * node/main.rs:61-74): all pairs x all candidate matrices.  fitness[k] = sum_pairs f(pair, k)
- * (added in pair order), best_k/best_f per pair (first maximum); f_grid/status_grid optional
+ * (fixed blocked order, see alnr_fitness_block_sums), best_k/best_f per pair (first maximum); f_grid/status_grid optional
  * [pairs * n_matrices]. */
 int alnr_matrix_search(const alnr_params *p, const alnr_batch *b, const double *matrices,
                        uint32_t n_matrices, double kd, double r_squared, const double *frequencies,
                        double *fitness, uint32_t *best_k, double *best_f, double *f_grid,
                        int32_t *status_grid);
+
+/* Fixed-order fitness reduction, the one step of the search that crosses GPUs.
+ * block_sums[b * n_matrices + k] = sum of f_grid[i * n_matrices + k] over the pairs i of block b
+ * (ALNR_FITNESS_BLOCK consecutive pairs, added in pair order; status != 0 items skipped).
+ * fitness[k] = sum over blocks in block order.  alnr_matrix_search uses exactly this order, so a
+ * search sharded over N GPUs on block boundaries (blocks exchanged with one NCCL all-reduce,
+ * every block owned by one rank) gives bit-identical fitness for every N. */
+#define ALNR_FITNESS_BLOCK 256
+int alnr_fitness_block_sums(const double *f_grid, const int32_t *status_grid, uint64_t n_pairs,
+                            uint32_t n_matrices, double *block_sums);
+int alnr_fitness_from_blocks(const double *block_sums, uint64_t n_blocks, uint32_t n_matrices,
+                             double *fitness);
 
 /* Roofline denominators measured on the device: arithmetic INT32 ops/s (an op = one
  * 32-bit add / max / logic op / multiply-add lane) of alu-pipe-only chains and of a 1:1

@@ -1,0 +1,65 @@
+"""Worker for tests/test_sharding.py: one rank of a world_size-N gloo job (launched by
+torch.distributed.run on 127.0.0.1).  mode "fitness": synthetic f grid, host math only (CPU test);
+mode "search" / "batch": the real sharded calls, every rank on cuda:0 (GPU test on a 1-GPU box)."""
+import os
+import pickle
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in (ROOT, os.path.join(ROOT, "tests")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import torch.distributed as dist  # noqa: E402
+
+import aligner_b200 as ab  # noqa: E402
+from aligner_b200 import sharding as S  # noqa: E402
+from aligner_b200 import workloads as W  # noqa: E402
+
+
+def synthetic_grid(P, K, seed=11):
+    rng = np.random.default_rng(seed)
+    f = rng.normal(50.0, 17.0, (P, K)) * rng.choice([1e-3, 1.0, 1e6], (P, K))
+    st = (rng.random((P, K)) < 0.03).astype(np.int32) * 11
+    return f, st
+
+
+def main():
+    mode, out_path = sys.argv[1], sys.argv[2]
+    dist.init_process_group("gloo")
+    rank, world = dist.get_rank(), dist.get_world_size()
+    result = None
+    if mode == "fitness":
+        P, K = int(sys.argv[3]), int(sys.argv[4])
+        f, st = synthetic_grid(P, K)
+        w = np.arange(P, dtype=np.float64) % 7 + 1
+        lo, hi = S.shard_range(P, rank, world, w, align=S.BLOCK)
+        blocks = S.fitness_block_sums(f[lo:hi], st[lo:hi]) if hi > lo else np.zeros((0, K))
+        fit = S.reduce_fitness(blocks, lo // S.BLOCK, (P + S.BLOCK - 1) // S.BLOCK)
+        result = {"fitness": fit, "range": (lo, hi)}
+    elif mode == "search":
+        P, K = int(sys.argv[3]), int(sys.argv[4])
+        pairs = W.protein_pairs(0, P, 40, 70)
+        mats = W.candidate_matrices(K)
+        freqs = W.pair_frequencies(pairs, 24)
+        fit, (lo, hi), bk, bf, f, st = S.matrix_search_sharded(pairs, mats, 5, 5, -1.0, 576.0, freqs, device=0)
+        result = {"fitness": fit, "range": (lo, hi), "best_k": bk, "f": f}
+    elif mode == "batch":
+        P = int(sys.argv[3])
+        pairs = W.dna_read_batch(0, P, n=150)
+        got = S.align_batch_sharded(ab.LOCAL, pairs, ab.dna_matrix(5, -4), 10, 2, device=0)
+        if rank == 0:
+            result = [(lo, hi, r.f, r.coords, r.aln_len) for lo, hi, r in got]
+    gathered = [None] * world if rank == 0 else None
+    dist.gather_object(result, gathered, dst=0)
+    if rank == 0:
+        with open(out_path, "wb") as fh:
+            pickle.dump(gathered, fh)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
