@@ -119,7 +119,7 @@ int alnr_align_batch(const alnr_params *p, const alnr_batch *b, alnr_batch_out *
   // uniform batches stream chunk by chunk (copies overlap compute); init() finds out which
   B.resident = false;
   B.ramp = true;
-  B.max_chunk = 600000;  // ~3 waves of the strip kernel: short pipeline fill / drain
+  B.max_chunk = 620000;  // ~4 waves of the strip kernel: short pipeline fill / drain
   static const bool timing = std::getenv("ALNR_TIMING") != nullptr;
   const auto t0 = std::chrono::steady_clock::now();
   int st = B.init(p, b, false);

@@ -80,7 +80,6 @@ int alnr_batch_impl::classify() {
   return ALNR_INVALID_ARGUMENT;
 }
 
-static const uint64_t kStripWavePairs = 148ull * 10 * 128;
 
 static __global__ void uniform_offsets_kernel(uint64_t *qo, uint64_t *to, uint64_t n_off, uint64_t n, uint64_t m) {
   const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -126,6 +125,7 @@ int alnr_batch_impl::plan_chunks(const uint64_t *q_off, const uint64_t *t_off) {
     for (uint64_t s = count; s-- > 0;) { uint32_t m, n; dims(s, m, n); mx = std::max(mx, n); nsuf[s] = mx; }
   }
   const uint64_t budget = scratch_budget_bytes() / 2;  // two parity copies of the chunk scratch
+  const uint64_t kStripWavePairs = numeric == ALNR_NUM_I16X2 ? strip_wave_pairs() : 1;
   const size_t num_sz = numeric == ALNR_NUM_F64 ? 8 : 4;
   uint64_t s = 0;
   while (s < count) {
@@ -139,8 +139,8 @@ int alnr_batch_impl::plan_chunks(const uint64_t *q_off, const uint64_t *t_off) {
     uint64_t c = std::min<uint64_t>(groups * 32, count - s);
     if (c < count - s) c = std::max<uint64_t>(c / 64 * 64, 32);  // keep duo-kernel warps whole
     if (c > max_chunk) c = max_chunk;
-    // whole waves of the strip kernel (148 SMs x 10 resident blocks x 128 pairs): kernels of one
-    // stream run back to back, so a partly filled last wave is idle time in every chunk
+    // whole waves of the (persistent) strip kernel: every resident block then walks the same
+    // number of virtual blocks and no SM idles at the end of a chunk
     if (numeric == ALNR_NUM_I16X2 && c < count - s && c >= kStripWavePairs) c = c / kStripWavePairs * kStripWavePairs;
     if (ramp && numeric == ALNR_NUM_I16X2 && count > 4 * kStripWavePairs) {
       // streaming call: a one-wave first chunk starts the compute after ~1 ms of copies, a

@@ -52,19 +52,29 @@ int strip_prepare(alnr_batch_impl &B) {
 }
 
 template <int R>
-static int launch_strip(alnr_batch_impl &B, cudaStream_t stream, const StripArgs &a, uint32_t duos, bool local, bool stateful) {
-  const size_t smem = a.hglobal ? 0 : (size_t)a.n * kStripBlock * 4;
-  const unsigned blocks = (duos + kStripBlock - 1) / kStripBlock;
-  if (blocks == 0) return ALNR_OK;
+static int launch_strip(alnr_batch_impl &B, cudaStream_t stream, const StripArgs &a_in, uint32_t duos, bool local, bool stateful) {
+  const size_t smem = a_in.hglobal ? 0 : (size_t)a_in.n * kStripBlock * 4;
+  const unsigned vblocks = (duos + kStripBlock - 1) / kStripBlock;
+  if (vblocks == 0) return ALNR_OK;
+  StripArgs a = a_in;
+  a.vblocks = vblocks;
 #define ALNR_STRIP_LAUNCH(L, S)                                                                   \
   do {                                                                                            \
     static bool attr_done = false;                                                                \
+    static unsigned resident = 0;                                                                 \
     if (!attr_done) {                                                                             \
       ALNR_CUDA(cudaFuncSetAttribute(fill_strip_kernel<R, L, S>,                                  \
                                      cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));   \
+      int occ = 0, sms = 0, dev = 0;                                                              \
+      ALNR_CUDA(cudaGetDevice(&dev));                                                             \
+      ALNR_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));               \
+      ALNR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fill_strip_kernel<R, L, S>,   \
+                                                              kStripBlock, smem));                \
+      resident = (unsigned)std::max(1, occ) * (unsigned)std::max(1, sms);                         \
       attr_done = true;                                                                           \
     }                                                                                             \
-    fill_strip_kernel<R, L, S><<<blocks, kStripBlock, smem, stream>>>(a);                       \
+    const unsigned blocks = a.hglobal ? std::min(vblocks, resident) : vblocks;                    \
+    fill_strip_kernel<R, L, S><<<blocks, kStripBlock, smem, stream>>>(a);                         \
   } while (0)
   if (!local) ALNR_STRIP_LAUNCH(false, false);
   else if (stateful) ALNR_STRIP_LAUNCH(true, true);
@@ -72,6 +82,23 @@ static int launch_strip(alnr_batch_impl &B, cudaStream_t stream, const StripArgs
 #undef ALNR_STRIP_LAUNCH
   ALNR_LAUNCHED();
   return ALNR_OK;
+}
+
+// Pairs one resident wave of the strip kernel processes (SMs x resident blocks x 128): chunk
+// sizes are multiples of it so every persistent block walks the same number of virtual blocks.
+uint32_t strip_wave_pairs() {
+  static uint32_t cached = 0;
+  if (cached) return cached;
+  int occ = 0, sms = 0, dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess ||
+      cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess ||
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fill_strip_kernel<15, true, true>, kStripBlock, 0) !=
+          cudaSuccess) {
+    (void)cudaGetLastError();
+    return 148u * 8u * 2u * kStripBlock;
+  }
+  cached = (uint32_t)std::max(1, occ) * (uint32_t)std::max(1, sms) * 2u * kStripBlock;
+  return cached;
 }
 
 namespace {

@@ -8,6 +8,8 @@ namespace alnr {
 bool strip_eligible(const alnr_batch_impl &B, double value_bound);
 // rows per 32-bit D word for a chunk whose longest target has m rows (<= 16).
 uint32_t d_rows_per_word(const alnr_batch_impl &B, uint32_t m);
+// pairs per resident wave of the strip kernel (chunk sizes are multiples of it).
+uint32_t strip_wave_pairs();
 // one-time per-batch preparation (packed sequences, profile table).
 int strip_prepare(alnr_batch_impl &B);
 // phase 1 (B.stream): pack the chunk's sequences and run the speculative main pass.

@@ -51,12 +51,12 @@ def launches(path):
         a[0] += 1
         a[1] += v
     tot = sum(a[1] for a in agg.values())
-    ours = sum(a[1] for k, a in agg.items() if "alnr::" in k and "peak_" not in k)
+    ours = sum(a[1] for k, a in agg.items() if ("alnr::" in k or "_kernel" in k) and "at::" not in k and "peak_" not in k)
     print("# per-kernel device time (ncu --metrics gpu__time_duration.sum, cold-cache, serialised)")
     print("# share_all = of every launch in the process; share_path = of the alnr:: hot-path kernels only")
     print("%-92s %5s %12s %9s %10s" % ("kernel", "n", "total_ms", "share_all", "share_path"))
     for k, a in sorted(agg.items(), key=lambda kv: -kv[1][1]):
-        path = ("%9.1f%%" % (100 * a[1] / ours)) if ("alnr::" in k and "peak_" not in k) else "         -"
+        path = ("%9.1f%%" % (100 * a[1] / ours)) if (("alnr::" in k or "_kernel" in k) and "at::" not in k and "peak_" not in k) else "         -"
         print("%-92s %5d %12.3f %8.1f%% %s" % (k, a[0], a[1] / 1e6, 100 * a[1] / tot, path))
 
 
