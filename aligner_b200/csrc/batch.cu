@@ -176,7 +176,7 @@ bool alnr_batch_impl::use_warp(uint32_t m) const {
 }
 
 DLayout alnr_batch_impl::layout_dims(uint32_t m, uint32_t n, bool wave) const {
-  if (wave) return DLayout::make(16, m, n, true, 0);
+  if (wave) return DLayout::make_blocked(wave_band_rows(m), m, n);
   if (use_warp(m)) return DLayout::make_skewed(want_matrices ? 8 : warp_pick_rows(m), m, n);
   return DLayout::make(d_rows_per_word(*this, m), m, n, numeric == ALNR_NUM_I16X2);
 }
@@ -485,6 +485,8 @@ int alnr_batch_impl::phase2(size_t ci) {
                                                       d_ctotal.p + ci);
     ALNR_LAUNCHED();
     trace_expand_kernel<<<(c.count + 127) / 128, 128, 0, s2>>>(ta, d_moves.p, stride);
+  } else if (dl.blocked) {
+    traceback_warp_kernel<<<c.count, 32, 0, s2>>>(ta);
   } else if ((size_t)nmw * kTraceBlock * 4 <= 44 * 1024 && to.freq == nullptr) {
     traceback_coop_kernel<<<(c.count + kTraceBlock - 1) / kTraceBlock, kTraceBlock,
                             (size_t)nmw * kTraceBlock * 4, s2>>>(ta, nmw);

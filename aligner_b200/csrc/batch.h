@@ -56,6 +56,7 @@ struct alnr_batch_impl {
   DevBuf<int> d_flags;
   DevBuf<double> d_f, d_corner, d_matd, d_Hout, d_hcol_d;
   DevBuf<int> d_mati, d_hcol_i;
+  DevBuf<int> d_band;           // band pipeline kernel: reduction cells, progress words, band rows
   DevBuf<uint32_t> d_pack;      // packed sequences for the strip kernel
   DevBuf<uint32_t> d_wz;        // warp kernel: [8 counters][fail list][z bits 2*nzw per slot]
   uint64_t rerun_total = 0;

@@ -38,13 +38,21 @@ struct DLayout {
   //   slot * nstrips * (ncols + 31) + ((band * (ncols + 31) + (x-1) + lane) * 32 + lane)
   // -> one 128-byte line per step.  rows_per_word = rows per lane.
   uint32_t skewed;
+  // Address map 4, "blocked" (band pipeline kernel, kernels_band.cuh; single pair): a word holds
+  // R = rows_per_word rows x C = 16 / R consecutive columns (blocked = C, a power of two): column
+  // (x-1) % C sits at bits [2R * ((x-1) % C), ...), row r at bits [2r, 2r+1] of that field; word
+  // index = strip * ncols + (x-1) / C with strip = (y-1) / R and ncols = words per strip.  A lane
+  // that owns R rows packs C columns into one aligned 32-bit store.
+  uint32_t blocked;
   __host__ __device__ inline uint32_t put(uint32_t code, uint32_t r) const {
     return planes ? (((code & 1u) << r) | ((code >> 1) << (16 + r))) : (code << (2 * r));
   }
-  __host__ __device__ inline uint32_t get(uint32_t w, uint32_t r) const {
+  __host__ __device__ inline uint32_t get(uint32_t w, uint32_t r, uint32_t xm1 = 0) const {
+    if (blocked) return (w >> (2 * rows_per_word * (xm1 & (blocked - 1)) + 2 * r)) & 3u;
     return planes ? (((w >> r) & 1u) | (((w >> (16 + r)) & 1u) << 1)) : ((w >> (2 * r)) & 3u);
   }
   __host__ __device__ inline uint64_t word(uint32_t slot, uint32_t strip, uint32_t xm1) const {
+    if (blocked) return ((uint64_t)slot * nstrips + strip) * ncols + xm1 / blocked;
     if (skewed) {
       const uint32_t band = strip >> 5, lane = strip & 31;
       return (uint64_t)slot * nstrips * (ncols + 31) + (((uint64_t)band * (ncols + 31) + xm1 + lane) * 32ull + lane);
@@ -54,6 +62,7 @@ struct DLayout {
     return (((uint64_t)group * nstrips + strip) * ncols + xm1) * 32ull + lane;
   }
   __host__ __device__ inline uint64_t words_for(uint64_t slots) const {
+    if (blocked) return slots * (uint64_t)nstrips * ncols + 4;
     if (skewed) return slots * (uint64_t)nstrips * (ncols + 31);
     if (contiguous) return slots * (uint64_t)nstrips * ncols + 4;
     return ((slots + 31) / 32) * (uint64_t)nstrips * ncols * 32ull;
@@ -67,6 +76,20 @@ struct DLayout {
     d.contiguous = contig ? 1u : 0u;
     d.planes = planes_opt >= 0 ? (uint32_t)planes_opt : (contig ? 1u : 0u);
     d.skewed = 0;
+    d.blocked = 0;
+    return d;
+  }
+  // band pipeline layout: R rows x 16/R columns per word (R = 1, 2, 4 or 8)
+  static inline DLayout make_blocked(uint32_t R, uint32_t m_max, uint32_t n_max) {
+    DLayout d;
+    const uint32_t C = 16 / R;
+    d.rows_per_word = R;
+    d.nstrips = (m_max + R - 1) / R;
+    d.ncols = (n_max + C - 1) / C;
+    d.contiguous = 1;
+    d.planes = 0;
+    d.skewed = 0;
+    d.blocked = C;
     return d;
   }
   // warp-per-pair layout: R rows per lane, bands of 32 * R rows
@@ -78,6 +101,7 @@ struct DLayout {
     d.contiguous = 0;
     d.planes = 0;
     d.skewed = 1;
+    d.blocked = 0;
     return d;
   }
 };

@@ -100,7 +100,7 @@ static __global__ void __launch_bounds__(128) traceback_kernel(TraceArgs a) {
       else d = (cy == 0) ? DIR_LEFT : DIR_TOP;  // simple/mod.rs:59-67
     } else {
       const uint32_t w = a.D[a.dl.word(slot, (cy - 1) / rpw, cx - 1)];
-      d = a.dl.get(w, (cy - 1) % rpw);
+      d = a.dl.get(w, (cy - 1) % rpw, cx - 1);
     }
     if (d == DIR_BEGINNING) break;
     if (d == DIR_TOP) { emit(kBlank, t[cy - 1]); --cy; }
@@ -153,7 +153,7 @@ static __global__ void __launch_bounds__(kTraceBlock) traceback_coop_kernel(Trac
           else d = (cy == 0) ? DIR_LEFT : DIR_TOP;
         } else {
           const uint32_t w = a.D[a.dl.word(slot, (cy - 1) / rpw, cx - 1)];
-          d = a.dl.get(w, (cy - 1) % rpw);
+          d = a.dl.get(w, (cy - 1) % rpw, cx - 1);
         }
         if (d == DIR_BEGINNING) break;
         acc |= (uint32_t)d << (2 * (K & 15));
@@ -247,7 +247,7 @@ static __global__ void __launch_bounds__(128) trace_moves_kernel(TraceArgs a, ui
       else d = (cy == 0) ? DIR_LEFT : DIR_TOP;
     } else {
       const uint32_t w = a.D[a.dl.word(slot, (cy - 1) / rpw, cx - 1)];
-      d = a.dl.get(w, (cy - 1) % rpw);
+      d = a.dl.get(w, (cy - 1) % rpw, cx - 1);
     }
     if (d == DIR_BEGINNING) break;
     acc |= (uint32_t)d << (2 * (K & 15));
@@ -375,6 +375,103 @@ static __global__ void __launch_bounds__(128) trace_expand_kernel(TraceArgs a, c
       }
       cx -= __popc(bq);
       cy -= __popc(bt);
+    }
+  }
+}
+
+}  // namespace alnr
+
+namespace alnr {
+
+// Traceback of ONE long pair through the "blocked" D layout (band pipeline kernel, 2.5 GB of
+// directions for 10^5 x 10^5 cells): a single dependent chain of ~n+m loads that mostly miss L2.
+// One warp walks the path in lockstep (every lane holds the same (cy, cx)); before each stretch
+// the 32 lanes fetch the words the path is expected to cross in the next 16 strips — two words
+// per strip around the diagonal through the current cell — in one batch of independent loads,
+// and the walk then takes its words from the owning lane by shuffle.  A word that was not
+// predicted (the path drifted by indels) is loaded directly.  Output as traceback_kernel.
+static __global__ void __launch_bounds__(32) traceback_warp_kernel(TraceArgs a) {
+  const uint32_t slot = blockIdx.x, lane = threadIdx.x;
+  if (slot >= a.cv.count) return;
+  const uint32_t pair = a.cv.order ? a.cv.order[a.cv.first + slot] : a.cv.first + slot;
+  const uint32_t sp = a.cv.seq(pair);
+  const uint64_t qo = a.cv.q_off[sp], to = a.cv.t_off[sp];
+  const uint32_t n = (uint32_t)(a.cv.q_off[sp + 1] - qo);
+  const uint32_t m = (uint32_t)(a.cv.t_off[sp + 1] - to);
+  const uint64_t slot_end = qo + to + pair + n + m + 1;
+  if (a.fo.status[pair] != 0) {
+    if (lane == 0) {
+      if (a.to.aln_len) a.to.aln_len[pair] = 0;
+      if (a.to.aln_off) a.to.aln_off[pair] = slot_end;
+      if (a.to.coords) for (int k = 0; k < 4; ++k) a.to.coords[4 * (size_t)pair + k] = 0;
+    }
+    return;
+  }
+  const uint8_t *q = a.cv.q + qo, *t = a.cv.t + to;
+  const bool glob = a.mode == 0;
+  // R and C are powers of two (R * C = 16): shifts and masks instead of divisions on the chain
+  const uint32_t R = a.dl.rows_per_word, C = a.dl.blocked;
+  const uint32_t rsh = __ffs(R) - 1, csh = __ffs(C) - 1, rmask = R - 1, cmask = C - 1;
+  const uint32_t sy = a.fo.start[2 * (size_t)pair], sx = a.fo.start[2 * (size_t)pair + 1];
+  uint32_t cy = sy, cx = sx;
+  uint64_t pos = slot_end;
+  const bool wr = lane == 0 && a.to.q_aln != nullptr && a.to.t_aln != nullptr;
+  auto emit = [&](uint8_t qc, uint8_t tc) {
+    --pos;
+    if (wr) { a.to.q_aln[pos] = qc; a.to.t_aln[pos] = tc; }
+  };
+  emit(q[cx - 1], t[cy - 1]);  // seed (simple/mod.rs:102-105, :213-216)
+  bool done = false;
+  while (!done) {
+    // ---- batch of predicted words: strip base - k, k = 0..15, two words each ---------------
+    uint32_t my_val = 0;
+    const uint32_t base = cy ? (cy - 1) >> rsh : 0;
+    const uint32_t rows_here = cy ? ((cy - 1) & rmask) + 1 : 0;  // rows left in the current strip
+    const int64_t cx0 = cx;                                // column at the start of this batch
+    auto pred_hi = [&](uint32_t k) -> int64_t {           // word column where the path enters strip base - k
+      const int64_t px = cx0 - 1 - (k ? (int64_t)rows_here + (int64_t)(k - 1) * R : 0);
+      return px >= 0 ? (px >> csh) : -1;
+    };
+    {
+      const uint32_t k = lane >> 1;
+      const int64_t wc = pred_hi(k) - (lane & 1);
+      if (cy && cx && k <= base && wc >= 0)
+        my_val = __ldcs(a.D + ((uint64_t)slot * a.dl.nstrips + (base - k)) * a.dl.ncols + (uint64_t)wc);
+    }
+    // ---- walk until the path leaves the 16 predicted strips ---------------------------------
+    uint32_t cur_strip = 0xffffffffu, cur_wc = 0xffffffffu, cur_w = 0;
+    for (;;) {
+      int d;
+      if (cy == 0 || cx == 0) {
+        if (!glob || (cy == 0 && cx == 0)) d = DIR_BEGINNING;
+        else d = (cy == 0) ? DIR_LEFT : DIR_TOP;  // simple/mod.rs:59-67
+      } else {
+        const uint32_t strip = (cy - 1) >> rsh, wc = (cx - 1) >> csh;
+        if (strip != cur_strip || wc != cur_wc) {
+          const uint32_t k = base - strip;
+          if (k >= 16) break;  // next batch
+          const int64_t hi = pred_hi(k);
+          const uint32_t src = 2 * k + (((int64_t)wc == hi) ? 0u : 1u);
+          const uint32_t v = __shfl_sync(0xffffffffu, my_val, src);
+          if ((int64_t)wc == hi || (int64_t)wc == hi - 1) cur_w = v;
+          else cur_w = a.D[((uint64_t)slot * a.dl.nstrips + strip) * a.dl.ncols + wc];  // not predicted
+          cur_strip = strip; cur_wc = wc;
+        }
+        d = (cur_w >> (2 * (((cx - 1) & cmask) << rsh) + 2 * ((cy - 1) & rmask))) & 3u;
+      }
+      if (d == DIR_BEGINNING) { done = true; break; }
+      if (d == DIR_TOP) { emit(kBlank, t[cy - 1]); --cy; }
+      else if (d == DIR_LEFT) { emit(q[cx - 1], kBlank); --cx; }
+      else { emit(q[cx - 1], t[cy - 1]); --cx; --cy; }
+    }
+  }
+  if (lane == 0) {
+    if (a.to.aln_len) a.to.aln_len[pair] = (uint32_t)(slot_end - pos);
+    if (a.to.aln_off) a.to.aln_off[pair] = pos;
+    if (a.to.coords) {
+      uint64_t *c = a.to.coords + 4 * (size_t)pair;
+      if (glob) { c[0] = 1; c[1] = n; c[2] = 1; c[3] = m; }                      // simple/mod.rs:137
+      else { c[0] = cx + 1; c[1] = sx + 1; c[2] = cy + 1; c[3] = sy + 1; }        // :254-257
     }
   }
 }

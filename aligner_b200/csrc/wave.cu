@@ -1,18 +1,21 @@
-// wave.cu — host side of the intra-pair wavefront kernel (kernels_wave.cuh).
+// wave.cu — host side of the intra-pair wavefront path for one long pair: the band pipeline
+// kernel (kernels_band.cuh).
 #include <algorithm>
 #include <cstdlib>
 
-#include "kernels_wave.cuh"
+#include "kernels_band.cuh"
 #include "strip_launch.h"
 #include "wave_launch.h"
 
 namespace alnr {
 
-static const uint64_t kWaveMinCells = 1ull << 24;  // below this the per-thread kernels win
+// One pair at a time on the band pipeline pays off from ~10^6 cells for single-pair calls; in a
+// batch the warp-per-pair kernel runs many pairs side by side, so only very long pairs qualify.
+static const uint64_t kWaveMinCellsSingle = 1ull << 20, kWaveMinCellsBatch = 1ull << 24;
 
 bool wave_eligible(const alnr_batch_impl &B, uint32_t m, uint32_t n) {
   if (B.numeric != ALNR_NUM_I32 || B.want_matrices) return false;
-  if ((uint64_t)m * n < kWaveMinCells) return false;
+  if ((uint64_t)m * n < (B.count <= 4 ? kWaveMinCellsSingle : kWaveMinCellsBatch)) return false;
   if (m >= 0xFFFFFu || n >= 0xFFFFFu) return false;       // arg-max key packs 20-bit coordinates
   if (B.mode == ALNR_LOCAL && B.del != B.ext) return false;  // stateful penalty: columns serialise
   double mag = 0;
@@ -21,44 +24,62 @@ bool wave_eligible(const alnr_batch_impl &B, uint32_t m, uint32_t n) {
   return true;
 }
 
-int wave_run_pair(alnr_batch_impl &B, const Chunk &c, const DLayout &dl, const FillOut &fo) {
-  static const int R = std::getenv("ALNR_WAVE_R8") ? 8 : 4;
-  static const uint32_t TWenv = std::getenv("ALNR_WAVE_TW") ? (uint32_t)std::atoi(std::getenv("ALNR_WAVE_TW")) : 128;
-  const uint32_t TH = 32 * R, TW = std::max(32u, TWenv / 32 * 32);
-  WaveArgs a;
+// Band pipeline (kernels_band.cuh): one persistent launch for the whole pair.
+static int band_run_pair(alnr_batch_impl &B, const Chunk &c, const DLayout &dl, const FillOut &fo) {
+  BandArgs a;
   a.q = B.d_q.p + c.q0; a.t = B.d_t.p + c.t0;
   a.n = c.n_max; a.m = c.m_max; a.V = B.V; a.matrix = B.d_mati.p;
-  a.del = (int)B.del; a.ext = (int)B.ext; a.local = B.mode == ALNR_LOCAL;
-  a.TW = TW;
-  a.tile_rows = (a.m + TH - 1) / TH; a.tile_cols = (a.n + TW - 1) / TW;
-  int *base = B.hcol_i();
-  a.rowbuf = base; a.colbuf = base + (a.n + 1); a.corner = a.colbuf + (a.m + 1);
-  a.corner_out = a.corner + a.tile_rows;
-  a.best = reinterpret_cast<unsigned long long *>(base + (((size_t)(a.n + 1) + (a.m + 1) + a.tile_rows + 1 + 1) / 2 * 2));
-  a.Dbytes = reinterpret_cast<uint8_t *>(B.Dp());
-  a.ncols = dl.ncols;
-  a.diag = 0;
-  const uint32_t mx = std::max(std::max(a.n, a.m) + 1, a.tile_rows);
-  wave_init_kernel<<<(mx + 255) / 256, 256, 0, B.stream>>>(a, TH);
-  ALNR_LAUNCHED();
-  const size_t smem = (size_t)B.V * B.V * 4 + 4 * (size_t)TW;
-  for (uint32_t d = 0; d < a.tile_rows + a.tile_cols - 1; ++d) {
-    a.diag = d;
-    const uint32_t i_lo = d >= a.tile_cols ? d - a.tile_cols + 1 : 0, i_hi = std::min(d, a.tile_rows - 1);
-    const uint32_t tiles = i_hi - i_lo + 1;
-    const unsigned grid = (tiles + 3) / 4;
-    if (a.local) {
-      if (R == 8) fill_wave_kernel<8, true><<<grid, 128, smem, B.stream>>>(a);
-      else fill_wave_kernel<4, true><<<grid, 128, smem, B.stream>>>(a);
-    } else {
-      if (R == 8) fill_wave_kernel<8, false><<<grid, 128, smem, B.stream>>>(a);
-      else fill_wave_kernel<4, false><<<grid, 128, smem, B.stream>>>(a);
-    }
-    ALNR_LAUNCHED();
+  a.del = (int)B.del; a.ext = (int)B.ext;
+  const uint32_t R = dl.rows_per_word, band_rows = 32 * R;
+  a.nbands = (a.m + band_rows - 1) / band_rows;
+  const bool local = B.mode == ALNR_LOCAL;
+  // scratch: [best (8 B)][corner][pad][prog nbands][rows nbands * (n + 1)]
+  const size_t words = 4 + (size_t)a.nbands + (size_t)a.nbands * (a.n + 1);
+  if (B.d_band.n < words) ALNR_CUDA(B.d_band.alloc(words));
+  int *base = B.d_band.p;
+  a.best = reinterpret_cast<unsigned long long *>(base);
+  a.corner_out = base + 2;
+  a.prog = reinterpret_cast<uint32_t *>(base + 4);
+  a.rows = base + 4 + a.nbands;
+  a.D = B.Dp();
+  a.dcols = dl.ncols;
+  static unsigned resident = 0;
+  if (!resident) {
+    int occ0 = 0, occ1 = 0, sms = 0, dev = 0;
+    ALNR_CUDA(cudaGetDevice(&dev));
+    ALNR_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    const size_t smem0 = 32 * 32 * 4;
+    ALNR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ0, fill_band_kernel<4, false>, 32, smem0));
+    ALNR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ1, fill_band_kernel<4, true>, 32, smem0));
+    resident = (unsigned)std::max(1, std::min(occ0, occ1)) * (unsigned)std::max(1, sms);
   }
-  wave_finish_kernel<<<1, 1, 0, B.stream>>>(a, fo, c.wave_pair);
+  band_init_kernel<<<(a.nbands + 255) / 256, 256, 0, B.stream>>>(a);
+  ALNR_LAUNCHED();
+  const unsigned grid = std::min<unsigned>(a.nbands, resident);  // every block must be resident
+  const size_t smem = (size_t)B.V * B.V * 4;
+  if (R == 2) {
+    if (local) fill_band_kernel<2, true><<<grid, 32, smem, B.stream>>>(a);
+    else fill_band_kernel<2, false><<<grid, 32, smem, B.stream>>>(a);
+  } else {
+    if (local) fill_band_kernel<4, true><<<grid, 32, smem, B.stream>>>(a);
+    else fill_band_kernel<4, false><<<grid, 32, smem, B.stream>>>(a);
+  }
+  ALNR_LAUNCHED();
+  band_finish_kernel<<<1, 1, 0, B.stream>>>(a, local ? 1 : 0, fo, c.wave_pair);
   ALNR_LAUNCHED();
   return ALNR_OK;
+}
+
+// rows per lane of the band pipeline: thinner bands = more warps in flight (ALNR_BAND_R overrides)
+uint32_t wave_band_rows(uint32_t m) {
+  static const int env = std::getenv("ALNR_BAND_R") ? std::atoi(std::getenv("ALNR_BAND_R")) : 0;
+  if (env == 2 || env == 4) return (uint32_t)env;
+  (void)m;
+  return 4u;  // measured: 128-row bands beat 64-row bands at 3 x 10^4 and at 10^5 (pipeline fill dominates)
+}
+
+int wave_run_pair(alnr_batch_impl &B, const Chunk &c, const DLayout &dl, const FillOut &fo) {
+  return band_run_pair(B, c, dl, fo);
 }
 
 }  // namespace alnr

@@ -1,8 +1,9 @@
 import sys, os, time
-sys.path.insert(0, "/root/repo")
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, aligner_b200 as ab
 from aligner_b200 import _native as N, workloads as W
-q, t = W.dna_long_pair(100000, seed=4)
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 100000
+q, t = W.dna_long_pair(n, seed=4)
 pairs = ab.PackedPairs.from_lists([q], [t])
 db = ab.DeviceBatch(N.GLOBAL, pairs, ab.dna_matrix(), 8, 8)
 db.run_timed(1)
