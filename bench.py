@@ -27,6 +27,7 @@ for _p in (ROOT, os.path.join(ROOT, "tests")):
 
 METRIC = "GCUPS (cell updates/s) batched SW/NW at 1/2/4/8 B200 vs reference CPU"
 OPS_PER_CELL = 10  # ALU ops per cell update of the full recurrence
+NCU_DRAM_BYTES_PER_CELL = (1.474577e9 + 7.807713e9) / (1e6 * 150 * 150)
 
 
 def parse():
@@ -295,7 +296,11 @@ def main():
                          "ops_per_cell": OPS_PER_CELL, "fill_ms_per_step": fill_ms_step,
                          "fill_share_of_step": fill_ms_step / ms_step if ms_step else None,
                          "peak_source": "measured in this run (alnr_measure_int_peak: IADD3/VIMNMX + IMAD chains, 148 SMs)",
-                         "alu_only_peak_tops": int_peak.get("alu_tops"), "traffic": None,
+                         "alu_only_peak_tops": int_peak.get("alu_tops"),
+                         # dram__bytes_read.sum + dram__bytes_write.sum of the main fill launch, scaled
+                         # from the one --set full capture (profiles/r01_fill_strip_ncu.txt:
+                         # 1.47 + 7.81 GB for 10^6 pairs = 0.412 B/cell, algorithmic 0.25 B/cell)
+                         "traffic": cells * NCU_DRAM_BYTES_PER_CELL,
                          "hbm": {"achieved": d_bytes / (fill_ms_step * 1e-3) / 1e9 if fill_ms_step else None,
                                  "peak": hbm_peak, "unit": "GB/s", "algorithmic_bytes": d_bytes,
                                  "note": "2-bit direction matrix writes, 0.25 B/cell; peak of measured" if peaks else "of fallback"}},
