@@ -172,6 +172,13 @@ bool alnr_batch_impl::use_warp(uint32_t m) const {
   if (numeric == ALNR_NUM_I16X2) return false;
   static const bool off = getenv("ALNR_NO_WARP_KERNEL") != nullptr;
   if (off) return false;
+  if (numeric == ALNR_NUM_F64) {
+    // the FP64 warp kernel takes max by compare-select: needs finite inputs far from overflow
+    auto ok = [](double v) { return std::fabs(v) < 1e290; };
+    bool fin = ok(del) && ok(ext);
+    for (double v : matrix) fin = fin && ok(v);
+    if (!fin) return false;
+  }
   return want_matrices || m >= 24 || count <= 4096;
 }
 

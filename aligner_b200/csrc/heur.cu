@@ -92,6 +92,7 @@ extern "C" int alnr_heuristic_batch(const alnr_params *p, const alnr_batch *b,
                                     const alnr_heuristic_items *it, alnr_heuristic_out *out) {
   if (!p || !b || !it || !out || !it->matrices || !it->frequencies) return ALNR_INVALID_ARGUMENT;
   if (p->volume < 1 || p->volume > 32) return ALNR_MATRIX_SHAPE_ERROR;
+  if (!(std::fabs(p->del) < 1e290 && std::fabs(p->ext) < 1e290)) return ALNR_INVALID_ARGUMENT;  // NaN / inf penalties
   const int V = p->volume, VV = V * V;
   const uint64_t P = b->count, K = it->n_matrices;
   const bool grid = it->pair_idx == nullptr;  // full grid: item = pair * K + k
@@ -121,7 +122,7 @@ extern "C" int alnr_heuristic_batch(const alnr_params *p, const alnr_batch *b,
   const bool stateful = p->del != p->ext;
   const uint32_t nzw = (n_max + 31) / 32;
   const uint64_t row_words = (uint64_t)std::max(m_max, n_max) + 1;  // band rows / exact-kernel column
-  const uint64_t per_item = dl0.words_for(1) * 4 + 8ull * row_words + 3ull * VV * 8 + 128 + (stateful ? 8ull * nzw + 4 : 0);
+  const uint64_t per_item = dl0.words_for(1) * 4 + 8ull * row_words + 3ull * VV * 8 + 132 + (stateful ? 8ull * nzw : 0);
   size_t free_b = 0, total_b = 0;
   ALNR_CUDA(cudaMemGetInfo(&free_b, &total_b));
   const uint64_t budget = std::max<uint64_t>(std::min<uint64_t>(free_b / 3, 16ull << 30), 64ull << 20);
@@ -149,7 +150,8 @@ extern "C" int alnr_heuristic_batch(const alnr_params *p, const alnr_batch *b,
   ALNR_CUDA(d_T.alloc(chunk * VV)); ALNR_CUDA(d_L.alloc(chunk * VV)); ALNR_CUDA(d_F.alloc(chunk * VV));
   ALNR_CUDA(d_maxf.alloc(chunk)); ALNR_CUDA(d_fcur.alloc(chunk)); ALNR_CUDA(d_fout.alloc(chunk));
   ALNR_CUDA(d_corner.alloc(chunk)); ALNR_CUDA(d_hcol.alloc((chunk + 31) / 32 * 32 * row_words));
-  if (stateful) ALNR_CUDA(d_wz.alloc(8 + chunk * (1 + 2ull * nzw)));
+  // fail list: items whose speculation never settles or whose matrix is not finite (exact kernel)
+  ALNR_CUDA(d_wz.alloc(8 + chunk * (1 + (stateful ? 2ull * nzw : 0))));
   ALNR_CUDA(d_cc.alloc(chunk * 4)); ALNR_CUDA(d_co.alloc(chunk * 4));
 
   auto h2d = [&](void *dst, const void *src, size_t bytes) {
@@ -199,12 +201,12 @@ extern "C" int alnr_heuristic_batch(const alnr_params *p, const alnr_batch *b,
       w.cv = cv; w.V = V; w.del = p->del; w.ext = p->ext; w.stateful = stateful;
       w.matrix = nullptr; w.item_matrices = d_T.p; w.D = d_D.p; w.dl = dl0; w.fo = fo;
       w.rowbuf = d_hcol.p; w.rowbuf_stride = n_max + 1;
-      w.nzw = nzw; w.fail_count = d_wz.p; w.fail_list = stateful ? d_wz.p + 8 : nullptr;
+      w.nzw = nzw; w.fail_count = d_wz.p; w.fail_list = d_wz.p + 8;
       w.zbuf = stateful ? d_wz.p + 8 + chunk : nullptr;
       w.H_out = nullptr; w.D_out = nullptr;
-      if (stateful) ALNR_CUDA(cudaMemsetAsync(d_wz.p, 0, 8 * sizeof(uint32_t), stream));
+      ALNR_CUDA(cudaMemsetAsync(d_wz.p, 0, 8 * sizeof(uint32_t), stream));
       { int wst = warp_launch_f64(stream, w, true, false); if (wst) return wst; }
-      if (stateful) {  // items whose speculation did not settle: exact column-major kernel
+      {  // items the warp kernel handed over (fail list): exact column-major kernel
         ExactArgs<double> e;
         e.cv = cv; e.mode = ALNR_LOCAL; e.V = V; e.del = p->del; e.ext = p->ext;
         e.matrix = nullptr; e.hcol = d_hcol.p; e.hrows = m_max + 1; e.D = d_D.p; e.dl = dl0; e.fo = fo;

@@ -32,8 +32,25 @@ __device__ __forceinline__ int shfl_up_t(int v) { return __shfl_up_sync(0xffffff
 __device__ __forceinline__ double shfl_up_t(double v) { return __shfl_up_sync(0xffffffffu, v, 1); }
 
 // grid: ceil(count / kWarpsPerBlock); smem: V*V*sizeof(T) * (item_matrices ? kWarpsPerBlock : 1)
-template <typename T, int R, bool LOCAL, bool MATS>
+// max of three for the warp kernel.  FP64: the host (shared matrix) or the staging loop below
+// (per-item matrices) guarantees finite inputs far from overflow, so no NaN can arise and
+// f64::max (enums.rs:19) reduces to compare-select — 1 DSETP + 2 selects instead of fmax's
+// DSETP + selects + NaN fix-up.  (Only the sign of a zero result can differ; `== 0.0` and the
+// EPSILON tests do not see it.)
+__device__ __forceinline__ int wmax3(int a, int b, int c) { return max(max(a, b), c); }
+__device__ __forceinline__ double wmax3(double a, double b, double c) {
+  const double g = a > b ? a : b;
+  return g > c ? g : c;
+}
+constexpr double kWarpFiniteBound = 1e290;
+
+// MODE: 0 global; 1 local with del == ext (static penalty, FP64 only: saves two selects per cell in
+// the matrix search); 2 local, any del / ext (a.stateful says whether the speculation is needed).
+// The INT32 instantiation of MODE 1 gave wrong scores on B200 (nvcc 12.9, cause not found; caught by
+// tests/test_warp.py::test_every_rows_per_lane_int), so INT32 static-penalty problems run MODE 2.
+template <typename T, int R, int MODE, bool MATS>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32) fill_warp_kernel(WarpArgs<T> a) {
+  constexpr bool LOCAL = MODE != 0;
   extern __shared__ unsigned char smem_raw[];
   T *smem = reinterpret_cast<T *>(smem_raw);
   const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -48,9 +65,19 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) fill_warp_kernel(WarpArgs
   const T *smat;
   if (a.item_matrices) {
     T *mine = smem + (size_t)warp * VV;
-    if (have) for (int i = lane; i < VV; i += 32) mine[i] = a.item_matrices[(size_t)pair * VV + i];
+    bool bad = false;
+    if (have) for (int i = lane; i < VV; i += 32) {
+      const T v = a.item_matrices[(size_t)pair * VV + i];
+      mine[i] = v;
+      if (sizeof(T) == 8) bad |= !(fabs((double)v) < kWarpFiniteBound);
+    }
     __syncwarp();
     smat = mine;
+    if (sizeof(T) == 8 && __any_sync(0xffffffffu, bad)) {
+      // non-finite matrix entry: the exact kernel keeps the reference's NaN-ignoring max
+      if (have && lane == 0) a.fail_list[atomicAdd(a.fail_count, 1u)] = slot;
+      have = false;
+    }
   } else {
     for (int i = threadIdx.x; i < VV; i += blockDim.x) smem[i] = a.matrix[i];
     __syncthreads();
@@ -67,7 +94,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) fill_warp_kernel(WarpArgs
   const uint32_t nbands = (m + BH - 1) / BH;
   const uint32_t m_lane = ((m - 1) % BH) / R, m_r = (m - 1) % R;  // where row m lives (last band)
   const T del = a.del, ext = a.ext;
-  const bool stateful = LOCAL && a.stateful;
+  const bool stateful = MODE == 2 && a.stateful;  // MODE 2 also runs static-penalty problems
   T *rowbuf = a.rowbuf + (size_t)slot * a.rowbuf_stride;
   uint32_t *Dslot = a.D + (uint64_t)slot * a.dl.nstrips * (a.dl.ncols + 31);
   const uint64_t band_words = (uint64_t)(a.dl.ncols + 31) * 32;
@@ -154,16 +181,15 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) fill_warp_kernel(WarpArgs
           for (int r = 0; r < R; ++r) {
             const T sc = smat[toff[r] + qs];
             const T top = nsub(hup, pen), lft = nsub(h[r], pen), dg = nadd(diag, sc);
-            const T mx = Num<T>::max3(top, lft, dg);
+            const T mx = wmax3(top, lft, dg);
             uint32_t d = Num<T>::same(mx, lft) ? DIR_LEFT : DIR_DIAGONAL;  // enums.rs:23/:41
             d = Num<T>::same(mx, top) ? DIR_TOP : d;                       // enums.rs:21/:39
             if (LOCAL) {
               const bool zero = Num<T>::is_zero(mx);                       // enums.rs:37
               d = zero ? DIR_BEGINNING : d;
-              pen = zero ? del : ext;
-            } else {
-              pen = ext;
+              if (MODE == 2) pen = zero ? del : ext;
             }
+            if (MODE != 2) pen = ext;
             bits |= d << (2 * r);
             diag = h[r];
             h[r] = mx;

@@ -5,26 +5,32 @@
 
 namespace alnr {
 
-template <typename T, int R, bool LOCAL, bool MATS>
+template <typename T, int R, int MODE, bool MATS>
 static int warp_launch_one(cudaStream_t stream, const WarpArgs<T> &a) {
   const unsigned blocks = (a.cv.count + kWarpsPerBlock - 1) / kWarpsPerBlock;
   if (blocks == 0) return ALNR_OK;
   const size_t smem = (size_t)a.V * a.V * sizeof(T) * (a.item_matrices ? kWarpsPerBlock : 1);
-  fill_warp_kernel<T, R, LOCAL, MATS><<<blocks, kWarpsPerBlock * 32, smem, stream>>>(a);
+  fill_warp_kernel<T, R, MODE, MATS><<<blocks, kWarpsPerBlock * 32, smem, stream>>>(a);
   ALNR_LAUNCHED();
   return ALNR_OK;
 }
 
 template <typename T>
 static int warp_launch_any(cudaStream_t stream, const WarpArgs<T> &a, bool local, bool mats) {
+  // MODE 1 (compile-time static penalty) only for FP64, see kernels_warp.cuh
+  constexpr bool kStaticMode = sizeof(T) == 8;
+  const int mode = !local ? 0 : ((a.stateful || !kStaticMode) ? 2 : 1);
   if (mats) {
     if (a.dl.rows_per_word != 8) return ALNR_INVALID_ARGUMENT;
-    return local ? warp_launch_one<T, 8, true, true>(stream, a) : warp_launch_one<T, 8, false, true>(stream, a);
+    return mode == 0 ? warp_launch_one<T, 8, 0, true>(stream, a) : warp_launch_one<T, 8, 2, true>(stream, a);
   }
 #define ALNR_WARP_CASE(RR)                                                        \
   case RR:                                                                        \
-    return local ? warp_launch_one<T, RR, true, false>(stream, a)                 \
-                 : warp_launch_one<T, RR, false, false>(stream, a);
+    if (mode == 0) return warp_launch_one<T, RR, 0, false>(stream, a);            \
+    if constexpr (kStaticMode) {                                                  \
+      if (mode == 1) return warp_launch_one<T, RR, 1, false>(stream, a);          \
+    }                                                                             \
+    return warp_launch_one<T, RR, 2, false>(stream, a);
   switch (a.dl.rows_per_word) {
     ALNR_WARP_CASE(2) ALNR_WARP_CASE(4) ALNR_WARP_CASE(6) ALNR_WARP_CASE(8)
     ALNR_WARP_CASE(10) ALNR_WARP_CASE(12) ALNR_WARP_CASE(14) ALNR_WARP_CASE(16)
