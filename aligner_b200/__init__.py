@@ -8,15 +8,16 @@ from . import _native
 from ._native import AlignerError, GLOBAL, LOCAL, NUM_AUTO, NUM_F64, NUM_I16X2, NUM_I32
 from .aligners import (Alignment, AlignmentResult, Heuristics, SimpleGlobalAligner,
                        SimpleLocalAligner)
-from .batch import BatchResult, DeviceBatch, PackedPairs, align_batch
+from .batch import BatchResult, DeviceBatch, PackedPairs, ScoreResult, align_batch, score_batch
 from .enums import DNA, Direction, Error, Protein
 from .heuristic import HeuristicAligner, heuristic_batch, matrix_search, transform_matrix
 from .matrices import dna_matrix, get_blosum62
+from .statistics import shuffle_scores, shuffled_targets
 from .sharding import align_batch_sharded, matrix_search_sharded, shard_range
 
 __all__ = [
     "AlignerError", "Alignment", "AlignmentResult", "BatchResult", "DNA", "DeviceBatch", "Direction",
     "Error", "GLOBAL", "HeuristicAligner", "Heuristics", "heuristic_batch", "matrix_search", "transform_matrix", "LOCAL", "NUM_AUTO", "NUM_F64", "NUM_I16X2", "NUM_I32",
     "PackedPairs", "Protein", "SimpleGlobalAligner", "SimpleLocalAligner", "align_batch",
-    "dna_matrix", "get_blosum62", "align_batch_sharded", "matrix_search_sharded", "shard_range",
+    "dna_matrix", "get_blosum62", "ScoreResult", "score_batch", "shuffled_targets", "shuffle_scores", "align_batch_sharded", "matrix_search_sharded", "shard_range",
 ]

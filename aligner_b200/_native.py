@@ -78,6 +78,9 @@ SIGNATURES = {
     "alnr_batch_numeric": (C.c_int, [C.c_void_p]),
     "alnr_batch_rerun_count": (C.c_uint64, [C.c_void_p]),
     "alnr_batch_destroy": (None, [C.c_void_p]),
+    "alnr_score_batch": (C.c_int, [C.POINTER(Params), C.POINTER(Batch), f64p, f64p, u32p, i32p]),
+    "alnr_batch_create_scores": (C.c_int, [C.POINTER(Params), C.POINTER(Batch), C.POINTER(C.c_void_p)]),
+    "alnr_batch_download_scores": (C.c_int, [C.c_void_p, f64p, f64p, u32p, i32p]),
     "alnr_transform_matrix": (C.c_int, [f64p, C.c_int, C.c_int, C.c_double, C.c_double, f64p, f64p]),
     "alnr_heuristic_batch": (C.c_int, [C.POINTER(Params), C.POINTER(Batch), C.POINTER(HeuristicItems),
                                        C.POINTER(HeuristicOut)]),

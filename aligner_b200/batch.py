@@ -111,15 +111,53 @@ def align_batch(mode, pairs, matrix, del_, ext, device=-1, numeric=N.NUM_AUTO, w
     return res
 
 
-class DeviceBatch:
-    """Device-resident batch: upload once, run many times (alnr_batch_*)."""
+class ScoreResult:
+    """Outputs of a score-only call: what the p-value shuffles keep of every alignment
+    (``alignment.f``, aligner-core/src/statistics/mod.rs:268-276) plus the corner score and the
+    1-based (target, query) cell the traceback would have started from."""
 
-    def __init__(self, mode, pairs, matrix, del_, ext, device=-1, numeric=N.NUM_AUTO):
+    def __init__(self, count):
+        self.count = count
+        self.f = np.zeros(count, dtype=np.float64)
+        self.corner = np.zeros(count, dtype=np.float64)
+        self.end_yx = np.zeros((count, 2), dtype=np.uint32)
+        self.status = np.zeros(count, dtype=np.int32)
+
+    def c_args(self):
+        return (self.f.ctypes.data_as(N.f64p), self.corner.ctypes.data_as(N.f64p),
+                self.end_yx.ctypes.data_as(N.u32p), self.status.ctypes.data_as(N.i32p))
+
+    def bytes_out(self):
+        return int(self.f.nbytes + self.corner.nbytes + self.end_yx.nbytes + self.status.nbytes)
+
+
+def score_batch(mode, pairs, matrix, del_, ext, device=-1, numeric=N.NUM_AUTO, out=None):
+    """Scores without alignments (alnr_score_batch): same fill kernels, no direction scratch and no
+    traceback."""
+    p = make_params(mode, matrix, del_, ext, device, numeric)
+    res = out if out is not None else ScoreResult(pairs.count)
+    b = pairs.c_struct()
+    N.check(N.lib().alnr_score_batch(C.byref(p), C.byref(b), *res.c_args()))
+    return res
+
+
+class DeviceBatch:
+    """Device-resident batch: upload once, run many times (alnr_batch_*).  ``score_only`` builds
+    the handle with alnr_batch_create_scores; read it with ``download_scores``."""
+
+    def __init__(self, mode, pairs, matrix, del_, ext, device=-1, numeric=N.NUM_AUTO, score_only=False):
         self.pairs = pairs
+        self.score_only = score_only
         self._p = make_params(mode, matrix, del_, ext, device, numeric)
         self._h = C.c_void_p()
         b = pairs.c_struct()
-        N.check(N.lib().alnr_batch_create(C.byref(self._p), C.byref(b), C.byref(self._h)))
+        create = N.lib().alnr_batch_create_scores if score_only else N.lib().alnr_batch_create
+        N.check(create(C.byref(self._p), C.byref(b), C.byref(self._h)))
+
+    def download_scores(self, out=None):
+        res = out if out is not None else ScoreResult(self.pairs.count)
+        N.check(N.lib().alnr_batch_download_scores(self._h, *res.c_args()))
+        return res
 
     def run(self):
         N.check(N.lib().alnr_batch_run(self._h))

@@ -61,6 +61,34 @@ int alnr_batch_create(const alnr_params *p, const alnr_batch *b, alnr_batch_hand
   return ALNR_OK;
 }
 
+int alnr_batch_create_scores(const alnr_params *p, const alnr_batch *b, alnr_batch_handle **h) {
+  if (!h) return ALNR_INVALID_ARGUMENT;
+  *h = nullptr;
+  alnr_batch_handle *hh = new (std::nothrow) alnr_batch_handle();
+  if (!hh) return ALNR_OUT_OF_MEMORY;
+  hh->impl.score_only = true;
+  int st = hh->impl.init(p, b, false);
+  if (st) { delete hh; return st; }
+  *h = hh;
+  return ALNR_OK;
+}
+
+int alnr_batch_download_scores(alnr_batch_handle *h, double *f, double *corner, uint32_t *end_yx,
+                               int32_t *status) {
+  return h ? h->impl.download_scores(f, corner, end_yx, status) : ALNR_INVALID_ARGUMENT;
+}
+
+int alnr_score_batch(const alnr_params *p, const alnr_batch *b, double *f, double *corner,
+                     uint32_t *end_yx, int32_t *status) {
+  alnr_batch_handle *hh = nullptr;
+  int st = alnr_batch_create_scores(p, b, &hh);
+  if (st) return st;
+  st = hh->impl.run();
+  if (!st) st = hh->impl.download_scores(f, corner, end_yx, status);
+  alnr_batch_destroy(hh);
+  return st;
+}
+
 int alnr_batch_run(alnr_batch_handle *h) { return h ? h->impl.run() : ALNR_INVALID_ARGUMENT; }
 
 int alnr_batch_sync(alnr_batch_handle *h) {

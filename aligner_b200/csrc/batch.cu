@@ -134,7 +134,7 @@ int alnr_batch_impl::plan_chunks(const uint64_t *q_off, const uint64_t *t_off) {
     if (!uniform) n = nsuf[s];
     m = std::max(m, 1u); n = std::max(n, 1u);
     const DLayout pl = layout_dims(m, n, false);
-    const uint64_t per_group = pl.words_for(32) * 4 + (((uint64_t)std::max(m, n) + 1) * num_sz + (uint64_t)(n + 1) * 4) * 32;
+    const uint64_t per_group = (score_only ? 0 : pl.words_for(32) * 4) + (((uint64_t)std::max(m, n) + 1) * num_sz + (uint64_t)(n + 1) * 4) * 32;
     uint64_t groups = std::max<uint64_t>(budget / per_group, 1);
     uint64_t c = std::min<uint64_t>(groups * 32, count - s);
     if (c < count - s) c = std::max<uint64_t>(c / 64 * 64, 32);  // keep duo-kernel warps whole
@@ -299,8 +299,8 @@ int alnr_batch_impl::init(const alnr_params *p, const alnr_batch *b, bool want_m
   ALNR_CUDA(d_coords.alloc(count * 4));
   ALNR_CUDA(d_alnoff.alloc(count));
   ALNR_CUDA(d_alnlen.alloc(count));
-  ALNR_CUDA(d_qaln.alloc(q_total + t_total + count));
-  ALNR_CUDA(d_taln.alloc(q_total + t_total + count));
+  ALNR_CUDA(d_qaln.alloc(score_only ? 1 : q_total + t_total + count));
+  ALNR_CUDA(d_taln.alloc(score_only ? 1 : q_total + t_total + count));
   ALNR_CUDA(d_flags.alloc(4));
   ALNR_CUDA(d_rerun.alloc(count + 1));
   {
@@ -310,7 +310,7 @@ int alnr_batch_impl::init(const alnr_params *p, const alnr_batch *b, bool want_m
     ALNR_CUDA(d_ctotal.alloc(chunks.size() + 1));
     uint64_t mwords = 1;
     for (const Chunk &c : chunks)
-      if (chunk_compact(c))
+      if (chunk_compact(c) && !score_only)
         mwords = std::max<uint64_t>(mwords, (uint64_t)((c.count + 31) / 32 * 32) * ((c.n_max + c.m_max + 1 + 15) / 16));
     ALNR_CUDA(d_moves.alloc(mwords));
   }
@@ -318,7 +318,7 @@ int alnr_batch_impl::init(const alnr_params *p, const alnr_batch *b, bool want_m
   uint64_t dwords = 1, hcol = 1;
   for (const Chunk &c : chunks) {
     const DLayout dl = layout_for(c);
-    dwords = std::max<uint64_t>(dwords, dl.words_for(c.count));
+    if (!score_only) dwords = std::max<uint64_t>(dwords, dl.words_for(c.count));
     hcol = std::max<uint64_t>(hcol, (uint64_t)((c.count + 31) / 32) * 32 * ((uint64_t)std::max(c.m_max, c.n_max) + 1));
   }
   const size_t copies = chunks.size() > 1 ? 2 : 1;
@@ -477,6 +477,7 @@ int alnr_batch_impl::phase2(size_t ci) {
     st = fill_mark(true);  // only recorded when profiling, i.e. when s2 == stream
     if (st) return st;
   }
+  if (score_only) return ALNR_OK;  // f, corner and the arg-max cell are final after the fill
   TraceArgs ta{cv, mode, V, Dp(), dl, fo, to};
   const uint32_t nmw = (c.n_max + c.m_max + 1 + 15) / 16;  // 2-bit move words per pair
   if (chunk_compact(c)) {
@@ -626,8 +627,27 @@ int alnr_batch_impl::stream_all(const alnr_batch *b, alnr_batch_out *out) {
   return st;
 }
 
+int alnr_batch_impl::download_scores(double *f, double *corner, uint32_t *end_yx, int32_t *status) {
+  ALNR_CUDA(cudaSetDevice(device));
+  if (count == 0) return ALNR_OK;
+  auto cp = [&](void *dst, const void *src, size_t bytes) -> cudaError_t {
+    if (!dst) return cudaSuccess;
+    return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, stream);
+  };
+  ALNR_CUDA(cp(f, d_f.p, count * 8));
+  ALNR_CUDA(cp(corner, d_corner.p, count * 8));
+  ALNR_CUDA(cp(end_yx, d_start.p, count * 8));
+  ALNR_CUDA(cp(status, d_status.p, count * 4));
+  ALNR_CUDA(cudaStreamSynchronize(stream));
+  return ALNR_OK;
+}
+
 int alnr_batch_impl::download(alnr_batch_out *out) {
   if (!out) return ALNR_INVALID_ARGUMENT;
+  if (score_only) {  // no alignments were produced
+    if (out->q_aln || out->t_aln || out->coords || out->aln_off || out->aln_len) return ALNR_INVALID_ARGUMENT;
+    return download_scores(out->f, out->corner, nullptr, out->status);
+  }
   ALNR_CUDA(cudaSetDevice(device));
   if (count == 0) return ALNR_OK;
   auto cp = [&](void *dst, const void *src, size_t bytes) -> cudaError_t {

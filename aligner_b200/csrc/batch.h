@@ -22,6 +22,9 @@ struct alnr_batch_impl {
   double del = 0, ext = 0;
   std::vector<double> matrix;
   bool want_matrices = false;   // single-pair calls: also produce H and D (reference layout)
+  // score-only calls (alnr_score_batch; statistics/mod.rs:255-292 keeps only alignment.f): no D
+  // scratch, no traceback, no alignment buffers
+  bool score_only = false;
 
   // shape
   uint64_t count = 0, q_total = 0, t_total = 0;
@@ -40,7 +43,7 @@ struct alnr_batch_impl {
   std::vector<cudaEvent_t> ev_p1, ev_p2;  // per chunk: phase 1 done, phase 2 done
   int par = 0;                      // parity of the chunk being enqueued
   uint64_t d_words = 0, hcol_elems = 0, rerun_words = 0;  // size of ONE parity copy
-  uint32_t *Dp() const { return d_D.p + (size_t)par * d_words; }
+  uint32_t *Dp() const { return score_only ? nullptr : d_D.p + (size_t)par * d_words; }
   int *hcol_i() const { return d_hcol_i.p ? d_hcol_i.p + (size_t)par * hcol_elems : nullptr; }
   double *hcol_d() const { return d_hcol_d.p ? d_hcol_d.p + (size_t)par * hcol_elems : nullptr; }
   int phase1(size_t ci);            // on `stream`
@@ -77,6 +80,7 @@ struct alnr_batch_impl {
   uint32_t max_chunk = 1u << 22;
   bool ramp = false;             // streaming: short first and last chunks
   int download(alnr_batch_out *out);
+  int download_scores(double *f, double *corner, uint32_t *end_yx, int32_t *status);
   int classify();
   DLayout layout_for(const Chunk &c) const;
   DLayout layout_dims(uint32_t m, uint32_t n, bool wave) const;

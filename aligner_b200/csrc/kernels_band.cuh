@@ -156,7 +156,7 @@ __global__ void __launch_bounds__(32) fill_band_kernel(BandArgs a) {
     int *my_row = a.rows + (size_t)band * (n + 1);
     volatile uint32_t *prog_prev = band ? a.prog + (band - 1) : nullptr;
     volatile uint32_t *prog_mine = a.prog + band;
-    const bool store_d = yl0 < m;
+    const bool store_d = yl0 < m && a.D != nullptr;  // score-only calls pass no D scratch
     const bool last_band = band + 1 == a.nbands;
     const bool row_out = lane == 31 && !last_band;
     L.dptr = a.D + (size_t)(yl0 / R) * a.dcols;  // this lane's R-row strip

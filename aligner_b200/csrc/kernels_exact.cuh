@@ -128,7 +128,7 @@ __global__ void __launch_bounds__(128) fill_exact_kernel(ExactArgs<T> a) {
       const uint32_t r = (y - 1) % rpw;
       dword |= a.dl.put((uint32_t)d, r);
       if (r == rpw - 1 || y == m) {
-        a.D[a.dl.word(slot, (y - 1) / rpw, x - 1)] = dword;
+        if (a.D) a.D[a.dl.word(slot, (y - 1) / rpw, x - 1)] = dword;  // nullptr: score-only call
         dword = 0;
       }
       if (a.H_out) a.H_out[y * W + x] = (double)mx;

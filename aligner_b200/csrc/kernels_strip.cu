@@ -58,27 +58,33 @@ static int launch_strip(alnr_batch_impl &B, cudaStream_t stream, const StripArgs
   if (vblocks == 0) return ALNR_OK;
   StripArgs a = a_in;
   a.vblocks = vblocks;
-#define ALNR_STRIP_LAUNCH(L, S)                                                                   \
+#define ALNR_STRIP_LAUNCH(L, S, SC)                                                                   \
   do {                                                                                            \
     static bool attr_done = false;                                                                \
     static unsigned resident = 0;                                                                 \
     if (!attr_done) {                                                                             \
-      ALNR_CUDA(cudaFuncSetAttribute(fill_strip_kernel<R, L, S>,                                  \
+      ALNR_CUDA(cudaFuncSetAttribute(fill_strip_kernel<R, L, S, SC>,                              \
                                      cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));   \
       int occ = 0, sms = 0, dev = 0;                                                              \
       ALNR_CUDA(cudaGetDevice(&dev));                                                             \
       ALNR_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));               \
-      ALNR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fill_strip_kernel<R, L, S>,   \
+      ALNR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fill_strip_kernel<R, L, S, SC>,\
                                                               kStripBlock, smem));                \
       resident = (unsigned)std::max(1, occ) * (unsigned)std::max(1, sms);                         \
       attr_done = true;                                                                           \
     }                                                                                             \
     const unsigned blocks = a.hglobal ? std::min(vblocks, resident) : vblocks;                    \
-    fill_strip_kernel<R, L, S><<<blocks, kStripBlock, smem, stream>>>(a);                         \
+    fill_strip_kernel<R, L, S, SC><<<blocks, kStripBlock, smem, stream>>>(a);                     \
   } while (0)
-  if (!local) ALNR_STRIP_LAUNCH(false, false);
-  else if (stateful) ALNR_STRIP_LAUNCH(true, true);
-  else ALNR_STRIP_LAUNCH(true, false);
+  if (B.score_only) {
+    if (!local) ALNR_STRIP_LAUNCH(false, false, true);
+    else if (stateful) ALNR_STRIP_LAUNCH(true, true, true);
+    else ALNR_STRIP_LAUNCH(true, false, true);
+  } else {
+    if (!local) ALNR_STRIP_LAUNCH(false, false, false);
+    else if (stateful) ALNR_STRIP_LAUNCH(true, true, false);
+    else ALNR_STRIP_LAUNCH(true, false, false);
+  }
 #undef ALNR_STRIP_LAUNCH
   ALNR_LAUNCHED();
   return ALNR_OK;

@@ -104,7 +104,9 @@ __device__ __forceinline__ uint32_t first_rows_equal(const uint32_t (&h)[R], uin
 // planes: P0 = Z | (T & ~L), P1 = Z | (T & L)  (code = P0 + 2*P1: 0 Top, 1 Left, 2 Diagonal,
 // 3 Beginning; enums.rs:18-46), stored as one word per pair: P0 in the low, P1 in the high
 // 16 bits ("plane" D format).
-template <int R, bool LOCAL, bool STATEFUL, bool LASTSTRIP>
+// SCORE: score-only calls (alnr_score_batch) — no direction planes are formed and nothing is
+// written to the D scratch; the cell is PRMT + max + add + add-max (+ the column max).
+template <int R, bool LOCAL, bool STATEFUL, bool LASTSTRIP, bool SCORE>
 __device__ __forceinline__ void strip_sweep(const StripArgs &a, StripCtx &c, const uint32_t *swt,
                                             uint32_t strip) {
   const uint32_t n = a.n, m = a.m;
@@ -164,6 +166,7 @@ __device__ __forceinline__ void strip_sweep(const StripArgs &a, StripCtx &c, con
       np = (!LOCAL && strip == 0 && x == 1) ? ndel2 : next2;  // simple/mod.rs:72: first cell pays del
     }
     uint32_t accG = 0, accU = 0, accN = 0, cm = 0x80008000u, mprev = 0x80008000u;
+    uint32_t hlast = 0;  // SCORE: H[m][x] of both pairs (its zero flag is the z bit)
 #pragma unroll
     for (int r = 0; r < R; ++r) {
       // max(top, left) = max(H_up, H_left) - penalty: one max + one add instead of two adds
@@ -171,13 +174,16 @@ __device__ __forceinline__ void strip_sweep(const StripArgs &a, StripCtx &c, con
       const uint32_t g = __vmaxs2(hup, h[r]);
       const uint32_t gl = __vadd2(g, np);
       const uint32_t mx = __viaddmax_s16x2(diag, s, gl);
-      accG += __vminu2(mx ^ gl, one2) << r;   // 1: neither gap move reaches the max -> Diagonal
-      accU += __vminu2(g ^ hup, one2) << r;   // 1: H_left > H_up -> Left beats Top (Top wins ties)
-      if (LOCAL) {
+      if (!SCORE) {
+        accG += __vminu2(mx ^ gl, one2) << r;   // 1: neither gap move reaches the max -> Diagonal
+        accU += __vminu2(g ^ hup, one2) << r;   // 1: H_left > H_up -> Left beats Top (Top wins ties)
+      }
+      if (LOCAL && (!SCORE || STATEFUL)) {
         const uint32_t nz = __vminu2(mx, one2);
-        accN += nz << r;
+        if (!SCORE) accN += nz << r;
         if (STATEFUL) np = nz * dme + ndel2;  // simple/mod.rs:201-205
       }
+      if (SCORE && STATEFUL && LASTSTRIP) { if ((uint32_t)r + 1 == rv) hlast = mx; }
       if (!STATEFUL) np = next2;
       diag = h[r];
       h[r] = mx;
@@ -194,15 +200,17 @@ __device__ __forceinline__ void strip_sweep(const StripArgs &a, StripCtx &c, con
     if (!LASTSTRIP) *hp = h[R - 1];
     // direction planes of this column (both pairs at once), then one word per pair:
     // Top = !G & !U, Left = !G & U, Diagonal = G, Beginning = Z  (enums.rs:18-46)
-    uint32_t P0, P1;
-    if (LOCAL) { P0 = ~accN | (~accG & accU); P1 = ~accN | accG; }
-    else { P0 = ~accG & accU; P1 = accG; }
-    a0 = a1; a1 = a2; a2 = a3; a3 = __byte_perm(P0, P1, 0x5410);
-    b0 = b1; b1 = b2; b2 = b3; b3 = __byte_perm(P0, P1, 0x7632);
-    if ((xm1 & 3) == 3) {
-      // streaming stores: D is written once and read only by the traceback; keep L2 for the rows
-      __stcs(reinterpret_cast<uint4 *>(dpA + (xm1 - 3)), make_uint4(a0, a1, a2, a3));
-      if (!c.dupB) __stcs(reinterpret_cast<uint4 *>(dpB + (xm1 - 3)), make_uint4(b0, b1, b2, b3));
+    if (!SCORE) {
+      uint32_t P0, P1;
+      if (LOCAL) { P0 = ~accN | (~accG & accU); P1 = ~accN | accG; }
+      else { P0 = ~accG & accU; P1 = accG; }
+      a0 = a1; a1 = a2; a2 = a3; a3 = __byte_perm(P0, P1, 0x5410);
+      b0 = b1; b1 = b2; b2 = b3; b3 = __byte_perm(P0, P1, 0x7632);
+      if ((xm1 & 3) == 3) {
+        // streaming stores: D is written once and read only by the traceback; keep L2 for the rows
+        __stcs(reinterpret_cast<uint4 *>(dpA + (xm1 - 3)), make_uint4(a0, a1, a2, a3));
+        if (!c.dupB) __stcs(reinterpret_cast<uint4 *>(dpB + (xm1 - 3)), make_uint4(b0, b1, b2, b3));
+      }
     }
 
     if (LOCAL) {
@@ -225,7 +233,7 @@ __device__ __forceinline__ void strip_sweep(const StripArgs &a, StripCtx &c, con
     }
     if (STATEFUL && LASTSTRIP) {
       // observe z[x-1] = (H[m][x] == 0); it sets the penalty of cell (1, x+1)
-      const uint32_t z = ~(accN >> (rv - 1));
+      const uint32_t z = SCORE ? ~__vminu2(hlast, one2) : ~(accN >> (rv - 1));
       zacc |= (z & 1u) << (xm1 & 31);
       zaccB |= ((z >> 16) & 1u) << (xm1 & 31);
       if ((xm1 & 31) == 31 || x == n) {
@@ -244,7 +252,7 @@ __device__ __forceinline__ void strip_sweep(const StripArgs &a, StripCtx &c, con
     }
   }
   // flush a partial group of D words (n not a multiple of 4)
-  if (n & 3) {
+  if (!SCORE && (n & 3)) {
     for (uint32_t k = n & 3; k < 4; ++k) { a0 = a1; a1 = a2; a2 = a3; a3 = 0; b0 = b1; b1 = b2; b2 = b3; b3 = 0; }
     __stcs(reinterpret_cast<uint4 *>(dpA + (n & ~3u)), make_uint4(a0, a1, a2, a3));
     if (!c.dupB) __stcs(reinterpret_cast<uint4 *>(dpB + (n & ~3u)), make_uint4(b0, b1, b2, b3));
@@ -256,7 +264,7 @@ __device__ __forceinline__ void strip_sweep(const StripArgs &a, StripCtx &c, con
   }
 }
 
-template <int R, bool LOCAL, bool STATEFUL>
+template <int R, bool LOCAL, bool STATEFUL, bool SCORE = false>
 __global__ void __launch_bounds__(kStripBlock) fill_strip_kernel(StripArgs a) {
   extern __shared__ uint32_t smem_h[];
   __shared__ uint32_t swt[4];
@@ -292,8 +300,8 @@ __global__ void __launch_bounds__(kStripBlock) fill_strip_kernel(StripArgs a) {
   c.tB = a.tpk + ((size_t)(bB >> 5) * a.nwt) * 32 + (bB & 31);
   const uint32_t n = a.n, m = a.m;
   const uint32_t nstrips = (m + R - 1) / R;
-  c.dA = a.D + a.dl.word(c.sA, 0, 0);
-  c.dB = a.D + a.dl.word(c.sB, 0, 0);
+  c.dA = SCORE ? nullptr : a.D + a.dl.word(c.sA, 0, 0);
+  c.dB = SCORE ? nullptr : a.D + a.dl.word(c.sB, 0, 0);
   if (a.hglobal) {  // [(duo group * n + x-1) * 32 + lane]: coalesced, L2-resident
     c.hrow = a.hglobal + ((size_t)(pduo >> 5) * a.n) * 32 + (pduo & 31);
     c.hstride = 32;
@@ -314,8 +322,8 @@ __global__ void __launch_bounds__(kStripBlock) fill_strip_kernel(StripArgs a) {
   }
 
   for (uint32_t strip = 0; strip + 1 < nstrips; ++strip)
-    strip_sweep<R, LOCAL, STATEFUL, false>(a, c, swt, strip);
-  strip_sweep<R, LOCAL, STATEFUL, true>(a, c, swt, nstrips - 1);
+    strip_sweep<R, LOCAL, STATEFUL, false, SCORE>(a, c, swt, strip);
+  strip_sweep<R, LOCAL, STATEFUL, true, SCORE>(a, c, swt, nstrips - 1);
 
   // ---- per-pair results ---------------------------------------------------------------
   auto finish = [&](uint32_t bslot, uint32_t slot, const Best &b, int cval, bool mism) {

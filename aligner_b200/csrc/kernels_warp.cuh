@@ -144,7 +144,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) fill_warp_kernel(WarpArgs
       uint32_t zw = 0, zacc = 0;
       uint32_t qn = q[0];
       uint32_t *dp = Dslot + band * band_words + lane;
-      const bool store_d = yb < m;
+      const bool store_d = yb < m && a.D != nullptr;  // score-only calls pass no D scratch
       const bool obs_lane = last_band && lane == m_lane;
       const bool top_lane = band == 0 && lane == 0;
       const uint32_t steps = n + 31;

@@ -153,6 +153,24 @@ int alnr_batch_numeric(alnr_batch_handle *h);           /* domain selected for t
 uint64_t alnr_batch_rerun_count(alnr_batch_handle *h);  /* pairs whose speculation was redone */
 void alnr_batch_destroy(alnr_batch_handle *h);
 
+/* ---- score-only batches ------------------------------------------------------------------------
+ * The p-value estimate (aligner-core/src/statistics/mod.rs:240-307) aligns one query against
+ * 4999 shuffled copies of the target and keeps ONLY `alignment.f` of each call (:268-276).  These
+ * entry points run the same fill kernels without direction scratch or traceback:
+ *   f[i]       Alignment.f (local: max H; global: 0.0, simple/mod.rs:139)
+ *   corner[i]  alignment_matrix[[m, n]] (the global score)
+ *   end_yx[2i], end_yx[2i+1]  1-based (target, query) cell the traceback would start from: the
+ *              first maximum in row-major order (simple/mod.rs:212), or (m, n) in global mode
+ *   status[i]  as in alnr_batch_out
+ * Any output pointer may be NULL. */
+int alnr_score_batch(const alnr_params *p, const alnr_batch *b, double *f, double *corner,
+                     uint32_t *end_yx, int32_t *status);
+/* Device-resident form: a handle for alnr_batch_run / _run_timed / _sync; read the results with
+ * alnr_batch_download_scores (alnr_batch_download accepts f / corner / status only). */
+int alnr_batch_create_scores(const alnr_params *p, const alnr_batch *b, alnr_batch_handle **h);
+int alnr_batch_download_scores(alnr_batch_handle *h, double *f, double *corner, uint32_t *end_yx,
+                               int32_t *status);
+
 /* ---- heuristic matrix search ---------------------------------------------------------------
  * transform_matrix (aligner-helpers/src/matrices/mod.rs:19-68): rows x cols matrix, frequencies
  * [rows]; out may alias nothing.  Returns ALNR_WRONG_MATRIX on Roots::No. */

@@ -18,6 +18,7 @@ for p in (ROOT, os.path.join(ROOT, "tests")):
 import aligner_b200 as ab  # noqa: E402
 from aligner_b200 import _native as N  # noqa: E402
 from aligner_b200 import workloads as W  # noqa: E402
+from aligner_b200.batch import PackedPairs  # noqa: E402
 
 
 def timed_pair(mode, q, t, d, e, M, symbols, reps=3):
@@ -83,6 +84,44 @@ def c5(P, K):
          items=P * K, mean_passes=float(passes.mean()), ok_items=int((res.status == 0).sum()))
 
 
+def n2():
+    """N2: the p-value shuffle batch (statistics/mod.rs:255-292) and the C3 reads, score-only."""
+    from aligner_b200 import statistics as S
+    pp = W.protein_pairs(1, 1, 280, 320)
+    query, target = pp.pair(0)
+    targets = S.shuffled_targets(target, rng=np.random.default_rng(1))
+    M = ab.get_blosum62()
+    ab.shuffle_scores(query, target, 100.0, 11, 2, M, targets=targets[:64])  # warm-up
+    best = 1e9
+    for _ in range(3):
+        t0 = time.perf_counter()
+        scores, lengths, _ = ab.shuffle_scores(query, target, 100.0, 11, 2, M, targets=targets)
+        best = min(best, time.perf_counter() - t0)
+    cells = float(len(query)) * float(sum(len(t) for t in targets))
+    emit("N2 p-value batch: %d aa query x 4999 shuffled targets, BLOSUM62 d=11 e=2, score-only (e2e call)" % len(query),
+         cells, best, mean_score=float(scores[1:].mean()))
+    pairs = PackedPairs.from_lists([query] * len(targets), targets)
+    db = ab.DeviceBatch(N.LOCAL, pairs, M, 11, 2, score_only=True)
+    db.run_timed(2, profile_fill=False)
+    ms, _ = db.run_timed(10, profile_fill=False)
+    emit("N2 p-value batch, device-resident, score-only", cells, ms / 10 / 1e3)
+    db.close()
+    db = ab.DeviceBatch(N.LOCAL, pairs, M, 11, 2)
+    db.run_timed(2, profile_fill=False)
+    ms, _ = db.run_timed(10, profile_fill=False)
+    emit("N2 p-value batch, device-resident, with traceback", cells, ms / 10 / 1e3)
+    db.close()
+    reads = W.dna_read_batch(0, 1000000, n=150)
+    for d, e in [(10, 2), (6, 6)]:
+        for so in (True, False):
+            db = ab.DeviceBatch(N.LOCAL, reads, ab.dna_matrix(5, -4), d, e, score_only=so)
+            db.run_timed(2, profile_fill=False)
+            ms, _ = db.run_timed(5, profile_fill=False)
+            emit("C3 reads 10^6 x 150x150 local d=%d e=%d device-resident, %s" % (d, e, "score-only" if so else "with traceback"),
+                 1e6 * 150 * 150, ms / 5 / 1e3)
+            db.close()
+
+
 if __name__ == "__main__":
     what = sys.argv[1:] or ["c12", "c4"]
     if N.lib().alnr_device_count() < 1:
@@ -97,6 +136,8 @@ if __name__ == "__main__":
         c5(200, 50)
     if "c5big" in what:
         c5(2000, 100)
+    if "n2" in what:
+        n2()
     if "peaks" in what:
         import ctypes as C
         a, b = C.c_double(), C.c_double()
