@@ -54,6 +54,22 @@ class HeuristicItems(C.Structure):
                 ("frequencies", f64p)]
 
 
+class PwmParams(C.Structure):
+    _fields_ = [("del_", C.c_double), ("ext", C.c_double), ("pwm", f64p), ("rows", C.c_uint32),
+                ("length", C.c_uint32), ("device", C.c_int), ("numeric", C.c_int)]
+
+
+class Windows(C.Structure):
+    _fields_ = [("count", C.c_uint64), ("starts", u64p), ("lens", u32p), ("first", C.c_uint64),
+                ("step", C.c_uint64), ("window", C.c_uint32)]
+
+
+class PwmOut(C.Structure):
+    _fields_ = [("f", f64p), ("coords", u64p), ("status", i32p), ("aln_off", u64p), ("aln_len", u32p),
+                ("numbered", u32p), ("query", u8p), ("aln_slot", C.c_uint64), ("freq", f64p),
+                ("H", f64p), ("D", u8p)]
+
+
 class HeuristicOut(C.Structure):
     _fields_ = [("f", f64p), ("passes", i32p), ("status", i32p), ("coords", u64p), ("matrices", f64p)]
 
@@ -81,6 +97,12 @@ SIGNATURES = {
     "alnr_score_batch": (C.c_int, [C.POINTER(Params), C.POINTER(Batch), f64p, f64p, u32p, i32p]),
     "alnr_batch_create_scores": (C.c_int, [C.POINTER(Params), C.POINTER(Batch), C.POINTER(C.c_void_p)]),
     "alnr_batch_download_scores": (C.c_int, [C.c_void_p, f64p, f64p, u32p, i32p]),
+    "alnr_pwm_seq_create": (C.c_int, [u8p, C.c_uint64, C.c_int, C.POINTER(C.c_void_p)]),
+    "alnr_pwm_seq_len": (C.c_uint64, [C.c_void_p]),
+    "alnr_pwm_seq_destroy": (None, [C.c_void_p]),
+    "alnr_pwm_align_windows": (C.c_int, [C.POINTER(PwmParams), C.c_void_p, C.POINTER(Windows),
+                                         C.POINTER(PwmOut)]),
+    "alnr_pwm_last_numeric": (C.c_int, []),
     "alnr_transform_matrix": (C.c_int, [f64p, C.c_int, C.c_int, C.c_double, C.c_double, f64p, f64p]),
     "alnr_heuristic_batch": (C.c_int, [C.POINTER(Params), C.POINTER(Batch), C.POINTER(HeuristicItems),
                                        C.POINTER(HeuristicOut)]),

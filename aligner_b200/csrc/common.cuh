@@ -119,6 +119,31 @@ struct ChunkView {
   // sequence pair under many matrices, so several result slots share one pair of sequences.
   const uint32_t *seqmap = nullptr;
   __device__ __forceinline__ uint32_t seq(uint32_t pair) const { return seqmap ? seqmap[pair] : pair; }
+  // PWM windows (pwm/mod.rs:29-126; latent-repeat-search/engine/calc.rs:47-69): pwm_len = L > 0
+  // switches the view: item i is the window t[win_start(i), +win_len(i)) of ONE resident sequence
+  // (the DP rows) against the L columns of a 4 x L profile; there is no query sequence and the
+  // column "symbol" of column x is x - 1.  Windows are explicit (win_starts / win_lens) or strided.
+  uint32_t pwm_len = 0;
+  const uint64_t *win_starts = nullptr;
+  const uint32_t *win_lens = nullptr;
+  uint64_t win_first = 0, win_step = 0, seq_len = 0;
+  uint32_t win_size = 0;
+  __device__ __forceinline__ void pair_dims(uint32_t sp, const uint8_t *&qp, const uint8_t *&tp,
+                                            uint32_t &n, uint32_t &m) const {
+    if (pwm_len) {
+      uint64_t s0;
+      if (win_starts) { s0 = win_starts[sp]; m = win_lens[sp]; }
+      else {
+        s0 = win_first + (uint64_t)sp * win_step;
+        m = s0 >= seq_len ? 0u : (uint32_t)(seq_len - s0 < win_size ? seq_len - s0 : win_size);
+      }
+      qp = nullptr; tp = t + s0; n = pwm_len;
+    } else {
+      qp = q + q_off[sp]; tp = t + t_off[sp];
+      n = (uint32_t)(q_off[sp + 1] - q_off[sp]);
+      m = (uint32_t)(t_off[sp + 1] - t_off[sp]);
+    }
+  }
 };
 
 // Per-pair results produced by the fill kernels and consumed by the traceback.

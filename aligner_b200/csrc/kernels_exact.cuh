@@ -59,7 +59,10 @@ template <typename T>
 __global__ void __launch_bounds__(128) fill_exact_kernel(ExactArgs<T> a) {
   extern __shared__ unsigned char smem_raw[];
   T *smat_s = reinterpret_cast<T *>(smem_raw);
-  if (!a.item_matrices) for (int i = threadIdx.x; i < a.V * a.V; i += blockDim.x) smat_s[i] = a.matrix[i];
+  // PWM view (common.cuh): the matrix is the 4 x L profile, indexed [target symbol][column]
+  const bool pwm = a.cv.pwm_len != 0;
+  const int stride = pwm ? (int)a.cv.pwm_len : a.V, elems = pwm ? 4 * stride : a.V * a.V;
+  if (!a.item_matrices) for (int i = threadIdx.x; i < elems; i += blockDim.x) smat_s[i] = a.matrix[i];
   __syncthreads();
 
   const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -75,11 +78,10 @@ __global__ void __launch_bounds__(128) fill_exact_kernel(ExactArgs<T> a) {
   if (a.list) a.fo.status[pair] = 0;
 
   const uint32_t sp = a.cv.seq(pair);
-  const uint8_t *q = a.cv.q + a.cv.q_off[sp];
-  const uint8_t *t = a.cv.t + a.cv.t_off[sp];
-  const uint32_t n = (uint32_t)(a.cv.q_off[sp + 1] - a.cv.q_off[sp]);
-  const uint32_t m = (uint32_t)(a.cv.t_off[sp + 1] - a.cv.t_off[sp]);
-  const T *smat = a.item_matrices ? a.item_matrices + (size_t)pair * a.V * a.V : smat_s;
+  const uint8_t *q, *t;
+  uint32_t n, m;
+  a.cv.pair_dims(sp, q, t, n, m);
+  const T *smat = a.item_matrices ? a.item_matrices + (size_t)pair * elems : smat_s;
   const bool glob = a.mode == 0;
   const uint32_t group = idx >> 5, lane = idx & 31;  // score-column scratch is per thread
   T *hc = a.hcol + (uint64_t)group * a.hrows * 32 + lane;  // hc[y*32]
@@ -100,7 +102,7 @@ __global__ void __launch_bounds__(128) fill_exact_kernel(ExactArgs<T> a) {
   uint32_t by = 0, bx = 0;
   T last = T(0);
   for (uint32_t x = 1; x <= n; ++x) {
-    const int qs = q[x - 1];
+    const int qs = pwm ? (int)(x - 1) : q[x - 1];  // pwm/mod.rs:62
     // row 0 of this column (simple/mod.rs:59-62, :69)
     T hup = T(0);
     if (glob) hup = (x == n) ? -(T(n) + T(1)) * a.del : -T(x) * a.del;
@@ -111,7 +113,7 @@ __global__ void __launch_bounds__(128) fill_exact_kernel(ExactArgs<T> a) {
     uint32_t dword = 0;
     for (uint32_t y = 1; y <= m; ++y) {
       const T left = hc[(size_t)y * 32];
-      const T s = smat[(int)t[y - 1] * a.V + qs];
+      const T s = smat[(int)t[y - 1] * stride + qs];
       const T top = nsub(hup, pen);
       const T lft = nsub(left, pen);
       const T dg = nadd(diag, s);
@@ -148,7 +150,8 @@ __global__ void __launch_bounds__(128) fill_exact_kernel(ExactArgs<T> a) {
     a.fo.f[pair] = (double)best;  // simple/mod.rs:247
     a.fo.start[2 * (size_t)pair] = by;
     a.fo.start[2 * (size_t)pair + 1] = bx;
-    if (by == 0 || bx == 0) a.fo.status[pair] = 11;  // ALNR_NO_POSITIVE_CELL (simple/mod.rs:214)
+    // ALNR_NO_POSITIVE_CELL (simple/mod.rs:214); the PWM aligner returns an empty alignment
+    if ((by == 0 || bx == 0) && !pwm) a.fo.status[pair] = 11;
   }
 }
 

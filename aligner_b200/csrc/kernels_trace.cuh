@@ -12,6 +12,15 @@ static __global__ void validate_kernel(ChunkView cv, int V, int32_t *status, con
   if (slot >= cv.count) return;
   const uint32_t pair = cv.order ? cv.order[cv.first + slot] : cv.first + slot;
   const uint32_t sp = cv.seq(pair);
+  if (cv.pwm_len) {  // PWM window: an empty window is a valid (empty) alignment, pwm/mod.rs:76-81
+    const uint8_t *qp, *tp;
+    uint32_t n, m;
+    cv.pair_dims(sp, qp, tp, n, m);
+    int st = 0;
+    if (*flag) for (uint32_t i = 0; i < m && !st; ++i) if (tp[i] >= 4) st = 12;
+    status[pair] = st;
+    return;
+  }
   const uint64_t q0 = cv.q_off[sp], q1 = cv.q_off[sp + 1];
   const uint64_t t0 = cv.t_off[sp], t1 = cv.t_off[sp + 1];
   int st = 0;

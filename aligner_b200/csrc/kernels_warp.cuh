@@ -54,7 +54,9 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) fill_warp_kernel(WarpArgs
   extern __shared__ unsigned char smem_raw[];
   T *smem = reinterpret_cast<T *>(smem_raw);
   const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int V = a.V, VV = V * V;
+  // PWM view (common.cuh): the shared matrix is the 4 x L profile, a row of it per target symbol
+  const bool pwm = a.cv.pwm_len != 0;
+  const int V = pwm ? (int)a.cv.pwm_len : a.V, VV = pwm ? 4 * V : V * V;
   const uint32_t slot = blockIdx.x * kWarpsPerBlock + warp;
   bool have = slot < a.cv.count;
   uint32_t pair = 0;
@@ -86,10 +88,9 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) fill_warp_kernel(WarpArgs
   if (!have) return;
 
   const uint32_t sp = a.cv.seq(pair);
-  const uint8_t *q = a.cv.q + a.cv.q_off[sp];
-  const uint8_t *t = a.cv.t + a.cv.t_off[sp];
-  const uint32_t n = (uint32_t)(a.cv.q_off[sp + 1] - a.cv.q_off[sp]);
-  const uint32_t m = (uint32_t)(a.cv.t_off[sp + 1] - a.cv.t_off[sp]);
+  const uint8_t *q, *t;
+  uint32_t n, m;
+  a.cv.pair_dims(sp, q, t, n, m);
   constexpr uint32_t BH = 32 * R;  // rows per band
   const uint32_t nbands = (m + BH - 1) / BH;
   const uint32_t m_lane = ((m - 1) % BH) / R, m_r = (m - 1) % R;  // where row m lives (last band)
@@ -119,6 +120,13 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) fill_warp_kernel(WarpArgs
     }
   }
 
+  if (m == 0) {  // only PWM windows get here (pwm/mod.rs:76-81: arg-max (0,0), empty alignment)
+    if (lane == 0) {
+      a.fo.f[pair] = 0.0; a.fo.corner[pair] = 0.0;
+      a.fo.start[2 * (size_t)pair] = 0; a.fo.start[2 * (size_t)pair + 1] = 0;
+    }
+    return;
+  }
   T best = T(0), corner = T(0);
   uint32_t by = 0, bx = 0;
   bool settled = true;
@@ -142,7 +150,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) fill_warp_kernel(WarpArgs
       T dprev = (LOCAL || yb == 0) ? T(0) : -T(yb) * del;  // H[yb][0]
       T bottom = T(0);
       uint32_t zw = 0, zacc = 0;
-      uint32_t qn = q[0];
+      uint32_t qn = pwm ? 0u : q[0];
       uint32_t *dp = Dslot + band * band_words + lane;
       const bool store_d = yb < m && a.D != nullptr;  // score-only calls pass no D scratch
       const bool obs_lane = last_band && lane == m_lane;
@@ -157,8 +165,8 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) fill_warp_kernel(WarpArgs
             if (band == 0) { up = T(0); if (!LOCAL) up = (x == n) ? -(T(n) + T(1)) * del : -T(x) * del; }  // :59-62, :69
             else up = rowbuf[x];
           }
-          const uint32_t qs = qn;
-          if (x < n) qn = q[x];
+          const uint32_t qs = qn;  // PWM view: the column index itself (pwm/mod.rs:62)
+          if (x < n) qn = pwm ? x : q[x];
           T diag = dprev;
           dprev = up;
           T hup = up;
@@ -261,7 +269,8 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) fill_warp_kernel(WarpArgs
       a.fo.f[pair] = (double)best;  // simple/mod.rs:247
       a.fo.start[2 * (size_t)pair] = by;
       a.fo.start[2 * (size_t)pair + 1] = bx;
-      if (by == 0 || bx == 0) a.fo.status[pair] = 11;  // ALNR_NO_POSITIVE_CELL (simple/mod.rs:214)
+      // ALNR_NO_POSITIVE_CELL (simple/mod.rs:214); the PWM aligner returns an empty alignment
+      if ((by == 0 || bx == 0) && !pwm) a.fo.status[pair] = 11;
     } else {
       a.fo.f[pair] = 0.0;  // simple/mod.rs:139
       a.fo.start[2 * (size_t)pair] = m;

@@ -9,7 +9,10 @@ template <typename T, int R, int MODE, bool MATS>
 static int warp_launch_one(cudaStream_t stream, const WarpArgs<T> &a) {
   const unsigned blocks = (a.cv.count + kWarpsPerBlock - 1) / kWarpsPerBlock;
   if (blocks == 0) return ALNR_OK;
-  const size_t smem = (size_t)a.V * a.V * sizeof(T) * (a.item_matrices ? kWarpsPerBlock : 1);
+  const size_t elems = a.cv.pwm_len ? 4 * (size_t)a.cv.pwm_len : (size_t)a.V * a.V;
+  const size_t smem = elems * sizeof(T) * (a.item_matrices ? kWarpsPerBlock : 1);
+  if (smem > 48 * 1024)  // long PWM profiles
+    ALNR_CUDA(cudaFuncSetAttribute(fill_warp_kernel<T, R, MODE, MATS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   fill_warp_kernel<T, R, MODE, MATS><<<blocks, kWarpsPerBlock * 32, smem, stream>>>(a);
   ALNR_LAUNCHED();
   return ALNR_OK;

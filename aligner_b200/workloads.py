@@ -174,3 +174,29 @@ def dna_read_pairs_torch(first, count, n=150, seed=0xA11C0DE, sub_rate=0.10, dev
         q[b0:b1] = qb.cpu().numpy()
         t[b0:b1] = tb.cpu().numpy()
     return q, t
+
+
+def dna_chromosome_with_repeats(length, repeat_length=300, copies=40, seed=7, sub_rate=0.25, indel_rate=0.02):
+    """N1 synthetic (the shape of bin/latent-repeat-search's input): an i.i.d. DNA sequence with
+    `copies` diverged copies of one random repeat planted at random places.  Returns (codes uint8,
+    repeat uint8, planted start positions)."""
+    rng = np.random.default_rng(seed)
+    seq = rng.integers(0, 4, length).astype(np.uint8)
+    repeat = rng.integers(0, 4, repeat_length).astype(np.uint8)
+    starts = np.sort(rng.choice(max(length - 2 * repeat_length, 1), size=copies, replace=False))
+    for s in starts:
+        copy = repeat.copy()
+        mut = rng.random(repeat_length) < sub_rate
+        copy[mut] = rng.integers(0, 4, int(mut.sum()))
+        keep = rng.random(repeat_length) >= indel_rate
+        copy = copy[keep]
+        seq[s:s + len(copy)] = copy
+    return seq, repeat, starts
+
+
+def pwm_from_repeat(repeat, match=1.0, mismatch=-1.0):
+    """4 x L profile scoring `match` for the repeat's base at each position, `mismatch` otherwise."""
+    L = len(repeat)
+    pwm = np.full((4, L), float(mismatch))
+    pwm[repeat.astype(np.intp), np.arange(L)] = float(match)
+    return pwm

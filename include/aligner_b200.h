@@ -171,6 +171,62 @@ int alnr_batch_create_scores(const alnr_params *p, const alnr_batch *b, alnr_bat
 int alnr_batch_download_scores(alnr_batch_handle *h, double *f, double *corner, uint32_t *end_yx,
                                int32_t *status);
 
+/* ---- PWM aligner --------------------------------------------------------
+ * PWMAligner::perform_alignment (aligner-core/src/pwm/mod.rs:29-126): Smith-Waterman-like local
+ * alignment of a DNA window (the DP rows) against the L columns of a 4 x L position-weight matrix,
+ * score = matrix[[symbol, x-1]], same tie / Beginning / stateful-penalty rules as the local
+ * aligner.  Differences the reference has and this path keeps: no seed pair before the traceback
+ * (:81-104) and no error when the arg-max is (0,0) — the alignment is empty, f = 0, coords
+ * ((1,1),(1,1)).  The reference's batch workload aligns sliding windows of one chromosome to one
+ * PWM on OS threads (bin/latent-repeat-search/engine/calc.rs:47-69, :107-137): here the sequence
+ * is uploaded once (alnr_pwm_seq) and every call aligns any set of its windows to one PWM. */
+typedef struct {
+  double del, ext;
+  const double *pwm;  /* rows x length, row-major: matrix[[symbol, position]] */
+  uint32_t rows;      /* must be 4, else ALNR_MATRIX_SHAPE_ERROR (pwm/mod.rs:40-42) */
+  uint32_t length;    /* L = matrix.shape()[1] */
+  int device;         /* must be the device of the sequence; -1 = that device */
+  int numeric;        /* ALNR_NUM_AUTO, or ALNR_NUM_I32 / ALNR_NUM_F64 forced (tests) */
+} alnr_pwm_params;
+
+typedef struct alnr_pwm_seq alnr_pwm_seq; /* DNA codes 0..3 resident in HBM */
+int alnr_pwm_seq_create(const uint8_t *seq, uint64_t len, int device, alnr_pwm_seq **h);
+uint64_t alnr_pwm_seq_len(const alnr_pwm_seq *h);
+void alnr_pwm_seq_destroy(alnr_pwm_seq *h);
+
+/* Window i = seq[start_i, start_i + len_i).  Explicit: starts / lens (both non-NULL).  Strided
+ * (starts == NULL): start_i = first + i * step, len_i = min(window, seq_len - start_i) — the
+ * j..border windows of calc.rs:50-56 with step = query_offset, window = repeat_length + query_offset. */
+typedef struct {
+  uint64_t count;
+  const uint64_t *starts;
+  const uint32_t *lens;
+  uint64_t first, step;
+  uint32_t window;
+} alnr_windows;
+
+/* Caller-provided host arrays; any pointer may be NULL.  With numbered == query == freq == NULL the
+ * call is score-only (no direction scratch, no traceback).  Window i owns entries
+ * [i * aln_slot, (i + 1) * aln_slot) of numbered / query; its alignment is the aln_len[i] entries
+ * from aln_off[i] on (right-aligned in the slot).  aln_slot >= L + longest window. */
+typedef struct {
+  double *f;          /* [count] PWMAlignment.f = max of the matrix */
+  uint64_t *coords;   /* [count*4] ((x_from, x_to), (y_from, y_to)), pwm/mod.rs:118-121 */
+  int32_t *status;    /* [count] 0 or ALNR_SYMBOL_OUT_OF_RANGE */
+  uint64_t *aln_off;  /* [count] */
+  uint32_t *aln_len;  /* [count] */
+  uint32_t *numbered; /* PWMAlignment.numbered: profile position 1..L, 0 = gap (Top move) */
+  uint8_t *query;     /* PWMAlignment.query: window symbol, ALNR_BLANK = gap (Left move) */
+  uint64_t aln_slot;
+  double *freq;       /* [count*4*L] PWMAlignment::get_frequency_matrix (alignment.rs:55-65) */
+  double *H;          /* count == 1 only: alignment_matrix, (m+1) x (L+1) row-major */
+  uint8_t *D;         /* count == 1 only: direction_matrix, 1 byte per cell */
+} alnr_pwm_out;
+
+int alnr_pwm_align_windows(const alnr_pwm_params *p, alnr_pwm_seq *seq, const alnr_windows *w,
+                           alnr_pwm_out *out);
+int alnr_pwm_last_numeric(void); /* numeric domain of this thread's last alnr_pwm_align_windows */
+
 /* ---- heuristic matrix search ---------------------------------------------------------------
  * transform_matrix (aligner-helpers/src/matrices/mod.rs:19-68): rows x cols matrix, frequencies
  * [rows]; out may alias nothing.  Returns ALNR_WRONG_MATRIX on Roots::No. */

@@ -43,7 +43,8 @@ enum {
   ORC_NO_POSITIVE_CELL = 2,  /* simple/mod.rs:214 usize underflow when argmax == (0,0) */
   ORC_SYMBOL_OUT_OF_RANGE = 3, /* matrix[[t,q]] out of bounds */
   ORC_WRONG_MATRIX = 4,      /* aligner-helpers/src/lib.rs:12-14 WrongMatrixSpecified */
-  ORC_BUFFER_TOO_SMALL = 5
+  ORC_BUFFER_TOO_SMALL = 5,
+  ORC_MATRIX_SHAPE_ERROR = 6 /* pwm/mod.rs:40-42 MatrixShapeError */
 };
 
 /* enums.rs:18-28 and :30-46.  Returns the max through *v, the direction as return value. */
@@ -129,6 +130,26 @@ int orc_heuristic_batch(const uint8_t *qs, const uint64_t *qoff, const uint8_t *
                         const double *freqs /* per pair, V each */, int threads, double *f,
                         int *passes, double *out_matrices /* items*V*V or NULL */,
                         int *status);
+
+/*
+ * pwm/mod.rs:29-126 PWMAligner::perform_alignment (oracle_pwm.cpp; parity unpinned, see there).
+ * query: m window symbols (rows); pwm: rows x L row-major, rows must be 4.
+ * H_out / D_out: optional (m+1) x (L+1).  numbered / q_aln: PWMAlignment.numbered / .query
+ * (0 = gap in the profile, ORC_BLANK = gap in the window), *aln_len entries.
+ * coords[4] = {x_from, x_to, y_from, y_to} (pwm/mod.rs:118-121).
+ */
+int orc_pwm_align(const uint8_t *query, size_t m, const double *pwm, size_t rows, size_t L,
+                  double del, double ext, double *H_out, uint8_t *D_out, uint32_t *numbered,
+                  uint8_t *q_aln, size_t aln_cap, size_t *aln_len, uint64_t *coords, double *f);
+/* alignment.rs:55-65 PWMAlignment::get_frequency_matrix -> out[4 * L] */
+void orc_pwm_frequency_matrix(const uint32_t *numbered, const uint8_t *q_aln, size_t len, size_t L,
+                              double *out);
+/* windows seq[starts[i], +lens[i]) against one PWM on `threads` threads
+ * (latent-repeat-search/engine/calc.rs:47-69, :107-137); alignment slots of `slot` entries. */
+void orc_pwm_windows(const uint8_t *seq, const uint64_t *starts, const uint32_t *lens, size_t count,
+                     const double *pwm, size_t L, double del, double ext, int threads, double *f,
+                     uint64_t *coords, uint64_t *aln_len, uint32_t *numbered, uint8_t *q_aln,
+                     size_t slot, int32_t *status);
 
 #ifdef __cplusplus
 }

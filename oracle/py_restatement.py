@@ -213,3 +213,61 @@ def heuristic(q, t, dele, ext, matrix, kd, r_squared, freq):
             T = transform_matrix(frequency_matrix(res["q_aln"], res["t_aln"], V), kd, r_squared, freq)
         else:
             return res, T, passes
+
+
+def pwm_align(query, pwm, dele, ext):
+    """aligner-core/src/pwm/mod.rs:29-126.  query: window symbols (rows); pwm: 4 rows of L scores.
+    Returns dict with H, D, numbered, q_aln, coords ((a,b),(c,d)), f."""
+    if len(pwm) != 4:
+        raise ValueError("MatrixShapeError")           # :40-42
+    L = len(pwm[0])
+    numbered_sequence = list(range(1, L + 1))          # :44
+    m = len(query)
+    H = [[0.0] * (L + 1) for _ in range(m + 1)]        # :48
+    D = [[BEGINNING] * (L + 1) for _ in range(m + 1)]  # :49-50
+    penalty = dele                                     # :52
+    for elem_1 in numbered_sequence:                   # :54
+        for y, elem_2 in enumerate(query):             # :55
+            y_real = y + 1
+            v, d = get_direction(H[y_real - 1][elem_1] - penalty, H[y_real][elem_1 - 1] - penalty,
+                                 H[y_real - 1][elem_1 - 1] + pwm[elem_2][elem_1 - 1], True)  # :59-63
+            penalty = ext if d != BEGINNING else dele  # :65-69
+            H[y_real][elem_1] = v
+            D[y_real][elem_1] = d
+    best, my, mx = H[0][0], 0, 0                       # :76 argmax: first maximum, row-major
+    for y in range(m + 1):
+        for x in range(L + 1):
+            if H[y][x] > best:
+                best, my, mx = H[y][x], y, x
+    numbered, qa = [], []
+    cx, cy = mx, my
+    while True:                                        # :81-104
+        d = D[cy][cx]
+        if d == BEGINNING:
+            break
+        if d == TOP:
+            numbered.append(0)
+            qa.append(query[cy - 1])
+            cy -= 1
+        elif d == LEFT:
+            numbered.append(numbered_sequence[cx - 1])
+            qa.append(BLANK)
+            cx -= 1
+        else:
+            numbered.append(numbered_sequence[cx - 1])
+            qa.append(query[cy - 1])
+            cx -= 1
+            cy -= 1
+    numbered.reverse()
+    qa.reverse()
+    return dict(H=H, D=D, numbered=numbered, q_aln=qa, f=best,
+                coords=((cx + 1, mx + 1), (cy + 1, my + 1)))  # :118-121
+
+
+def pwm_frequency_matrix(numbered, qa, L):
+    """aligner-core/src/alignment.rs:55-65"""
+    F = [[0.0] * L for _ in range(4)]
+    for x, y in zip(numbered, qa):
+        if x != 0 and y != BLANK:
+            F[y][x - 1] += 1.0
+    return F

@@ -122,6 +122,44 @@ def n2():
             db.close()
 
 
+def n1(length=20_000_000):
+    """N1: one cycle of bin/latent-repeat-search's window scan (engine/calc.rs:107-137): windows of
+    repeat_length + query_offset = 330 every query_offset = 30 bases against a 4 x 300 FP64 profile."""
+    from aligner_b200 import pwm as P
+    import oracle_lib as O
+    seq, repeat, _ = W.dna_chromosome_with_repeats(length, 300, 200, seed=9)
+    pwm = W.pwm_from_repeat(repeat, 1.0, -1.0) + 0.03125 * np.random.default_rng(2).normal(0, 1, (4, 300))
+    t0 = time.perf_counter()
+    rs = P.ResidentSequence(seq)
+    up = time.perf_counter() - t0
+    rs.align_windows(pwm, 5.0, 5.0, first=0, step=30, window=330, count=1000)  # warm-up
+    for d, e, tag in [(5.0, 5.0, "del == ext"), (6.0, 2.0, "stateful penalty")]:
+        best = 1e9
+        for _ in range(2):
+            t0 = time.perf_counter()
+            res = rs.align_windows(pwm, d, e, first=0, step=30, window=330)
+            best = min(best, time.perf_counter() - t0)
+        starts = np.arange(0, length, 30, dtype=np.uint64)
+        lens = np.minimum(330, length - starts).astype(np.uint32)
+        cells = float(lens.astype(np.float64).sum()) * 300
+        # bounded CPU sample of the same windows on all host threads + parity of that sample
+        sub = np.arange(0, len(starts), max(1, len(starts) // 4000))
+        t0 = time.perf_counter()
+        ref = O.pwm_windows(seq, starts[sub], lens[sub], pwm, d, e, threads=os.cpu_count() or 8, want_alignments=False)
+        cpu = time.perf_counter() - t0
+        emit("N1 PWM window scan: %d bp, %d windows of 330 vs 4x300 FP64 profile, %s, score-only (call incl. D2H)"
+             % (length, res.count, tag), cells, best, upload_seconds=up, parity=bool((res.f[sub] == ref["f"]).all()),
+             cpu_gcups=float(lens[sub].astype(np.float64).sum()) * 300 / cpu / 1e9, cpu_threads=os.cpu_count(),
+             hits_z3=int((res.f > res.f.mean() + 3 * res.f.std()).sum()))
+        hits = np.flatnonzero(res.f > res.f.mean() + 3 * res.f.std())
+        t0 = time.perf_counter()
+        al = rs.align_windows(pwm, d, e, starts=starts[hits], lens=lens[hits], want_alignments=True, want_freq=True)
+        emit("N1 PWM alignments + frequency matrices of the z >= 3 hits (%d windows), %s" % (len(hits), tag),
+             float(lens[hits].astype(np.float64).sum()) * 300, time.perf_counter() - t0,
+             mean_aln_len=float(al.aln_len.mean()) if len(hits) else 0.0)
+    rs.close()
+
+
 if __name__ == "__main__":
     what = sys.argv[1:] or ["c12", "c4"]
     if N.lib().alnr_device_count() < 1:
@@ -136,6 +174,8 @@ if __name__ == "__main__":
         c5(200, 50)
     if "c5big" in what:
         c5(2000, 100)
+    if "n1" in what:
+        n1()
     if "n2" in what:
         n2()
     if "peaks" in what:

@@ -55,6 +55,14 @@ def lib():
         L.orc_heuristic_batch.argtypes = [u8p, u64p, u8p, u64p, u32p, u32p, C.c_size_t, C.c_double,
                                           C.c_double, f64p, C.c_int, C.c_double, C.c_double, f64p,
                                           C.c_int, f64p, i32p, f64p, i32p]
+        L.orc_pwm_align.restype = C.c_int
+        L.orc_pwm_align.argtypes = [u8p, C.c_size_t, f64p, C.c_size_t, C.c_size_t, C.c_double, C.c_double,
+                                    f64p, u8p, u32p, u8p, C.c_size_t, C.POINTER(C.c_size_t), u64p, f64p]
+        L.orc_pwm_frequency_matrix.restype = None
+        L.orc_pwm_frequency_matrix.argtypes = [u32p, u8p, C.c_size_t, C.c_size_t, f64p]
+        L.orc_pwm_windows.restype = None
+        L.orc_pwm_windows.argtypes = [u8p, u64p, u32p, C.c_size_t, f64p, C.c_size_t, C.c_double, C.c_double,
+                                      C.c_int, f64p, u64p, u64p, u32p, u8p, C.c_size_t, i32p]
         L.orc_ndarray_sum.restype = C.c_double
         L.orc_ndarray_sum.argtypes = [f64p, C.c_size_t]
         L.orc_find_roots_quadratic.restype = C.c_int
@@ -70,7 +78,7 @@ def _p(a, ty):
 
 
 MODES = {"global": 0, "local": 1, 0: 0, 1: 1}
-STATUS_TO_ALNR = {0: 0, 1: 10, 2: 11, 3: 12, 4: 9, 5: 14}  # oracle status -> alnr_status
+STATUS_TO_ALNR = {0: 0, 1: 10, 2: 11, 3: 12, 4: 9, 5: 14, 6: 8}  # oracle status -> alnr_status
 
 
 def align_pair(mode, q, t, del_, ext, matrix, want_matrices=True, lean=False):
@@ -157,3 +165,52 @@ def heuristic(q, t, del_, ext, matrix, kd, r_squared, freq):
     return dict(status=st, f=f.value, q_aln=qa[:L.value].copy(), t_aln=ta[:L.value].copy(),
                 coords=((int(coords[0]), int(coords[1])), (int(coords[2]), int(coords[3]))),
                 matrix=om, passes=passes.value)
+
+
+def pwm_align(query, pwm, del_, ext, want_matrices=True):
+    """orc_pwm_align -> dict(status, f, coords, numbered, q_aln, H, D)."""
+    q = np.ascontiguousarray(query, dtype=np.uint8)
+    mat = np.ascontiguousarray(pwm, dtype=np.float64)
+    rows, L = mat.shape
+    m = len(q)
+    cap = m + L + 1
+    num = np.zeros(cap, dtype=np.uint32)
+    qa = np.zeros(cap, dtype=np.uint8)
+    n = C.c_size_t(0)
+    coords = np.zeros(4, dtype=np.uint64)
+    f = C.c_double(0)
+    H = np.zeros((m + 1, L + 1), dtype=np.float64) if want_matrices else None
+    D = np.zeros((m + 1, L + 1), dtype=np.uint8) if want_matrices else None
+    st = lib().orc_pwm_align(_p(q, u8p), m, _p(mat, f64p), rows, L, del_, ext, _p(H, f64p), _p(D, u8p),
+                             _p(num, u32p), _p(qa, u8p), cap, C.byref(n), _p(coords, u64p), C.byref(f))
+    return dict(status=st, f=f.value, numbered=num[:n.value].copy(), q_aln=qa[:n.value].copy(), H=H, D=D,
+                coords=((int(coords[0]), int(coords[1])), (int(coords[2]), int(coords[3]))))
+
+
+def pwm_frequency_matrix(numbered, q_aln, L):
+    num = np.ascontiguousarray(numbered, dtype=np.uint32)
+    qa = np.ascontiguousarray(q_aln, dtype=np.uint8)
+    out = np.zeros((4, L), dtype=np.float64)
+    lib().orc_pwm_frequency_matrix(_p(num, u32p), _p(qa, u8p), len(num), L, _p(out, f64p))
+    return out
+
+
+def pwm_windows(seq, starts, lens, pwm, del_, ext, threads=8, want_alignments=True):
+    """orc_pwm_windows -> dict(f, coords, aln_len, numbered[count, slot], q_aln[count, slot], status)."""
+    s = np.ascontiguousarray(seq, dtype=np.uint8)
+    st_a = np.ascontiguousarray(starts, dtype=np.uint64)
+    ln_a = np.ascontiguousarray(lens, dtype=np.uint32)
+    mat = np.ascontiguousarray(pwm, dtype=np.float64)
+    L = mat.shape[1]
+    c = len(st_a)
+    slot = L + (int(ln_a.max()) if c else 0) + 1
+    f = np.zeros(c)
+    coords = np.zeros((c, 4), dtype=np.uint64)
+    alen = np.zeros(c, dtype=np.uint64)
+    status = np.zeros(c, dtype=np.int32)
+    num = np.zeros((c, slot), dtype=np.uint32) if want_alignments else None
+    qa = np.zeros((c, slot), dtype=np.uint8) if want_alignments else None
+    lib().orc_pwm_windows(_p(s, u8p), _p(st_a, u64p), _p(ln_a, u32p), c, _p(mat, f64p), L, del_, ext, threads,
+                          _p(f, f64p), _p(coords, u64p), _p(alen, u64p), _p(num, u32p), _p(qa, u8p), slot,
+                          _p(status, i32p))
+    return dict(f=f, coords=coords, aln_len=alen, numbered=num, q_aln=qa, status=status)

@@ -182,3 +182,43 @@ def test_oracle_batch_threads_agree():
         assert (a[k] == b[k]).all()
     one = O.align_pair("local", *pairs.pair(17), 10.0, 2.0, dna_matrix())
     assert one["f"] == a["f"][17] and (one["q_aln"] == a["q_aln"][17][: len(one["q_aln"])]).all()
+
+
+@pytest.mark.parametrize("integral", [True, False])
+def test_pwm_oracle_vs_python_restatement(integral):
+    """oracle_pwm.cpp against the independently written Python text of pwm/mod.rs:29-126 (the
+    reference has no PWM vectors: this row's parity is unpinned, see oracle_pwm.cpp)."""
+    rng = np.random.default_rng(21 if integral else 22)
+    for it in range(200):
+        m, L = int(rng.integers(0, 40)), int(rng.integers(0, 30))
+        q = rng.integers(0, 4, m).astype(np.uint8)
+        pwm = rng.integers(-3, 4, (4, L)).astype(np.float64) if integral else rng.normal(0, 1.5, (4, L))
+        d, e = [(3.0, 1.0), (2.0, 2.0), (1.25, 0.5)][it % 3]
+        a = O.pwm_align(q, pwm, d, e)
+        b = PY.pwm_align(list(q), pwm.tolist(), d, e)
+        assert a["status"] == 0 and a["f"] == b["f"] and a["coords"] == b["coords"]
+        assert list(a["numbered"]) == b["numbered"] and list(a["q_aln"]) == b["q_aln"]
+        assert (a["H"] == np.array(b["H"]).reshape(m + 1, L + 1)).all()
+        assert (a["D"] == np.array(b["D"]).reshape(m + 1, L + 1)).all()
+        if L:
+            F = O.pwm_frequency_matrix(a["numbered"], a["q_aln"], L)
+            assert (F == np.array(PY.pwm_frequency_matrix(b["numbered"], b["q_aln"], L))).all()
+
+
+def test_pwm_oracle_statuses_and_windows():
+    q = np.array([0, 1, 2, 3, 1], dtype=np.uint8)
+    assert O.pwm_align(q, np.ones((5, 3)), 1.0, 1.0)["status"] == 6          # MatrixShapeError
+    assert O.pwm_align(np.array([0, 9], dtype=np.uint8), np.ones((4, 3)), 1.0, 1.0)["status"] == 3
+    r = O.pwm_align(q, -np.ones((4, 3)), 1.0, 1.0)                           # arg-max (0,0): no error
+    assert r["status"] == 0 and r["f"] == 0.0 and len(r["numbered"]) == 0 and r["coords"] == ((1, 1), (1, 1))
+    rng = np.random.default_rng(23)
+    seq = rng.integers(0, 4, 500).astype(np.uint8)
+    pwm = rng.integers(-1, 2, (4, 20)).astype(np.float64)
+    starts = np.arange(0, 480, 13, dtype=np.uint64)
+    lens = np.minimum(30, 500 - starts).astype(np.uint32)
+    w1 = O.pwm_windows(seq, starts, lens, pwm, 2.0, 1.0, threads=1)
+    w8 = O.pwm_windows(seq, starts, lens, pwm, 2.0, 1.0, threads=8)
+    for k in ("f", "coords", "aln_len", "numbered", "q_aln", "status"):
+        assert (w1[k] == w8[k]).all()
+    one = O.pwm_align(seq[13:43], pwm, 2.0, 1.0)
+    assert one["f"] == w1["f"][1] and (one["numbered"] == w1["numbered"][1, :len(one["numbered"])]).all()
