@@ -35,13 +35,18 @@ struct HeurState {
   const int32_t *pair_status;
 };
 
+// Both kernels below give every item a group of 8 lanes (transform_matrix_g8): grid = items * 8 threads.
 static __global__ void heur_init_kernel(HeurState h, uint32_t items, uint32_t *list, uint32_t *count) {
-  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t i = tid >> 3;
   if (i >= items) return;
+  const int gl = threadIdx.x & 7;
+  const unsigned gmask = 0xffu << (threadIdx.x & 24);
   const int VV = h.V * h.V;
   int st = h.pair_status[h.pair_idx[i]];
-  if (!st) st = transform_matrix_rc(h.matrices + (size_t)h.mat_idx[i] * VV, h.V, h.V, h.kd, h.r2,
-                                    h.freqs + (size_t)h.pair_idx[i] * h.V, h.Tcur + (size_t)i * VV);
+  if (!st) st = transform_matrix_g8(h.matrices + (size_t)h.mat_idx[i] * VV, h.V, h.V, h.kd, h.r2,
+                                    h.freqs + (size_t)h.pair_idx[i] * h.V, h.Tcur + (size_t)i * VV, gmask, gl);
+  if (gl != 0) return;
   h.status[i] = st;
   h.maxf[i] = 0.0;  // heuristic/mod.rs:55
   h.passes[i] = 0;
@@ -52,23 +57,31 @@ static __global__ void heur_init_kernel(HeurState h, uint32_t items, uint32_t *l
 // after fill + traceback of one round
 static __global__ void heur_update_kernel(HeurState h, const uint32_t *list, uint32_t n_active,
                                           uint32_t *next, uint32_t *next_count) {
-  const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t k = tid >> 3;
   if (k >= n_active) return;
+  const int gl = threadIdx.x & 7;
+  const unsigned gmask = 0xffu << (threadIdx.x & 24);
   const uint32_t i = list[k];
   const int VV = h.V * h.V;
   if (h.status[i] != 0) return;  // e.g. 11: no positive cell — the reference panics (simple/mod.rs:214)
-  h.passes[i] += 1;
   const double f = h.fcur[i];
+  const bool improved = f > h.maxf[i];  // heuristic/mod.rs:64
+  __syncwarp(gmask);                    // every lane has read maxf before lane 0 updates it
   double *T = h.Tcur + (size_t)i * VV, *L = h.Tlast + (size_t)i * VV;
-  if (f > h.maxf[i]) {  // heuristic/mod.rs:64
+  if (improved) {
+    const int st = transform_matrix_g8(h.freqm + (size_t)i * VV, h.V, h.V, h.kd, h.r2,
+                                       h.freqs + (size_t)h.pair_idx[i] * h.V, T, gmask, gl);  // :66-72
+    if (gl != 0) return;
+    h.passes[i] += 1;
     h.maxf[i] = f;
-    const int st = transform_matrix_rc(h.freqm + (size_t)i * VV, h.V, h.V, h.kd, h.r2,
-                                       h.freqs + (size_t)h.pair_idx[i] * h.V, T);  // :66-72
     if (st) { h.status[i] = st; return; }  // .unwrap() panic in the reference
     next[atomicAdd(next_count, 1u)] = i;
   } else {  // :73-76 — the LAST (non-improving) result and the matrix that produced it
+    for (int j = gl; j < VV; j += 8) L[j] = T[j];
+    if (gl != 0) return;
+    h.passes[i] += 1;
     h.fout[i] = f;
-    for (int j = 0; j < VV; ++j) L[j] = T[j];
     for (int j = 0; j < 4; ++j) h.coords_out[4 * (size_t)i + j] = h.coords_cur[4 * (size_t)i + j];
   }
 }
@@ -185,7 +198,7 @@ extern "C" int alnr_heuristic_batch(const alnr_params *p, const alnr_batch *b,
     uint32_t *lists[2] = {d_lists.p, d_lists.p + chunk};
     ALNR_CUDA(cudaMemsetAsync(d_cnt.p, 0, 64 * sizeof(uint32_t), stream));
     ALNR_CUDA(cudaMemsetAsync(d_co.p, 0, (size_t)cnt * 32, stream));
-    heur_init_kernel<<<(cnt + 127) / 128, 128, 0, stream>>>(hs, cnt, lists[0], d_cnt.p); ALNR_LAUNCHED();
+    heur_init_kernel<<<(cnt + 15) / 16, 128, 0, stream>>>(hs, cnt, lists[0], d_cnt.p); ALNR_LAUNCHED();
     uint32_t n_active = 0;
     ALNR_CUDA(cudaMemcpyAsync(&n_active, d_cnt.p, 4, cudaMemcpyDeviceToHost, stream));
     ALNR_CUDA(cudaStreamSynchronize(stream));
@@ -216,8 +229,17 @@ extern "C" int alnr_heuristic_batch(const alnr_params *p, const alnr_batch *b,
       }
       TraceOut to{d_cc.p, nullptr, nullptr, nullptr, nullptr, d_F.p};
       TraceArgs ta{cv, ALNR_LOCAL, V, d_D.p, dl0, fo, to};
-      traceback_kernel<<<(n_active + 127) / 128, 128, 0, stream>>>(ta); ALNR_LAUNCHED();
-      heur_update_kernel<<<(n_active + 127) / 128, 128, 0, stream>>>(hs, cur, n_active, nxt, cnt_next); ALNR_LAUNCHED();
+      // one warp per item, counts in shared memory (kernels_trace.cuh); very long pairs whose staged
+      // sequences do not fit shared memory take the one-thread-per-item kernel
+      const size_t tsm = 4 * ((size_t)VV + ((n_max + 7) / 8 * 8 + (m_max + 7) / 8 * 8) / 8) * sizeof(double);
+      if (tsm <= 200 * 1024) {
+        if (tsm > 48 * 1024)
+          ALNR_CUDA(cudaFuncSetAttribute(traceback_freq_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsm));
+        traceback_freq_warp_kernel<<<(n_active + 3) / 4, 128, tsm, stream>>>(ta, n_max, m_max); ALNR_LAUNCHED();
+      } else {
+        traceback_kernel<<<(n_active + 127) / 128, 128, 0, stream>>>(ta); ALNR_LAUNCHED();
+      }
+      heur_update_kernel<<<(n_active + 15) / 16, 128, 0, stream>>>(hs, cur, n_active, nxt, cnt_next); ALNR_LAUNCHED();
       ALNR_CUDA(cudaMemcpyAsync(&n_active, cnt_next, 4, cudaMemcpyDeviceToHost, stream));
       ALNR_CUDA(cudaStreamSynchronize(stream));
     }

@@ -485,4 +485,79 @@ static __global__ void __launch_bounds__(32) traceback_warp_kernel(TraceArgs a) 
   }
 }
 
+// Traceback of the matrix search (heur.cu): one WARP per item through the "skewed" D layout of the
+// warp fill kernel; only the coords and the frequency matrix of the alignment (alignment.rs:13-23)
+// are produced.  Every lane holds the same (cy, cx); before each stretch the 32 lanes fetch a
+// window of 2 strips x 16 columns up-left of the current cell in one batch of independent loads
+// and the walk takes its words from the owning lane by shuffle, so the chain pays one L2 latency
+// per ~14 steps instead of one per step.  The counts are kept in shared memory (lane 0 adds) and
+// written once, coalesced; the two sequences are staged in shared memory too.
+// grid: ceil(count / 4) blocks of 128 threads; smem: 4 * (V*V*8 + pad8(n_max) + pad8(m_max)).
+static __global__ void __launch_bounds__(128) traceback_freq_warp_kernel(TraceArgs a, uint32_t n_max, uint32_t m_max) {
+  extern __shared__ double trace_smem[];
+  const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t slot = blockIdx.x * 4 + warp;
+  if (slot >= a.cv.count) return;
+  const uint32_t pair = a.cv.order ? a.cv.order[a.cv.first + slot] : a.cv.first + slot;
+  const int VV = a.V * a.V;
+  const uint32_t nq = (n_max + 7) / 8 * 8, nt = (m_max + 7) / 8 * 8;
+  double *sf = trace_smem + (size_t)warp * (VV + (nq + nt) / 8);
+  uint8_t *sq = reinterpret_cast<uint8_t *>(sf + VV), *st = sq + nq;
+  double *freq = a.to.freq + (size_t)pair * VV;
+  if (a.fo.status[pair] != 0) {
+    for (int i = lane; i < VV; i += 32) freq[i] = 0.0;
+    if (lane == 0 && a.to.coords) for (int k = 0; k < 4; ++k) a.to.coords[4 * (size_t)pair + k] = 0;
+    return;
+  }
+  const uint32_t sp = a.cv.seq(pair);
+  const uint8_t *q, *t;
+  uint32_t n, m;
+  a.cv.pair_dims(sp, q, t, n, m);
+  for (int i = lane; i < VV; i += 32) sf[i] = 0.0;
+  for (uint32_t i = lane; i < n; i += 32) sq[i] = q[i];
+  for (uint32_t i = lane; i < m; i += 32) st[i] = t[i];
+  __syncwarp();
+  const uint32_t R = a.dl.rows_per_word;
+  const uint32_t sy = a.fo.start[2 * (size_t)pair], sx = a.fo.start[2 * (size_t)pair + 1];
+  uint32_t cy = sy, cx = sx;
+  const uint32_t *Dslot = a.D + (uint64_t)slot * a.dl.nstrips * (a.dl.ncols + 31);
+  auto word_at = [&](uint32_t strip, uint32_t xm1) {
+    const uint32_t band = strip >> 5, l = strip & 31;
+    return Dslot[((uint64_t)band * (a.dl.ncols + 31) + xm1 + l) * 32ull + l];
+  };
+  auto emit = [&](uint32_t qc, uint32_t tc) {
+    if (lane == 0 && qc != (uint32_t)kBlank && tc != (uint32_t)kBlank) sf[tc * a.V + qc] += 1.0;  // alignment.rs:16-20
+  };
+  emit(sq[cx - 1], st[cy - 1]);  // seed (simple/mod.rs:213-216)
+  uint32_t strip = (cy - 1) / R, r = (cy - 1) % R;  // kept incrementally: no division on the chain
+  bool done = false;
+  while (!done) {
+    // ---- window: strips strip0, strip0 - 1; columns cx0 - 1 ... cx0 - 16 (0-based xm1) -------
+    const uint32_t strip0 = strip, x0 = cx;  // x0 >= 1 here
+    uint32_t my_w = 0;
+    {
+      const uint32_t j = lane >> 4, k = lane & 15;
+      if (j <= strip0 && k < x0) my_w = word_at(strip0 - j, x0 - 1 - k);
+    }
+    for (;;) {
+      if (cy == 0 || cx == 0) { done = true; break; }  // local mode: row 0 / column 0 are Beginning
+      const uint32_t j = strip0 - strip, k = x0 - cx;
+      if (j >= 2 || k >= 16) break;  // next window
+      const uint32_t w = __shfl_sync(0xffffffffu, my_w, j * 16 + k);
+      const uint32_t d = (w >> (2 * r)) & 3u;
+      if (d == DIR_BEGINNING) { done = true; break; }
+      const bool up = d != DIR_LEFT, left = d != DIR_TOP;
+      emit(left ? sq[cx - 1] : (uint32_t)kBlank, up ? st[cy - 1] : (uint32_t)kBlank);
+      if (up) { --cy; if (r == 0) { r = R - 1; --strip; } else --r; }
+      if (left) --cx;
+    }
+  }
+  __syncwarp();
+  for (int i = lane; i < VV; i += 32) freq[i] = sf[i];
+  if (lane == 0 && a.to.coords) {
+    uint64_t *c = a.to.coords + 4 * (size_t)pair;
+    c[0] = cx + 1; c[1] = sx + 1; c[2] = cy + 1; c[3] = sy + 1;  // simple/mod.rs:254-257
+  }
+}
+
 }  // namespace alnr

@@ -91,4 +91,58 @@ __host__ __device__ inline int transform_matrix_rc(const double *M, int R, int C
   return 0;
 }
 
+#ifdef __CUDACC__
+// The same routine run by a GROUP of 8 consecutive lanes (gl = lane & 7, gmask = the group's lanes):
+// ndarray's eight running partial sums are independent chains, so lane j keeps p_j; the combine
+// and the tail follow the same order as nd_sum, every lane ends up with the same bits.  Element-
+// wise work is strided over the group.  All 8 lanes must call it together.
+template <class F>
+__device__ inline double nd_sum_g8(int N, F f, unsigned gmask, int gl) {
+  double p = 0.0;
+  int i = 0;
+  for (; i + 8 <= N; i += 8) p = p + f(i + gl);
+  const double s = p + __shfl_down_sync(gmask, p, 4, 8);  // lanes 0..3: p_j + p_{j+4}
+  double acc = 0.0;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) acc = acc + __shfl_sync(gmask, s, j, 8);
+  for (; i < N; ++i) acc = acc + f(i);
+  return acc;
+}
+
+__device__ inline int transform_matrix_g8(const double *M, int R, int C, double k_d, double r_squared,
+                                          const double *freq, double *out, unsigned gmask, int gl) {
+  const int N = R * C;
+  const double fcol = 1.0 / (double)C;
+  auto p = [&](int i) { return freq[i / C] * fcol; };
+  const double p_squared = nd_sum_g8(N, [&](int i) { double v = p(i); return v * v; }, gmask, gl);
+  const double k_0 = nd_sum_g8(N, [&](int i) { return p(i) * M[i]; }, gmask, gl);
+  const double a = (k_d - k_0) / p_squared;
+  const double b = k_d / p_squared;
+  const double difference = a - b;
+  auto e = [&](int i) { return M[i] + p(i) * difference; };
+  const double denominator = nd_sum_g8(N, [&](int i) { double v = e(i); return v * v; }, gmask, gl);
+  const double a_coeff = (2.0 * b * nd_sum_g8(N, [&](int i) { return p(i) * e(i); }, gmask, gl)) / denominator;
+  const double b_coeff = (b * b * p_squared - r_squared) / denominator;
+  double roots[2];
+  const int nr = roots_quadratic_monic(a_coeff, b_coeff, roots);
+  if (nr == 0) return 9;
+  auto elem = [&](double root, int i) { return p(i) * b + root * (M[i] + p(i) * (a - b)); };
+  double pick;
+  if (nr == 1) pick = roots[0];
+  else if (roots[0] > 0.0 && roots[1] < 0.0) pick = roots[0];
+  else if (roots[0] < 0.0 && roots[1] > 0.0) pick = roots[1];
+  else {  // l2_dist is a sequential fold: every lane runs it (same bits), rare branch
+    double s1 = 0.0, s2 = 0.0;
+    for (int i = 0; i < N; ++i) {
+      const double d1 = M[i] - elem(roots[0], i), d2 = M[i] - elem(roots[1], i);
+      s1 += d1 * d1;
+      s2 += d2 * d2;
+    }
+    pick = (sqrt(s1) < sqrt(s2)) ? roots[0] : roots[1];
+  }
+  for (int i = gl; i < N; i += 8) out[i] = elem(pick, i);
+  return 0;
+}
+#endif
+
 }  // namespace alnr
