@@ -84,6 +84,27 @@ def c5(P, K):
          items=P * K, mean_passes=float(passes.mean()), ok_items=int((res.status == 0).sum()))
 
 
+def n3(length=20_000_000):
+    """N3: the repeat-search engine loop (engine/calc.rs:149-241) on a synthetic chromosome with planted
+    repeats: shuffle scan for mean / std, then `repeats` cycles of scan -> z filter -> align hits ->
+    overlap filter -> PWM rebuild (reference defaults: 300 / 30, del 30, ext 7)."""
+    from aligner_b200 import repeat_search as R
+    seq, repeat, planted = W.dna_chromosome_with_repeats(length, 300, 400, seed=11, sub_rate=0.2)
+    raw = np.frombuffer(b"ATCG", dtype=np.uint8)[seq].tobytes()
+    opts = R.Options(repeats=3)
+    start = W.pwm_from_repeat(repeat, 1.0, -1.0)
+    R.perform_calculation_per_sequence(R.Options(repeats=1), raw[:200000], "warm", np.random.default_rng(0), matrix=start)
+    t0 = time.perf_counter()
+    res = R.perform_calculation_per_sequence(opts, raw, "chr", np.random.default_rng(1), matrix=start)
+    secs = time.perf_counter() - t0
+    windows = (length + 29) // 30
+    cells = 4.0 * windows * 330 * 300  # one shuffled scan + three cycles
+    tasks = res["direct"][0]
+    emit("N3 repeat search: %d bp, 1 shuffled scan + 3 cycles of %d windows (330 x 300 FP64), hits aligned, PWM rebuilt"
+         % (length, windows), cells, secs, hits=len(tasks), planted=len(planted),
+         strong_hits=int(sum(t.z >= 8 for t in tasks)))
+
+
 def n2():
     """N2: the p-value shuffle batch (statistics/mod.rs:255-292) and the C3 reads, score-only."""
     from aligner_b200 import statistics as S
@@ -176,6 +197,8 @@ if __name__ == "__main__":
         c5(2000, 100)
     if "n1" in what:
         n1()
+    if "n3" in what:
+        n3()
     if "n2" in what:
         n2()
     if "peaks" in what:
