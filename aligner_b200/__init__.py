@@ -15,11 +15,12 @@ from .matrices import dna_matrix, get_blosum62
 from .pwm import (HeuristicPWMAligner, PWMAligner, PWMAlignment, ResidentSequence,
                   get_random_pwm)
 from .statistics import shuffle_scores, shuffled_targets
-from .sharding import align_batch_sharded, matrix_search_sharded, shard_range
+from .sharding import (align_batch_sharded, matrix_search_sharded, pwm_scan_sharded, score_batch_sharded,
+                       shard_range)
 
 __all__ = [
     "AlignerError", "Alignment", "AlignmentResult", "BatchResult", "DNA", "DeviceBatch", "Direction",
     "Error", "GLOBAL", "HeuristicAligner", "Heuristics", "heuristic_batch", "matrix_search", "transform_matrix", "LOCAL", "NUM_AUTO", "NUM_F64", "NUM_I16X2", "NUM_I32",
     "PackedPairs", "Protein", "SimpleGlobalAligner", "SimpleLocalAligner", "align_batch",
-    "dna_matrix", "get_blosum62", "ScoreResult", "score_batch", "PWMAligner", "PWMAlignment", "HeuristicPWMAligner", "ResidentSequence", "get_random_pwm", "shuffled_targets", "shuffle_scores", "align_batch_sharded", "matrix_search_sharded", "shard_range",
+    "dna_matrix", "get_blosum62", "ScoreResult", "score_batch", "PWMAligner", "PWMAlignment", "HeuristicPWMAligner", "ResidentSequence", "get_random_pwm", "shuffled_targets", "shuffle_scores", "align_batch_sharded", "matrix_search_sharded", "shard_range", "pwm_scan_sharded", "score_batch_sharded",
 ]

@@ -142,3 +142,56 @@ def align_batch_sharded(mode, pairs, matrix, del_, ext, device=-1, gather=True):
     out = [None] * world if rank == 0 else None
     d.gather_object(mine, out, dst=0)
     return out if rank == 0 else [mine]
+
+
+def score_batch_sharded(mode, pairs, matrix, del_, ext, device=-1, gather=True):
+    """N2 on N ranks: every rank scores its contiguous range of pairs (balanced by sum of n*m); the
+    8-byte scores are all-gathered so that every rank can run the Gumbel fit.  Returns (f[count],
+    status[count]) on every rank when ``gather`` (else the rank's own slice and (lo, hi))."""
+    from .batch import score_batch
+    rank, world = _rank_world()
+    cells = np.diff(pairs.q_off).astype(np.float64) * np.diff(pairs.t_off).astype(np.float64)
+    lo, hi = shard_range(pairs.count, rank, world, cells)
+    res = score_batch(mode, slice_pairs(pairs, lo, hi), matrix, del_, ext, device=device)
+    d = _dist()
+    if not gather or d is None or world == 1:
+        return (res.f, res.status) if gather else (res.f, res.status, (lo, hi))
+    parts = [None] * world
+    d.all_gather_object(parts, (lo, hi, res.f, res.status))
+    f = np.zeros(pairs.count)
+    st = np.zeros(pairs.count, dtype=np.int32)
+    for plo, phi, pf, pst in parts:
+        f[plo:phi] = pf
+        st[plo:phi] = pst
+    return f, st
+
+
+def window_range(count, rank, world):
+    """Windows [lo, hi) of rank ``rank``: equal counts (the windows of a scan have equal sizes)."""
+    return count * rank // world, count * (rank + 1) // world
+
+
+def pwm_scan_sharded(seq, pwm, del_, ext, first=0, step=1, window=0, device=-1, resident=None):
+    """N1 on N ranks: every rank keeps the whole sequence resident in its own HBM (1 byte per base)
+    and scans a contiguous range of the strided windows score-only; the f values are all-gathered (8
+    bytes per window — no collective on the data path).  Returns f[count] on every rank."""
+    from .pwm import ResidentSequence
+    rank, world = _rank_world()
+    n = len(seq) if resident is None else resident.len
+    count = 0 if first >= n else (n - first + step - 1) // step
+    lo, hi = window_range(count, rank, world)
+    rs = resident if resident is not None else ResidentSequence(seq, device)
+    try:
+        mine = rs.align_windows(pwm, del_, ext, first=first + lo * step, step=step, window=window, count=hi - lo).f
+    finally:
+        if resident is None:
+            rs.close()
+    d = _dist()
+    if d is None or world == 1:
+        return mine
+    parts = [None] * world
+    d.all_gather_object(parts, (lo, hi, mine))
+    f = np.zeros(count)
+    for plo, phi, pf in parts:
+        f[plo:phi] = pf
+    return f

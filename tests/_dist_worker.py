@@ -52,6 +52,18 @@ def main():
         got = S.align_batch_sharded(ab.LOCAL, pairs, ab.dna_matrix(5, -4), 10, 2, device=0)
         if rank == 0:
             result = [(lo, hi, r.f, r.coords, r.aln_len) for lo, hi, r in got]
+    elif mode == "windows":  # host logic only (CPU test): the ranges tile the windows
+        count = int(sys.argv[3])
+        result = S.window_range(count, rank, world)
+    elif mode == "pwm":
+        length = int(sys.argv[3])
+        seq, repeat, _ = W.dna_chromosome_with_repeats(length, 80, 12, seed=2)
+        pwm = W.pwm_from_repeat(repeat, 1.0, -1.0) + 0.25
+        result = S.pwm_scan_sharded(seq, pwm, 3.0, 1.0, first=5, step=20, window=100, device=0)
+    elif mode == "scores":
+        P = int(sys.argv[3])
+        pairs = W.protein_pairs(0, P, 40, 90)
+        result = S.score_batch_sharded(ab.LOCAL, pairs, ab.get_blosum62(), 11, 2, device=0)
     gathered = [None] * world if rank == 0 else None
     dist.gather_object(result, gathered, dst=0)
     if rank == 0:

@@ -122,3 +122,29 @@ def test_align_batch_sharded_two_ranks(tmp_path):
     for lo, hi, f, coords, aln_len in got:
         assert (f == ref.f[lo:hi]).all() and (coords == ref.coords[lo:hi]).all()
         assert (aln_len == ref.aln_len[lo:hi]).all()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_window_ranges_tile_the_scan_gloo(world, tmp_path):
+    got = _launch(world, "windows", tmp_path, 1001)
+    assert got[0][0] == 0 and got[-1][1] == 1001
+    assert all(a[1] == b[0] for a, b in zip(got, got[1:]))
+    assert max(b - a for a, b in got) - min(b - a for a, b in got) <= 1
+
+
+@pytest.mark.gpu
+def test_pwm_scan_and_score_batch_sharded_two_ranks(tmp_path):
+    from aligner_b200 import pwm as P
+    seq, repeat, _ = W.dna_chromosome_with_repeats(30000, 80, 12, seed=2)
+    pwm = W.pwm_from_repeat(repeat, 1.0, -1.0) + 0.25
+    rs = P.ResidentSequence(seq)
+    ref = rs.align_windows(pwm, 3.0, 1.0, first=5, step=20, window=100).f
+    rs.close()
+    single = S.pwm_scan_sharded(seq, pwm, 3.0, 1.0, first=5, step=20, window=100)
+    assert (single == ref).all()
+    for f in _launch(2, "pwm", tmp_path, 30000):  # every rank holds the whole scan
+        assert (f == ref).all()
+    pairs = W.protein_pairs(0, 500, 40, 90)
+    want = ab.score_batch(ab.LOCAL, pairs, ab.get_blosum62(), 11, 2)
+    for f, st in _launch(2, "scores", tmp_path, 500):
+        assert (f == want.f).all() and (st == want.status).all()
