@@ -3,6 +3,7 @@
 #include "batch.h"
 
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -143,11 +144,15 @@ int alnr_batch_impl::plan_chunks(const uint64_t *q_off, const uint64_t *t_off) {
     // number of virtual blocks and no SM idles at the end of a chunk
     if (numeric == ALNR_NUM_I16X2 && c < count - s && c >= kStripWavePairs) c = c / kStripWavePairs * kStripWavePairs;
     if (ramp && numeric == ALNR_NUM_I16X2 && count > 4 * kStripWavePairs) {
-      // streaming call: a one-wave first chunk starts the compute after ~1 ms of copies, a
-      // one-wave last chunk leaves only ~2 ms of device->host copies behind the last kernel
-      const uint64_t rem = count - s;
-      if (s == 0) c = std::min<uint64_t>(c, kStripWavePairs);
-      else if (rem <= c && rem > kStripWavePairs + kStripWavePairs / 2) c = (rem - kStripWavePairs) / 64 * 64;
+      // streaming call: a one-wave first chunk starts the compute after ~1 ms of copies; the last
+      // chunks shrink 3, 2, 1 waves.  A chunk's results cross PCIe in ~1.1 ms per wave while the next
+      // chunk computes ~1.7 ms per wave, so a chunk at least 0.65x its predecessor leaves no copy
+      // backlog and only the last wave's ~1 ms of device->host copies follows the last kernel.
+      const uint64_t W = kStripWavePairs, rem = count - s;
+      if (s == 0) c = std::min<uint64_t>(c, W);
+      else if (rem > 7 * W) c = std::min<uint64_t>(c, (rem - 6 * W) / 64 * 64);
+      else if (rem > 3 * W + W / 2) c = std::min<uint64_t>(c, (rem - 3 * W) / 64 * 64);
+      else if (rem > W + W / 2) c = std::min<uint64_t>(c, (rem - W) / 64 * 64);
     }
     uint32_t m1, n1;
     dims(s, m1, n1);
@@ -199,6 +204,18 @@ bool alnr_batch_impl::chunk_compact(const Chunk &c) const {
 
 int alnr_batch_impl::init(const alnr_params *p, const alnr_batch *b, bool want_mats) {
   if (!p || !b || !p->matrix) return ALNR_INVALID_ARGUMENT;
+  // ALNR_TIMING: host milliseconds of the stages of init()
+  static const bool timing = getenv("ALNR_TIMING") != nullptr;
+  auto t_prev = std::chrono::steady_clock::now();
+  std::string t_log;
+  auto lap = [&](const char *what) {
+    if (!timing) return;
+    const auto now = std::chrono::steady_clock::now();
+    char buf[64];
+    std::snprintf(buf, sizeof(buf), " %s %.2f", what, std::chrono::duration<double, std::milli>(now - t_prev).count());
+    t_log += buf;
+    t_prev = now;
+  };
   if (p->mode != ALNR_GLOBAL && p->mode != ALNR_LOCAL) return ALNR_INVALID_ARGUMENT;
   if (p->volume < 1 || p->volume > 32) return ALNR_MATRIX_SHAPE_ERROR;
   if (b->count >= (1ull << 31)) return ALNR_INVALID_ARGUMENT;
@@ -258,6 +275,7 @@ int alnr_batch_impl::init(const alnr_params *p, const alnr_batch *b, bool want_m
       m_max = std::max(m_max, pt.m_max);
     }
   }
+  lap("streams+sweep");
   int st = classify();
   if (st) return st;
 
@@ -289,8 +307,10 @@ int alnr_batch_impl::init(const alnr_params *p, const alnr_batch *b, bool want_m
   ALNR_CUDA(cudaMemcpyAsync(d_mati.p, mi.data(), mi.size() * 4, cudaMemcpyHostToDevice, stream));
   ALNR_CUDA(cudaStreamSynchronize(stream));
 
+  lap("inputs");
   st = plan_chunks(b->q_off, b->t_off);
   if (st) return st;
+  lap("plan");
 
   ALNR_CUDA(d_f.alloc(count));
   ALNR_CUDA(d_corner.alloc(count));
@@ -337,6 +357,8 @@ int alnr_batch_impl::init(const alnr_params *p, const alnr_batch *b, bool want_m
     ALNR_CUDA(d_Hout.alloc(((size_t)m_max + 1) * ((size_t)n_max + 1)));
     ALNR_CUDA(d_Dout.alloc(((size_t)m_max + 1) * ((size_t)n_max + 1)));
   }
+  lap("buffers");
+  if (timing) std::fprintf(stderr, "[alnr] init:%s ms\n", t_log.c_str());
   if (numeric == ALNR_NUM_I16X2) {
     st = strip_prepare(*this);
     if (st) return st;
@@ -551,7 +573,10 @@ int alnr_batch_impl::stream_all(const alnr_batch *b, alnr_batch_out *out) {
     const size_t f0 = c.first, fc = c.count;
     const size_t a0 = c.q0 + c.t0 + f0;  // first byte of the chunk's alignment region
     size_t abytes = (c.q1 + c.t1 + f0 + fc) - a0;
-    if (chunk_compact(c)) {
+    // s_out waits for THIS chunk only (a wait for the next chunk queued ahead of these copies
+    // would hold them back by a whole chunk period)
+    e = cudaStreamWaitEvent(s_out, ev_done[ci], 0);
+    if (e == cudaSuccess && chunk_compact(c)) {
       e = cudaEventSynchronize(ev_done[ci]);  // h_tot[ci] was copied before ev_done was recorded
       if (e == cudaSuccess) abytes = (size_t)h_tot[ci];
     }
@@ -570,17 +595,24 @@ int alnr_batch_impl::stream_all(const alnr_batch *b, alnr_batch_out *out) {
     if (e != cudaSuccess) fail(e, "D2H chunk");
     mark(s_out);
   };
-  // every chunk has its own region of d_q / d_t, so all host->device copies are queued up front
-  // (they run back to back on the copy engine) and each chunk's compute waits for its own event
-  for (size_t ci = 0; ci < chunks.size() && !st; ++ci) {
+  // Host->device copies run kAhead chunks ahead of the compute.  Queuing all of them up front keeps
+  // the link busy in the upward direction for the first half of the call, and the device->host
+  // copies of the first chunks then run at half speed (measured: 22-33 GB/s next to a saturating
+  // upload, 51 GB/s alone) and pile up a backlog that is still draining after the last kernel.
+  const size_t kAhead = 3;
+  auto upload = [&](size_t ci) {
+    if (ci >= chunks.size() || st) return;
     const Chunk &c = chunks[ci];
     cudaError_t e = cudaMemcpyAsync(d_q.p + c.q0, b->q + c.q0, c.q1 - c.q0, cudaMemcpyHostToDevice, s_in);
     if (e == cudaSuccess) e = cudaMemcpyAsync(d_t.p + c.t0, b->t + c.t0, c.t1 - c.t0, cudaMemcpyHostToDevice, s_in);
     if (e == cudaSuccess) e = cudaEventRecord(ev_in[ci], s_in);
     if (e != cudaSuccess) fail(e, "H2D chunk");
-  }
+  };
+  for (size_t ci = 0; ci < kAhead; ++ci) upload(ci);
   for (size_t ci = 0; ci < chunks.size() && !st; ++ci) {
     const Chunk &c = chunks[ci];
+    upload(ci + kAhead);
+    if (st) break;
     cudaError_t e = cudaStreamWaitEvent(stream, ev_in[ci], 0);
     if (e != cudaSuccess) { fail(e, "H2D wait"); break; }
     mark(stream);
@@ -591,7 +623,6 @@ int alnr_batch_impl::stream_all(const alnr_batch *b, alnr_batch_out *out) {
     if (chunk_compact(c))
       e = cudaMemcpyAsync(h_tot + ci, d_ctotal.p + ci, sizeof(uint64_t), cudaMemcpyDeviceToHost, s2);
     if (e == cudaSuccess) e = cudaEventRecord(ev_done[ci], s2);
-    if (e == cudaSuccess) e = cudaStreamWaitEvent(s_out, ev_done[ci], 0);
     if (e != cudaSuccess) { fail(e, "chunk events"); break; }
     if (ci > 0) drain(ci - 1);
   }
