@@ -38,6 +38,17 @@ __device__ __forceinline__ double shfl_up_t(double v) { return __shfl_up_sync(0x
 // DSETP + selects + NaN fix-up.  (Only the sign of a zero result can differ; `== 0.0` and the
 // EPSILON tests do not see it.)
 __device__ __forceinline__ int wmax3(int a, int b, int c) { return max(max(a, b), c); }
+// score lookups by 32-bit shared address: row base per DP row, one add per cell
+__device__ __forceinline__ int lds_score(uint32_t addr, int) {
+  int v;
+  asm volatile("ld.shared.s32 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ double lds_score(uint32_t addr, double) {
+  double v;
+  asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(addr));
+  return v;
+}
 __device__ __forceinline__ double wmax3(double a, double b, double c) {
   const double g = a > b ? a : b;
   return g > c ? g : c;
@@ -86,6 +97,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) fill_warp_kernel(WarpArgs
     smat = smem;
   }
   if (!have) return;
+  const uint32_t smat_addr = (uint32_t)__cvta_generic_to_shared(smat);
 
   const uint32_t sp = a.cv.seq(pair);
   const uint8_t *q, *t;
@@ -142,7 +154,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) fill_warp_kernel(WarpArgs
       for (int r = 0; r < R; ++r) {
         const uint32_t y = yb + r + 1;
         const bool valid = y <= m;
-        toff[r] = valid ? (uint32_t)t[y - 1] * V : 0u;
+        toff[r] = smat_addr + (valid ? (uint32_t)t[y - 1] * V : 0u) * (uint32_t)sizeof(T);  // row of the matrix
         T v = T(0);
         if (!LOCAL && valid) v = (y == m) ? -(T(m) + T(1)) * del : -T(y) * del;  // :64-67, :70
         h[r] = v;
@@ -159,13 +171,13 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) fill_warp_kernel(WarpArgs
       for (uint32_t s = 0; s < steps; ++s, dp += 32) {
         T up = shfl_up_t(bottom);
         const uint32_t c = s - lane;  // 0-based column; wraps for s < lane
-        if (c < n) {
+        if (c < n && yb < m) {  // lanes whose rows all lie below row m idle (last band)
           const uint32_t x = c + 1;
           if (lane == 0) {
             if (band == 0) { up = T(0); if (!LOCAL) up = (x == n) ? -(T(n) + T(1)) * del : -T(x) * del; }  // :59-62, :69
             else up = rowbuf[x];
           }
-          const uint32_t qs = qn;  // PWM view: the column index itself (pwm/mod.rs:62)
+          const uint32_t qoff = qn * (uint32_t)sizeof(T);  // PWM view: the column index itself (pwm/mod.rs:62)
           if (x < n) qn = pwm ? x : q[x];
           T diag = dprev;
           dprev = up;
@@ -185,9 +197,10 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) fill_warp_kernel(WarpArgs
             pen = Num<T>::is_zero(up) ? del : ext;        // cell above is Beginning iff it is 0
           }
           uint32_t bits = 0;
+          bool hit = false;  // some cell of this step reaches the running maximum (rare)
 #pragma unroll
           for (int r = 0; r < R; ++r) {
-            const T sc = smat[toff[r] + qs];
+            const T sc = lds_score(toff[r] + qoff, T(0));
             const T top = nsub(hup, pen), lft = nsub(h[r], pen), dg = nadd(diag, sc);
             const T mx = wmax3(top, lft, dg);
             uint32_t d = Num<T>::same(mx, lft) ? DIR_LEFT : DIR_DIAGONAL;  // enums.rs:23/:41
@@ -202,15 +215,20 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) fill_warp_kernel(WarpArgs
             diag = h[r];
             h[r] = mx;
             hup = mx;
-            if (LOCAL) {
-              if (mx >= best) {  // rare: first maximum in row-major order (simple/mod.rs:212)
-                const uint32_t y = yb + r + 1;
-                if (y <= m && (mx > best || (mx == best && y < by))) { best = mx; by = y; bx = x; }
-              }
-            }
+            if (LOCAL) hit |= mx >= best;
             if (MATS) {
               const uint32_t y = yb + r + 1;
               if (y <= m) { a.H_out[y * W + x] = (double)mx; a.D_out[y * W + x] = (uint8_t)d; }
+            }
+          }
+          if (LOCAL && hit) {
+            // first maximum in row-major order (simple/mod.rs:212): the rows of this step in
+            // ascending order, exactly the updates a per-cell test would make
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+              const uint32_t y = yb + r + 1;
+              const T v = h[r];
+              if (y <= m && (v > best || (v == best && y < by))) { best = v; by = y; bx = x; }
             }
           }
           bottom = hup;
