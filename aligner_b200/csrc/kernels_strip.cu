@@ -144,6 +144,15 @@ StripPlan strip_plan(alnr_batch_impl &B, const Chunk &c, const ChunkView &cv, co
     a.wtab[qs] = w;
   }
   a.del = (int)B.del; a.ext = (int)B.ext;
+  {
+    double top = 0.0;
+    for (double v : B.matrix) top = std::max(top, v);
+    a.safe_mask = 0;
+    static const bool off = getenv("ALNR_NO_SAFE_MASK") != nullptr;
+    for (int ts = 0; ts < B.V && !off; ++ts)
+      for (int qs = 0; qs < B.V; ++qs)
+        if (B.matrix[(size_t)ts * B.V + qs] > top - B.ext) a.safe_mask |= 1u << (ts * 4 + qs);
+  }
   a.D = B.Dp(); a.dl = dl; a.fo = fo;
   a.list = nullptr; a.list_count = nullptr; a.z_in = nullptr; a.z_out = P.zbuf[0]; a.nzw = nzw;
   a.fail_list = P.lists[0]; a.fail_count = P.counters + 0;

@@ -44,6 +44,10 @@ struct StripArgs {
   uint32_t nzw;
   uint32_t *fail_list;
   uint32_t *fail_count;
+  // bit (tsym * 4 + qsym): score(tsym, qsym) > max(0, largest score) - ext.  With such a score cell
+  // (1, x+1) is Diagonal with the same value under either penalty (row 0 is zero, H[1][x] cannot
+  // exceed the largest score), so a wrongly assumed z bit in front of it changes nothing.
+  uint32_t safe_mask;
   uint32_t *hglobal;           // strip boundary rows in global memory (nullptr: shared memory)
   uint32_t vblocks;            // virtual blocks of kStripBlock duos (the grid may be smaller)
 };
@@ -243,8 +247,17 @@ __device__ __forceinline__ void strip_sweep(const StripArgs &a, StripCtx &c, con
         // bits at column index >= n-1 never feed a penalty (there is no column n+1)
         const uint32_t nb = (n - 1) - (w << 5);
         const uint32_t valid = (n - 1 <= (w << 5)) ? 0u : (nb >= 32 ? 0xffffffffu : ((1u << nb) - 1u));
-        if ((zacc ^ asA) & valid) c.mismatch |= 1u;
-        if ((zaccB ^ asB) & valid) c.mismatch |= 0x10000u;
+        // a wrong bit only counts if the cell it feeds, (1, x+1), can tell the penalties apart
+        auto matters = [&](uint32_t diff, const uint32_t *qp, const uint32_t *tp) {
+          const uint32_t t0 = sym2(tp, 0);
+          for (; diff; diff &= diff - 1) {
+            const uint32_t col = (w << 5) + (uint32_t)__ffs(diff);  // 0-based query index of column x+1
+            if (!((a.safe_mask >> (t0 * 4 + sym2(qp, col))) & 1u)) return true;
+          }
+          return false;
+        };
+        if (matters((zacc ^ asA) & valid, c.qA, c.tA)) c.mismatch |= 1u;
+        if (matters((zaccB ^ asB) & valid, c.qB, c.tB)) c.mismatch |= 0x10000u;
         a.z_out[(size_t)c.sA * a.nzw + w] = zacc;
         if (!c.dupB) a.z_out[(size_t)c.sB * a.nzw + w] = zaccB;
         zacc = zaccB = 0;
