@@ -61,6 +61,8 @@ struct alnr_batch_impl {
   DevBuf<int> d_mati, d_hcol_i;
   DevBuf<int> d_band;           // band pipeline kernel: reduction cells, progress words, band rows
   DevBuf<uint32_t> d_pack;      // packed sequences for the strip kernel
+  DevBuf<uint32_t> d_brow;      // strip kernel: kept bottom rows of strip 0 (incremental re-run), per parity
+  uint64_t brow_words = 0;
   DevBuf<uint32_t> d_wz;        // warp kernel: [8 counters][fail list][z bits 2*nzw per slot]
   uint64_t rerun_total = 0;
   bool profile = false;                 // record events around every fill launch

@@ -36,6 +36,12 @@ uint32_t d_rows_per_word(const alnr_batch_impl &B, uint32_t m) {
   return B.numeric == ALNR_NUM_I16X2 ? pick_rows(m) : 16;
 }
 
+// Incremental re-run (rerun_strip0_kernel): local mode with del != ext and at least two strips.
+static bool strip_incremental(const alnr_batch_impl &B) {
+  static const bool off = getenv("ALNR_NO_INCREMENTAL") != nullptr;
+  return !off && B.mode == ALNR_LOCAL && B.del != B.ext && B.m_max > pick_rows(B.m_max);
+}
+
 int strip_prepare(alnr_batch_impl &B) {
   const uint32_t nwq = (B.n_max + 15) / 16, nwt = (B.m_max + 15) / 16;
   const uint64_t groups = (B.count + 31) / 32;
@@ -48,6 +54,10 @@ int strip_prepare(alnr_batch_impl &B) {
   // [list0 cmax][list1 cmax][z0 cmax*nzw][z1 cmax*nzw]
   B.rerun_words = 2ull * cmax + 2ull * cmax * nzw;
   ALNR_CUDA(B.d_rerun.alloc(8 * B.chunks.size() + (B.chunks.size() > 1 ? 2 : 1) * B.rerun_words));
+  if (strip_incremental(B)) {
+    B.brow_words = ((uint64_t)(cmax + 63) / 64 + 1) * 32 * B.n_max;  // one word per duo and column
+    ALNR_CUDA(B.d_brow.alloc((B.chunks.size() > 1 ? 2 : 1) * B.brow_words));
+  }
   return ALNR_OK;
 }
 
@@ -158,6 +168,7 @@ StripPlan strip_plan(alnr_batch_impl &B, const Chunk &c, const ChunkView &cv, co
   a.fail_list = P.lists[0]; a.fail_count = P.counters + 0;
   static const bool hrow_global = getenv("ALNR_STRIP_HROW_SMEM") == nullptr;
   a.hglobal = hrow_global ? (uint32_t *)B.hcol_i() : nullptr;
+  a.brow0 = (B.d_brow.p && a.hglobal) ? B.d_brow.p + (size_t)B.par * B.brow_words : nullptr;
   P.R = dl.rows_per_word;
   return P;
 }
@@ -189,13 +200,42 @@ int strip_rerun_passes(alnr_batch_impl &B, const Chunk &c, const ChunkView &cv, 
                        const FillOut &fo) {
   StripPlan P = strip_plan(B, c, cv, dl, fo);
   cudaStream_t stream = B.s2;
+  // Incremental pass first (rerun_strip0_kernel): strip 0 only, with the observed bits; what it
+  // cannot settle goes on list 1.  The full passes then read list `off + pass`.
+  const int off = (P.a.brow0 && c.m_max > P.R) ? 1 : 0;
+  if (off) {
+    StripArgs r = P.a;
+    r.list = P.lists[0]; r.list_count = P.counters + 0;
+    r.z_in = P.zbuf[0]; r.z_out = nullptr;
+    r.fail_list = P.lists[1]; r.fail_count = P.counters + 1;
+    static unsigned resident = 0;
+    if (!resident) {
+      int occ = 0, sms = 0, dev = 0;
+      ALNR_CUDA(cudaGetDevice(&dev));
+      ALNR_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+      ALNR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, rerun_strip0_kernel<15, false>, kStripBlock, 0));
+      resident = (unsigned)std::max(1, occ) * (unsigned)std::max(1, sms);
+    }
+    // the list length is only known on the device: one resident wave of persistent blocks (the
+    // physical-thread row buffer is sized for that), blocks past the list exit at once
+    const unsigned blocks = std::min<unsigned>(resident, ((c.count + 1) / 2 + kStripBlock - 1) / kStripBlock);
+    if (P.R == 15) {
+      if (B.score_only) rerun_strip0_kernel<15, true><<<blocks, kStripBlock, 0, stream>>>(r);
+      else rerun_strip0_kernel<15, false><<<blocks, kStripBlock, 0, stream>>>(r);
+    } else {
+      if (B.score_only) rerun_strip0_kernel<16, true><<<blocks, kStripBlock, 0, stream>>>(r);
+      else rerun_strip0_kernel<16, false><<<blocks, kStripBlock, 0, stream>>>(r);
+    }
+    ALNR_LAUNCHED();
+  }
   // re-run passes over the (device-side) fail list; grids are sized for the worst case and
   // exit at once past the list length, so no host synchronisation is needed.
   for (int pass = 0; pass < kRedoPasses; ++pass) {
     StripArgs r = P.a;
-    r.list = P.lists[pass & 1]; r.list_count = P.counters + pass;
+    const int li = pass + off;
+    r.list = P.lists[li & 1]; r.list_count = P.counters + li;
     r.z_in = P.zbuf[pass & 1]; r.z_out = P.zbuf[(pass + 1) & 1];
-    r.fail_list = P.lists[(pass + 1) & 1]; r.fail_count = P.counters + pass + 1;
+    r.fail_list = P.lists[(li + 1) & 1]; r.fail_count = P.counters + li + 1;
     // the fail fraction shrinks quickly: size each grid for a generous bound, the kernel exits
     // past the list length (a list longer than the grid would be wrong, so bound by the chunk)
     const uint32_t duos = (c.count + 1) / 2;
@@ -208,7 +248,7 @@ int strip_rerun_passes(alnr_batch_impl &B, const Chunk &c, const ChunkView &cv, 
   e.cv = cv; e.mode = B.mode; e.V = B.V; e.del = (int)B.del; e.ext = (int)B.ext;
   e.matrix = B.d_mati.p; e.hcol = B.hcol_i(); e.hrows = c.m_max + 1; e.D = B.Dp(); e.dl = dl; e.fo = fo;
   e.H_out = nullptr; e.D_out = nullptr;
-  e.list = P.lists[kRedoPasses & 1]; e.list_count = P.counters + kRedoPasses;
+  e.list = P.lists[(kRedoPasses + off) & 1]; e.list_count = P.counters + kRedoPasses + off;
   fill_exact_kernel<int><<<(c.count + 127) / 128, 128, (size_t)B.V * B.V * sizeof(int), stream>>>(e);
   ALNR_LAUNCHED();
   return ALNR_OK;

@@ -48,6 +48,9 @@ struct StripArgs {
   // (1, x+1) is Diagonal with the same value under either penalty (row 0 is zero, H[1][x] cannot
   // exceed the largest score), so a wrongly assumed z bit in front of it changes nothing.
   uint32_t safe_mask;
+  // bottom row of strip 0 of every duo of the chunk, kept for the incremental re-run
+  // (rerun_strip0_kernel): [((vduo >> 5) * n + x-1) * 32 + (vduo & 31)], pair A in the low half
+  uint32_t *brow0;
   uint32_t *hglobal;           // strip boundary rows in global memory (nullptr: shared memory)
   uint32_t vblocks;            // virtual blocks of kStripBlock duos (the grid may be smaller)
 };
@@ -334,8 +337,14 @@ __global__ void __launch_bounds__(kStripBlock) fill_strip_kernel(StripArgs a) {
     c.hrow[(size_t)(x - 1) * c.hstride] = pack2(hv, hv);
   }
 
-  for (uint32_t strip = 0; strip + 1 < nstrips; ++strip)
+  for (uint32_t strip = 0; strip + 1 < nstrips; ++strip) {
     strip_sweep<R, LOCAL, STATEFUL, false, SCORE>(a, c, swt, strip);
+    if (STATEFUL && strip == 0 && a.brow0 && !a.list) {
+      // speculative pass: keep the bottom row of strip 0 (the next strip overwrites hrow)
+      uint32_t *bp = a.brow0 + ((size_t)(duo >> 5) * n) * 32 + (duo & 31);
+      for (uint32_t x = 0; x < n; ++x) __stcs(bp + (size_t)x * 32, c.hrow[(size_t)x * c.hstride]);
+    }
+  }
   strip_sweep<R, LOCAL, STATEFUL, true, SCORE>(a, c, swt, nstrips - 1);
 
   // ---- per-pair results ---------------------------------------------------------------
@@ -358,6 +367,85 @@ __global__ void __launch_bounds__(kStripBlock) fill_strip_kernel(StripArgs a) {
   finish(bA, c.sA, c.bestA, lane_lo(c.corner), (c.mismatch & 1u) != 0);
   if (!c.dupB) finish(bB, c.sB, c.bestB, lane_hi(c.corner), (c.mismatch >> 16) != 0);
   }  // virtual blocks
+}
+
+// Incremental re-run (local mode, del != ext, more than one strip).  A wrongly assumed z bit changes
+// the penalty of ONE cell, (1, x+1); the disturbance dies out within a few rows (measured on the C3
+// reads: at most 9 rows deep in 99 % of the failing pairs, never below strip 0).  So the pairs on the
+// fail list first get only strip 0 recomputed with the observed bits: if its bottom row equals the
+// one the speculative pass kept (brow0), every lower strip, row m and with it the observed bits are
+// unchanged — the pair is settled after 1/nstrips of a full re-run.  The arg-max is re-derived from
+// the new best of strip 0 (P) and the pair's previous arg-max (G): G outside strip 0 is still the first
+// maximum of the unchanged strips, so the answer is P if P.v >= G.v (strip 0 wins ties by smaller y),
+// else G; G inside strip 0 stands only if P.v >= G.v.  Pairs whose bottom row changed, or whose
+// arg-max cannot be decided this way, go on to the full re-run passes.
+template <int R, bool SCORE>
+__global__ void __launch_bounds__(kStripBlock) rerun_strip0_kernel(StripArgs a) {
+  __shared__ uint32_t swt[4];
+  const uint32_t tid = threadIdx.x;
+  if (tid < 4) swt[tid] = a.wtab[tid];
+  __syncthreads();
+  const uint32_t cnt = *a.list_count;
+  for (uint32_t vb = blockIdx.x; vb * kStripBlock * 2 < cnt; vb += gridDim.x) {
+    const uint32_t duo = vb * kStripBlock + tid;
+    const uint32_t pduo = blockIdx.x * kStripBlock + tid;
+    if (2 * duo >= cnt) break;
+    StripCtx c;
+    c.dupB = false;
+    c.sA = a.list[2 * duo];
+    if (2 * duo + 1 < cnt) c.sB = a.list[2 * duo + 1]; else { c.sB = c.sA; c.dupB = true; }
+    const uint32_t bA = a.first + c.sA, bB = a.first + c.sB;
+    c.qA = a.qpk + ((size_t)(bA >> 5) * a.nwq) * 32 + (bA & 31);
+    c.qB = a.qpk + ((size_t)(bB >> 5) * a.nwq) * 32 + (bB & 31);
+    c.tA = a.tpk + ((size_t)(bA >> 5) * a.nwt) * 32 + (bA & 31);
+    c.tB = a.tpk + ((size_t)(bB >> 5) * a.nwt) * 32 + (bB & 31);
+    const uint32_t n = a.n;
+    c.dA = SCORE ? nullptr : a.D + a.dl.word(c.sA, 0, 0);
+    c.dB = SCORE ? nullptr : a.D + a.dl.word(c.sB, 0, 0);
+    c.hrow = a.hglobal + ((size_t)(pduo >> 5) * n) * 32 + (pduo & 31);
+    c.hstride = 32;
+    c.bestA = Best{0, 0, 0, -1};
+    c.bestB = Best{0, 0, 0, -1};
+    c.mismatch = 0;
+    c.corner = 0;
+    for (uint32_t x = 0; x < n; ++x) c.hrow[(size_t)x * 32] = 0u;  // row 0 (local)
+    strip_sweep<R, true, true, false, SCORE>(a, c, swt, 0);
+
+    // the kept bottom row of a slot: its duo in the speculative pass, low or high half
+    auto kept = [&](uint32_t slot) {
+      const uint32_t vduo = (slot >> 6) * 32 + (slot & 31), half = (slot >> 5) & 1u;
+      return reinterpret_cast<const uint16_t *>(a.brow0 + ((size_t)(vduo >> 5) * n) * 32 + (vduo & 31)) + half;
+    };
+    const uint16_t *kA = kept(c.sA), *kB = kept(c.sB);
+    bool chA = false, chB = false;
+    for (uint32_t x = 0; x < n; ++x) {
+      const uint32_t v = c.hrow[(size_t)x * 32];
+      chA |= (uint16_t)(v & 0xffffu) != kA[(size_t)x * 64];
+      chB |= (uint16_t)(v >> 16) != kB[(size_t)x * 64];
+    }
+    auto settle = [&](uint32_t bslot, uint32_t slot, const Best &p, bool changed) {
+      const uint32_t pair = a.order ? a.order[bslot] : bslot;
+      const int32_t st = a.fo.status[pair];
+      if (st != 0 && st != 11) return;  // rejected by validation
+      bool decided = !changed;
+      if (decided) {
+        const int gv = (int)a.fo.f[pair];
+        const uint32_t gy = a.fo.start[2 * (size_t)pair];
+        const bool p_ok = p.y != 0;
+        if (gy == 0 || (p_ok && p.v >= gv)) {  // no positive cell before, or strip 0 wins
+          a.fo.f[pair] = (double)p.v;
+          a.fo.start[2 * (size_t)pair] = p.y;
+          a.fo.start[2 * (size_t)pair + 1] = p.x;
+          a.fo.status[pair] = p_ok ? 0 : 11;  // ALNR_NO_POSITIVE_CELL
+        } else if (gy <= (uint32_t)R) {
+          decided = false;  // the old arg-max sat in strip 0 and the new strip 0 stays below it
+        }
+      }
+      if (!decided) a.fail_list[atomicAdd(a.fail_count, 1u)] = slot;
+    };
+    settle(bA, c.sA, c.bestA, chA);
+    if (!c.dupB) settle(bB, c.sB, c.bestB, chB);
+  }
 }
 
 // 2-bit packing of the slots [first, first+count) of one sequence set into the coalesced
