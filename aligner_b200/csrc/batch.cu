@@ -699,6 +699,10 @@ int alnr_batch_impl::download(alnr_batch_out *out) {
     int st = strip_fail_counts(*this, fc);
     if (st) return st;
     rerun_total = fc[0];
+    static const bool timing = getenv("ALNR_TIMING") != nullptr;
+    if (timing)  // pairs on the list after the speculative pass, the incremental pass, full passes 1 and 2
+      std::fprintf(stderr, "[alnr] speculation lists: %llu %llu %llu %llu of %llu pairs\n", (unsigned long long)fc[0],
+                   (unsigned long long)fc[1], (unsigned long long)fc[2], (unsigned long long)fc[3], (unsigned long long)count);
   }
   return ALNR_OK;
 }
