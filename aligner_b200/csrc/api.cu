@@ -148,6 +148,7 @@ int alnr_align_batch(const alnr_params *p, const alnr_batch *b, alnr_batch_out *
   B.resident = false;
   B.ramp = true;
   B.max_chunk = 620000;  // ~4 waves of the strip kernel: short pipeline fill / drain
+  if (const char *mc = std::getenv("ALNR_STREAM_CHUNK")) B.max_chunk = (uint32_t)std::max(1L, std::atol(mc));
   static const bool timing = std::getenv("ALNR_TIMING") != nullptr;
   const auto t0 = std::chrono::steady_clock::now();
   int st = B.init(p, b, false);

@@ -88,8 +88,19 @@ static __global__ void uniform_offsets_kernel(uint64_t *qo, uint64_t *to, uint64
 }
 
 static uint64_t scratch_budget_bytes() {
+  // cudaMemGetInfo was seen to take 0.1 - 60 ms per call: ask at most every few seconds per device
+  struct Cached { uint64_t free_b = 0; std::chrono::steady_clock::time_point at; bool valid = false; };
+  static thread_local Cached cache[16];
+  int dev = 0;
+  (void)cudaGetDevice(&dev);
+  Cached &cd = cache[dev & 15];
+  const auto now = std::chrono::steady_clock::now();
   size_t free_b = 0, total_b = 0;
-  if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) return 1ull << 30;
+  if (cd.valid && now - cd.at < std::chrono::seconds(5)) free_b = cd.free_b;
+  else {
+    if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) return 1ull << 30;
+    cd.free_b = free_b; cd.at = now; cd.valid = true;
+  }
   uint64_t b = free_b / 3;
   const uint64_t cap = 24ull << 30;
   return std::max<uint64_t>(std::min<uint64_t>(b, cap), 64ull << 20);
@@ -599,7 +610,7 @@ int alnr_batch_impl::stream_all(const alnr_batch *b, alnr_batch_out *out) {
   // the link busy in the upward direction for the first half of the call, and the device->host
   // copies of the first chunks then run at half speed (measured: 22-33 GB/s next to a saturating
   // upload, 51 GB/s alone) and pile up a backlog that is still draining after the last kernel.
-  const size_t kAhead = 3;
+  const size_t kAhead = 3, kDrainLag = 2;
   auto upload = [&](size_t ci) {
     if (ci >= chunks.size() || st) return;
     const Chunk &c = chunks[ci];
@@ -624,25 +635,28 @@ int alnr_batch_impl::stream_all(const alnr_batch *b, alnr_batch_out *out) {
       e = cudaMemcpyAsync(h_tot + ci, d_ctotal.p + ci, sizeof(uint64_t), cudaMemcpyDeviceToHost, s2);
     if (e == cudaSuccess) e = cudaEventRecord(ev_done[ci], s2);
     if (e != cudaSuccess) { fail(e, "chunk events"); break; }
-    if (ci > 0) drain(ci - 1);
+    // drain() blocks the host until its chunk is complete: draining chunk ci-2 here keeps the
+    // kernels of chunk ci queued behind chunk ci-1 on the device (draining ci-1 would enqueue every
+    // chunk only when the one before it has finished its second phase)
+    if (ci >= kDrainLag) drain(ci - kDrainLag);
   }
-  if (!st && !chunks.empty()) drain(chunks.size() - 1);
+  for (size_t ci = chunks.size() > kDrainLag ? chunks.size() - kDrainLag : 0; ci < chunks.size() && !st; ++ci) drain(ci);
   cudaError_t e1 = cudaStreamSynchronize(s_in), e2 = cudaStreamSynchronize(stream), e3 = cudaStreamSynchronize(s_out);
   if (e2 == cudaSuccess) e2 = cudaStreamSynchronize(stream2);
   if (!st && e1 != cudaSuccess) fail(e1, "sync s_in");
   if (!st && e2 != cudaSuccess) fail(e2, "sync compute");
   if (!st && e3 != cudaSuccess) fail(e3, "sync s_out");
   if (trace && !st && tev.size() == 1 + 3 * chunks.size()) {
-    // order of marks: [0] start, then per chunk ci: compute begin, compute end; the D2H end
-    // of chunk ci-1 is recorded inside iteration ci (after its compute-end mark), the last one at the end
+    // order of marks: [0] start, then per chunk ci: compute begin, compute end; the D2H end of
+    // chunk ci - kDrainLag is recorded inside iteration ci (after its compute-end mark), the last ones at the end
     auto ms = [&](size_t k) { float t = 0; cudaEventElapsedTime(&t, tev[0], tev[k]); return t; };
     std::vector<size_t> c0(chunks.size()), c1(chunks.size()), d2h(chunks.size());
     size_t k = 1;
     for (size_t ci = 0; ci < chunks.size(); ++ci) {
       c0[ci] = k++; c1[ci] = k++;
-      if (ci > 0) d2h[ci - 1] = k++;
+      if (ci >= kDrainLag) d2h[ci - kDrainLag] = k++;
     }
-    d2h[chunks.size() - 1] = k++;
+    for (size_t ci = chunks.size() > kDrainLag ? chunks.size() - kDrainLag : 0; ci < chunks.size(); ++ci) d2h[ci] = k++;
     for (size_t ci = 0; ci < chunks.size(); ++ci)
       std::fprintf(stderr, "[alnr] chunk %2zu: compute %7.2f -> %7.2f  d2h_end %7.2f ms\n", ci,
                    ms(c0[ci]), ms(c1[ci]), ms(d2h[ci]));
