@@ -376,7 +376,7 @@ int alnr_batch_impl::init(const alnr_params *p, const alnr_batch *b, bool want_m
   } else if (mode == ALNR_LOCAL && del != ext) {
     uint32_t cmax = 0;
     for (const Chunk &c : chunks) cmax = std::max(cmax, c.count);
-    ALNR_CUDA(d_wz.alloc(8 + (uint64_t)cmax * (1 + 2ull * ((n_max + 31) / 32))));
+    ALNR_CUDA(d_wz.alloc(warp_scratch_words(cmax, (n_max + 31) / 32, true)));
   }
   return ALNR_OK;
 }
@@ -406,8 +406,8 @@ static int launch_warp(alnr_batch_impl &B, const Chunk &c, const ChunkView &cv, 
   a.rowbuf = hcol; a.rowbuf_stride = c.n_max + 1;
   a.nzw = (B.n_max + 31) / 32;
   uint32_t *counters = B.d_wz.p;
-  a.fail_count = counters; a.fail_list = counters ? counters + 8 : nullptr;
-  a.zbuf = counters ? counters + 8 + c.count : nullptr;
+  static const bool no_inc = getenv("ALNR_NO_INCREMENTAL") != nullptr;
+  warp_scratch_bind(a, counters, c.count, !no_inc);
   a.H_out = B.d_Hout.p; a.D_out = B.d_Dout.p;
   const bool mats = B.want_matrices && B.count == 1;
   if (a.stateful) ALNR_CUDA(cudaMemsetAsync(counters, 0, 8 * sizeof(uint32_t), B.stream));

@@ -164,7 +164,7 @@ extern "C" int alnr_heuristic_batch(const alnr_params *p, const alnr_batch *b,
   ALNR_CUDA(d_maxf.alloc(chunk)); ALNR_CUDA(d_fcur.alloc(chunk)); ALNR_CUDA(d_fout.alloc(chunk));
   ALNR_CUDA(d_corner.alloc(chunk)); ALNR_CUDA(d_hcol.alloc((chunk + 31) / 32 * 32 * row_words));
   // fail list: items whose speculation never settles or whose matrix is not finite (exact kernel)
-  ALNR_CUDA(d_wz.alloc(8 + chunk * (1 + (stateful ? 2ull * nzw : 0))));
+  ALNR_CUDA(d_wz.alloc(warp_scratch_words(chunk, nzw, stateful)));
   ALNR_CUDA(d_cc.alloc(chunk * 4)); ALNR_CUDA(d_co.alloc(chunk * 4));
 
   auto h2d = [&](void *dst, const void *src, size_t bytes) {
@@ -214,8 +214,8 @@ extern "C" int alnr_heuristic_batch(const alnr_params *p, const alnr_batch *b,
       w.cv = cv; w.V = V; w.del = p->del; w.ext = p->ext; w.stateful = stateful;
       w.matrix = nullptr; w.item_matrices = d_T.p; w.D = d_D.p; w.dl = dl0; w.fo = fo;
       w.rowbuf = d_hcol.p; w.rowbuf_stride = n_max + 1;
-      w.nzw = nzw; w.fail_count = d_wz.p; w.fail_list = d_wz.p + 8;
-      w.zbuf = stateful ? d_wz.p + 8 + chunk : nullptr;
+      w.nzw = nzw;
+      warp_scratch_bind(w, d_wz.p, chunk, true);
       w.H_out = nullptr; w.D_out = nullptr;
       ALNR_CUDA(cudaMemsetAsync(d_wz.p, 0, 8 * sizeof(uint32_t), stream));
       { int wst = warp_launch_f64(stream, w, true, false); if (wst) return wst; }

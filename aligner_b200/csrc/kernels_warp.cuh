@@ -68,12 +68,17 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) fill_warp_kernel(WarpArgs
   // PWM view (common.cuh): the shared matrix is the 4 x L profile, a row of it per target symbol
   const bool pwm = a.cv.pwm_len != 0;
   const int V = pwm ? (int)a.cv.pwm_len : a.V, VV = pwm ? 4 * V : V * V;
-  const uint32_t slot = blockIdx.x * kWarpsPerBlock + warp;
+  uint32_t slot = blockIdx.x * kWarpsPerBlock + warp;
   bool have = slot < a.cv.count;
+  if (a.list) {  // second launch of the incremental speculation: the slots the verify kernel left
+    have = slot < *a.list_count;
+    if (have) slot = a.list[slot];
+  }
   uint32_t pair = 0;
   if (have) {
     pair = a.cv.order ? a.cv.order[a.cv.first + slot] : a.cv.first + slot;
-    if (a.fo.status[pair] != 0) have = false;  // rejected by validation
+    // rejected by validation; 11 may be left over from the first launch
+    if (a.fo.status[pair] != 0 && !(a.list && a.fo.status[pair] == 11)) have = false;
   }
   const T *smat;
   if (a.item_matrices) {
@@ -107,14 +112,20 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) fill_warp_kernel(WarpArgs
   const uint32_t nbands = (m + BH - 1) / BH;
   const uint32_t m_lane = ((m - 1) % BH) / R, m_r = (m - 1) % R;  // where row m lives (last band)
   const T del = a.del, ext = a.ext;
+  const T ndel0 = nsub(T(0), del);  // 0 - del: "top" below a Beginning cell
   const bool stateful = MODE == 2 && a.stateful;  // MODE 2 also runs static-penalty problems
   T *rowbuf = a.rowbuf + (size_t)slot * a.rowbuf_stride;
   uint32_t *Dslot = a.D + (uint64_t)slot * a.dl.nstrips * (a.dl.ncols + 31);
   const uint64_t band_words = (uint64_t)(a.dl.ncols + 31) * 32;
   const size_t W = (size_t)n + 1;
   uint32_t *zb0 = stateful ? a.zbuf + (size_t)slot * 2 * a.nzw : nullptr;
-  const uint32_t *zin = nullptr;
-  uint32_t *zout = zb0;
+  // first launch: assume all-zero bits, observe into zb0; second launch: start from those
+  const uint32_t *zin = (stateful && a.list) ? zb0 : nullptr;
+  uint32_t *zout = (stateful && a.list) ? zb0 + a.nzw : zb0;
+  // one pass only, mispredicted slots go to the verify kernel (needs lane 0's bottom row: rowbuf is
+  // free when there is a single band)
+  const bool defer = stateful && !MATS && a.vlist && !a.list && nbands == 1 && m > (uint32_t)R;
+  if (a.list && lane == 0) a.fo.status[pair] = 0;
 
   // row 0 and column 0 of the optional full matrices (simple/mod.rs:59-70; zeros/Beginning local)
   if (MATS) {
@@ -198,17 +209,28 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) fill_warp_kernel(WarpArgs
           }
           uint32_t bits = 0;
           bool hit = false;  // some cell of this step reaches the running maximum (rare)
+          bool zp = false;   // MODE 2: the cell above is Beginning
 #pragma unroll
           for (int r = 0; r < R; ++r) {
             const T sc = lds_score(toff[r] + qoff, T(0));
-            const T top = nsub(hup, pen), lft = nsub(h[r], pen), dg = nadd(diag, sc);
+            T top, lft;
+            if (MODE == 2 && r > 0) {
+              // penalty = del iff the cell above is Beginning, i.e. hup == 0: both candidates are
+              // formed off the dependent chain, the zero test of the cell above only selects
+              const T le = nsub(h[r], ext), ld = nsub(h[r], del);
+              top = zp ? ndel0 : nsub(hup, ext);
+              lft = zp ? ld : le;
+            } else {
+              top = nsub(hup, pen); lft = nsub(h[r], pen);
+            }
+            const T dg = nadd(diag, sc);
             const T mx = wmax3(top, lft, dg);
             uint32_t d = Num<T>::same(mx, lft) ? DIR_LEFT : DIR_DIAGONAL;  // enums.rs:23/:41
             d = Num<T>::same(mx, top) ? DIR_TOP : d;                       // enums.rs:21/:39
             if (LOCAL) {
               const bool zero = Num<T>::is_zero(mx);                       // enums.rs:37
               d = zero ? DIR_BEGINNING : d;
-              if (MODE == 2) pen = zero ? del : ext;
+              if (MODE == 2) zp = zero;
             }
             if (MODE != 2) pen = ext;
             bits |= d << (2 * r);
@@ -234,6 +256,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) fill_warp_kernel(WarpArgs
           bottom = hup;
           if (store_d) *dp = bits;
           if (lane == 31 && !last_band) rowbuf[x] = hup;
+          if (defer && lane == 0) rowbuf[x] = hup;  // row R, kept for warp_verify_kernel
           if (obs_lane && (stateful || x == n)) {
             T hm = h[0];
 #pragma unroll
@@ -260,6 +283,10 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) fill_warp_kernel(WarpArgs
     }
     if (!stateful) break;
     if (!__any_sync(0xffffffffu, mism)) break;
+    if (defer) {  // provisional results are written below; the verify kernel takes it from there
+      if (lane == 0) a.vlist[atomicAdd(a.vcount, 1u)] = slot;
+      break;
+    }
     if (pass + 1 == kWarpPasses) { settled = false; break; }
     zin = zout;
     zout = (zout == zb0) ? zb0 + a.nzw : zb0;
@@ -295,6 +322,93 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) fill_warp_kernel(WarpArgs
       a.fo.start[2 * (size_t)pair + 1] = n;
     }
   }
+}
+
+// Incremental speculation, step 2 (see WarpArgs::vlist).  One THREAD per mispredicted slot recomputes
+// the rows lane 0 held (1..R) over all columns with the observed bits, in the reference's own order
+// (x outer, y inner; only row 1 takes its penalty from the bits).  A wrong penalty disturbs the
+// matrix only a few rows deep, so row R almost always comes out as the first launch kept it in
+// rowbuf: then every row below, row m and the observed bits stand, the direction words of lane 0
+// are rewritten and the arg-max is re-derived from the best P of rows 1..R and the previous arg-max
+// G (G below row R is still the first maximum of the unchanged rows: P wins iff P.v >= G.v; G
+// inside rows 1..R stands only if P.v >= G.v, else undecided).  Changed or undecided slots go on
+// rlist for the second launch of the warp kernel.
+template <typename T>
+__global__ void __launch_bounds__(128) warp_verify_kernel(WarpArgs<T> a) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= *a.vcount) return;
+  const uint32_t slot = a.vlist[i];
+  const uint32_t pair = a.cv.order ? a.cv.order[a.cv.first + slot] : a.cv.first + slot;
+  const bool pwm = a.cv.pwm_len != 0;
+  const int stride = pwm ? (int)a.cv.pwm_len : a.V, elems = pwm ? 4 * stride : a.V * a.V;
+  const T *mat = a.item_matrices ? a.item_matrices + (size_t)pair * elems : a.matrix;
+  const uint32_t sp = a.cv.seq(pair);
+  const uint8_t *q, *t;
+  uint32_t n, m;
+  a.cv.pair_dims(sp, q, t, n, m);
+  const uint32_t R = a.dl.rows_per_word;  // m > R and a single band: checked by the first launch
+  const T del = a.del, ext = a.ext;
+  const uint32_t *zobs = a.zbuf + (size_t)slot * 2 * a.nzw;
+  const T *kept = a.rowbuf + (size_t)slot * a.rowbuf_stride;
+  uint32_t *Dslot = a.D ? a.D + (uint64_t)slot * a.dl.nstrips * (a.dl.ncols + 31) : nullptr;
+  constexpr int kMaxR = 16;
+  T h[kMaxR];
+  uint32_t toff[kMaxR];
+#pragma unroll
+  for (int r = 0; r < kMaxR; ++r) {
+    h[r] = T(0);
+    toff[r] = (uint32_t)r < R ? (uint32_t)t[r] * stride : 0u;
+  }
+  T best = T(0);
+  uint32_t by = 0, bx = 0, zw = 0;
+  bool changed = false;
+  for (uint32_t x = 1; x <= n; ++x) {
+    const uint32_t qs = pwm ? x - 1 : q[x - 1];
+    bool z = x == 1;  // initial penalty = del (simple/mod.rs:185)
+    if (x > 1) {
+      if (((x - 2) & 31) == 0) zw = zobs[(x - 2) >> 5];
+      z = (zw >> ((x - 2) & 31)) & 1u;  // H[m][x-1] == 0
+    }
+    T pen = z ? del : ext;
+    T diag = T(0), hup = T(0);
+    uint32_t bits = 0;
+#pragma unroll
+    for (int r = 0; r < kMaxR; ++r) {
+      if ((uint32_t)r < R) {
+        const T sc = mat[toff[r] + qs];
+        const T top = nsub(hup, pen), lft = nsub(h[r], pen), dg = nadd(diag, sc);
+        const T mx = wmax3(top, lft, dg);
+        uint32_t d = Num<T>::same(mx, lft) ? DIR_LEFT : DIR_DIAGONAL;
+        d = Num<T>::same(mx, top) ? DIR_TOP : d;
+        const bool zero = Num<T>::is_zero(mx);
+        d = zero ? DIR_BEGINNING : d;
+        pen = zero ? del : ext;
+        bits |= d << (2 * r);
+        diag = h[r];
+        h[r] = mx;
+        hup = mx;
+        const uint32_t y = r + 1;
+        if (mx > best || (mx == best && y < by)) { best = mx; by = y; bx = x; }
+      }
+    }
+    changed |= !(hup == kept[x]);
+    if (Dslot) Dslot[(uint64_t)(x - 1) * 32] = bits;  // band 0, lane 0 of the skewed layout
+  }
+  bool decided = !changed;
+  if (decided) {
+    const T gv = (T)a.fo.f[pair];
+    const uint32_t gy = a.fo.start[2 * (size_t)pair];
+    const bool p_ok = by != 0 && bx != 0;
+    if (gy == 0 || (p_ok && best >= gv)) {
+      a.fo.f[pair] = (double)best;
+      a.fo.start[2 * (size_t)pair] = by;
+      a.fo.start[2 * (size_t)pair + 1] = bx;
+      a.fo.status[pair] = (p_ok || pwm) ? 0 : 11;  // ALNR_NO_POSITIVE_CELL (simple/mod.rs:214)
+    } else if (gy <= R) {
+      decided = false;
+    }
+  }
+  if (!decided) a.rlist[atomicAdd(a.rcount, 1u)] = slot;
 }
 
 }  // namespace alnr

@@ -10,6 +10,8 @@
 // symbols, arg-max (0,0) is an empty alignment.
 #include <algorithm>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 #include <vector>
 
 #include "host_util.h"
@@ -221,7 +223,7 @@ int pwm_run(const alnr_pwm_params *p, alnr_pwm_seq *seq, const alnr_windows *w, 
   ALNR_CUDA(d_start.alloc(2 * count)); ALNR_CUDA(d_coords.alloc(4 * count));
   ALNR_CUDA(d_alnoff.alloc(count)); ALNR_CUDA(d_alnlen.alloc(count));
   ALNR_CUDA(d_hcol.alloc((chunk + 31) / 32 * 32 * row_words));
-  ALNR_CUDA(d_wz.alloc(8 + chunk * (1 + (stateful ? 2ull * nzw : 0))));
+  ALNR_CUDA(d_wz.alloc(warp_scratch_words(chunk, nzw, stateful)));
   if (want_aln || mats) ALNR_CUDA(d_D.alloc(dl.words_for(chunk)));
   if (out->numbered || out->query) { ALNR_CUDA(d_num.alloc(chunk * slot)); ALNR_CUDA(d_qry.alloc(chunk * slot)); }
   if (out->freq) ALNR_CUDA(d_freq.alloc(chunk * 4 * L));
@@ -256,8 +258,8 @@ int pwm_run(const alnr_pwm_params *p, alnr_pwm_seq *seq, const alnr_windows *w, 
       a.cv = cv; a.V = 4; a.del = (T)p->del; a.ext = (T)p->ext; a.stateful = stateful;
       a.matrix = d_pwm.p; a.item_matrices = nullptr; a.D = D; a.dl = dl; a.fo = fo;
       a.rowbuf = d_hcol.p; a.rowbuf_stride = L + 1;
-      a.nzw = nzw; a.fail_count = d_wz.p; a.fail_list = d_wz.p + 8;
-      a.zbuf = stateful ? d_wz.p + 8 + chunk : nullptr;
+      a.nzw = nzw;
+      warp_scratch_bind(a, d_wz.p, chunk, !mats);
       a.H_out = mats ? d_Hout.p : nullptr; a.D_out = mats ? d_Dout.p : nullptr;
       ALNR_CUDA(cudaMemsetAsync(d_wz.p, 0, 8 * sizeof(uint32_t), stream));
       int st = pwm_warp_launch<T>(stream, a, mats);
@@ -281,6 +283,13 @@ int pwm_run(const alnr_pwm_params *p, alnr_pwm_seq *seq, const alnr_windows *w, 
     ALNR_CUDA(d2h(out->query ? out->query + base * slot : nullptr, d_qry.p, (size_t)cnt * slot));
     ALNR_CUDA(d2h(out->freq ? out->freq + base * 4 * L : nullptr, d_freq.p, (size_t)cnt * 4 * L * 8));
     ALNR_CUDA(cudaStreamSynchronize(stream));  // the staging buffers are reused by the next chunk
+    static const bool timing = getenv("ALNR_TIMING") != nullptr;
+    if (timing && use_warp && stateful) {  // exact-kernel list, mispredicted, left after the verify kernel
+      uint32_t hc[4] = {0, 0, 0, 0};
+      ALNR_CUDA(cudaMemcpy(hc, d_wz.p, sizeof(hc), cudaMemcpyDeviceToHost));
+      std::fprintf(stderr, "[alnr] pwm speculation: %u windows, mispredicted %u, second launch %u, exact kernel %u\n",
+                   cnt, hc[1], hc[2], hc[0]);
+    }
   }
   ALNR_CUDA(d2h(out->f, d_f.p, count * 8));
   ALNR_CUDA(d2h(out->coords, d_coords.p, count * 32));

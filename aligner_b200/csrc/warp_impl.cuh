@@ -15,6 +15,16 @@ static int warp_launch_one(cudaStream_t stream, const WarpArgs<T> &a) {
     ALNR_CUDA(cudaFuncSetAttribute(fill_warp_kernel<T, R, MODE, MATS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   fill_warp_kernel<T, R, MODE, MATS><<<blocks, kWarpsPerBlock * 32, smem, stream>>>(a);
   ALNR_LAUNCHED();
+  if (MODE == 2 && !MATS && a.stateful && a.vlist && !a.list) {
+    // incremental speculation: settle the mispredicted slots from their top rows, loop over the rest
+    warp_verify_kernel<T><<<(a.cv.count + 127) / 128, 128, 0, stream>>>(a);
+    ALNR_LAUNCHED();
+    WarpArgs<T> b = a;
+    b.list = a.rlist; b.list_count = a.rcount;
+    b.vlist = nullptr; b.vcount = nullptr;
+    fill_warp_kernel<T, R, MODE, MATS><<<blocks, kWarpsPerBlock * 32, smem, stream>>>(b);
+    ALNR_LAUNCHED();
+  }
   return ALNR_OK;
 }
 
