@@ -462,10 +462,26 @@ static __global__ void pack2bit_kernel(const uint8_t *seq, const uint64_t *off, 
   const uint64_t slot = first + local;
   const uint32_t pair = order ? order[slot] : (uint32_t)slot;
   const uint64_t b = off[pair], e = off[pair + 1];
+  const uint64_t i0 = b + (uint64_t)w * 16;
   uint32_t word = 0;
-  for (uint32_t k = 0; k < 16; ++k) {
-    const uint64_t i = b + (uint64_t)w * 16 + k;
-    if (i < e) word |= (uint32_t)(seq[i] & 3u) << (2 * k);
+  if (i0 < e) {
+    // the 16 symbols as five aligned 32-bit loads + funnel shifts (the buffers are padded by 16
+    // bytes), then four 2-bit fields squeezed out of every word
+    const uintptr_t addr = reinterpret_cast<uintptr_t>(seq + i0);
+    const uint32_t *p4 = reinterpret_cast<const uint32_t *>(addr & ~(uintptr_t)3);
+    const uint32_t sh = 8u * (uint32_t)(addr & 3);
+    uint32_t W[5];
+#pragma unroll
+    for (int k = 0; k < 5; ++k) W[k] = p4[k];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      uint32_t x = __funnelshift_r(W[k], W[k + 1], sh) & 0x03030303u;
+      x = (x | (x >> 6)) & 0x000F000Fu;
+      x = (x | (x >> 12)) & 0xFFu;
+      word |= x << (8 * k);
+    }
+    const uint64_t left = e - i0;  // symbols of this pair in the word
+    if (left < 16) word &= (1u << (2 * (uint32_t)left)) - 1u;
   }
   out[((slot >> 5) * nw + w) * 32 + lane] = word;
 }
