@@ -343,7 +343,7 @@ int alnr_batch_impl::init(const alnr_params *p, const alnr_batch *b, bool want_m
     for (const Chunk &c : chunks)
       if (chunk_compact(c) && !score_only)
         mwords = std::max<uint64_t>(mwords, (uint64_t)((c.count + 31) / 32 * 32) * ((c.n_max + c.m_max + 1 + 15) / 16));
-    ALNR_CUDA(d_moves.alloc(mwords));
+    ALNR_CUDA(d_moves.alloc(2 * mwords));  // move words, then the start cell of every word
   }
 
   uint64_t dwords = 1, hcol = 1;
@@ -517,7 +517,8 @@ int alnr_batch_impl::phase2(size_t ci) {
     // alignments of the chunk back to back from the start of its region (kernels_trace.cuh A/S/B)
     const uint32_t stride = (c.count + 31) / 32 * 32;
     const uint32_t tiles = (c.count + kScanBlock * kScanItems - 1) / (kScanBlock * kScanItems);
-    trace_moves_kernel<<<(c.count + 127) / 128, 128, 0, s2>>>(ta, d_moves.p, stride);
+    uint32_t *cxy = d_moves.p + (size_t)stride * nmw;
+    trace_moves_kernel<<<(c.count + 127) / 128, 128, 0, s2>>>(ta, d_moves.p, cxy, stride);
     ALNR_LAUNCHED();
     ALNR_CUDA(cudaMemsetAsync(d_desc.p, 0, ((size_t)tiles + 1) * 8, s2));
     scan_lengths_kernel<<<tiles, kScanBlock, 0, s2>>>(d_alnlen.p, d_alnoff.p, c.first, c.count,
@@ -525,7 +526,9 @@ int alnr_batch_impl::phase2(size_t ci) {
                                                       reinterpret_cast<unsigned long long *>(d_desc.p),
                                                       d_ctotal.p + ci);
     ALNR_LAUNCHED();
-    trace_expand_kernel<<<(c.count + 127) / 128, 128, 0, s2>>>(ta, d_moves.p, stride);
+    const uint32_t G = trace_expand_group(c.n_max, c.m_max);
+    trace_expand_kernel<<<(c.count + G - 1) / G, kExpandThreads, trace_expand_smem(G, c.n_max, c.m_max), s2>>>(
+        ta, d_moves.p, cxy, stride, G, c.n_max, c.m_max, nmw);
   } else if (dl.blocked) {
     traceback_warp_kernel<<<c.count, 32, 0, s2>>>(ta);
   } else if ((size_t)nmw * kTraceBlock * 4 <= 44 * 1024 && to.freq == nullptr) {

@@ -228,12 +228,17 @@ namespace alnr {
 // ---- compact output for batches of equal-length short pairs (identity pair order) -----------
 // Three launches: (A) one thread per pair chases the directions and stores its 2-bit move string
 // in global memory, (S) a single-pass chained scan turns the alignment lengths into offsets —
-// alignment i starts at base + sum of aln_len of the chunk's earlier pairs — and (B) each warp
-// expands 32 move strings into the packed output.  The chunk's alignments are back to back, so
+// alignment i starts at base + sum of aln_len of the chunk's earlier pairs — and (B) each block
+// expands the move strings of 32 pairs into the packed output through shared memory.  The chunk's alignments are back to back, so
 // the device->host copy moves only the bytes that exist.
 
-// (A) mvg[w * stride + slot]; writes aln_len (0 for rejected pairs) and coords.
-static __global__ void __launch_bounds__(128) trace_moves_kernel(TraceArgs a, uint32_t *mvg, uint32_t stride) {
+// (A) mvg[w * stride + slot] = moves 16w .. 16w+15, cxyg[w * stride + slot] = cx | cy << 16 of the
+// walk before move 16w (word 0: the start cell); writes aln_len (0 for rejected pairs) and coords.
+// (A per-thread queue of speculatively fetched direction words along the diagonal was measured at
+// 2.6 ms per launch against 0.9 ms for this plain walk: the warp's 32 walks already overlap their
+// misses, the queue only added instructions and DRAM sectors.)
+static __global__ void __launch_bounds__(128) trace_moves_kernel(TraceArgs a, uint32_t *mvg, uint32_t *cxyg,
+                                                                 uint32_t stride) {
   const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
   if (slot >= a.cv.count) return;
   const uint32_t pair = a.cv.first + slot;
@@ -248,8 +253,9 @@ static __global__ void __launch_bounds__(128) trace_moves_kernel(TraceArgs a, ui
   const uint32_t m = (uint32_t)(a.cv.t_off[pair + 1] - a.cv.t_off[pair]);
   const uint32_t sy = a.fo.start[2 * (size_t)pair], sx = a.fo.start[2 * (size_t)pair + 1];
   uint32_t cy = sy, cx = sx, acc = 0, K = 0;
-  uint32_t *mv = mvg + slot;
+  uint32_t *mv = mvg + slot, *cw = cxyg + slot;
   for (;;) {
+    if ((K & 15) == 0) cw[(size_t)(K >> 4) * stride] = cx | (cy << 16);
     int d;
     if (cy == 0 || cx == 0) {
       if (!glob || (cy == 0 && cx == 0)) d = DIR_BEGINNING;
@@ -340,52 +346,104 @@ static __global__ void __launch_bounds__(kScanBlock) scan_lengths_kernel(const u
   }
 }
 
-// (B) each warp expands the move strings of 32 consecutive pairs: 32 moves at a time, symbol
-// positions by ballot/popc prefix counts, 32 consecutive output bytes per store.  The reference
-// seeds the string with the start pair and reverses it (simple/mod.rs:102-105,:129-130): move i
-// lands at aln_off + aln_len - 2 - i, the seed at aln_off + aln_len - 1.
-static __global__ void __launch_bounds__(128) trace_expand_kernel(TraceArgs a, const uint32_t *mvg, uint32_t stride) {
-  const uint32_t lane = threadIdx.x & 31;
-  const uint32_t wslot = (blockIdx.x * blockDim.x + threadIdx.x) & ~31u;  // first slot of this warp
-  if (wslot >= a.cv.count) return;
-  const uint32_t ltmask = (1u << lane) - 1u;
-  // lane l preloads pair wslot + l
-  uint32_t my_len = 0, my_sy = 0, my_sx = 0;
-  uint64_t my_off = 0;
-  if (wslot + lane < a.cv.count) {
-    const uint32_t pair = a.cv.first + wslot + lane;
-    my_len = a.to.aln_len[pair];
-    my_off = a.to.aln_off[pair];
-    my_sy = a.fo.start[2 * (size_t)pair];
-    my_sx = a.fo.start[2 * (size_t)pair + 1];
-  }
-  for (uint32_t pi = 0; pi < 32; ++pi) {
-    const uint32_t L = __shfl_sync(0xffffffffu, my_len, pi);
-    const uint64_t dst = __shfl_sync(0xffffffffu, my_off, pi);
-    uint32_t cy = __shfl_sync(0xffffffffu, my_sy, pi), cx = __shfl_sync(0xffffffffu, my_sx, pi);
-    if (L == 0) continue;
-    const uint32_t Kp = L - 1;
-    const uint32_t pair = a.cv.first + wslot + pi;
-    const uint8_t *q = a.cv.q + a.cv.q_off[pair], *t = a.cv.t + a.cv.t_off[pair];
-    const uint32_t *mv = mvg + wslot + pi;
-    const uint64_t end = dst + L;
-    if (lane == 0) { a.to.q_aln[end - 1] = q[cx - 1]; a.to.t_aln[end - 1] = t[cy - 1]; }
-    for (uint32_t b0 = 0; b0 < Kp; b0 += 32) {
-      const uint32_t i = b0 + lane;
-      const bool valid = i < Kp;
-      const uint32_t code = valid ? (mv[(size_t)(i >> 4) * stride] >> (2 * (i & 15))) & 3u : 3u;
-      const bool cq = valid && code != DIR_TOP, ct = valid && code != DIR_LEFT;
-      const uint32_t bq = __ballot_sync(0xffffffffu, cq), bt = __ballot_sync(0xffffffffu, ct);
-      if (valid) {
-        const uint32_t xi = cx - __popc(bq & ltmask), yi = cy - __popc(bt & ltmask);
-        const uint64_t pos = end - 2 - i;
-        a.to.q_aln[pos] = cq ? q[xi - 1] : (uint8_t)kBlank;
-        a.to.t_aln[pos] = ct ? t[yi - 1] : (uint8_t)kBlank;
-      }
-      cx -= __popc(bq);
-      cy -= __popc(bt);
+// (B) a block expands the move strings of G consecutive pairs.  Their symbols are one contiguous
+// range of q / t and their alignments one contiguous range of q_aln / t_aln, so both pass through
+// shared memory: the inputs arrive and the outputs leave as aligned 16-byte vectors (the shared
+// image has the global range's offset within its first 16 bytes), and in between one thread per
+// (pair, move word) walks its 16 moves from the word's start cell (cxyg) with byte accesses to
+// shared memory only.  The reference seeds the string with the start pair and reverses it
+// (simple/mod.rs:102-105,:129-130): move i lands at aln_off + aln_len - 2 - i, the seed at
+// aln_off + aln_len - 1.
+constexpr int kExpandThreads = 256;
+
+// shared bytes of trace_expand_kernel for G pairs of n x m symbols
+static inline size_t trace_expand_smem(uint32_t G, uint32_t n, uint32_t m) {
+  auto r16 = [](size_t v) { return (v + 15) / 16 * 16; };
+  return r16((size_t)G * 8) + r16((size_t)G * n + 32) + r16((size_t)G * m + 32) + 2 * r16((size_t)G * (n + m + 1) + 32);
+}
+
+// pairs per block: 32 (one warp reads a 128-byte line of move words) unless the strings are long
+static inline uint32_t trace_expand_group(uint32_t n, uint32_t m) {
+  uint32_t G = 32;
+  while (G > 1 && trace_expand_smem(G, n, m) > 46 * 1024) G >>= 1;
+  return G;
+}
+
+static __device__ __forceinline__ void stage_in(uint8_t *dst, const uint8_t *src, uint32_t bytes, uint32_t &shift) {
+  // dst[shift + i] = src[i]: whole aligned vectors around the range (the buffers are padded)
+  shift = (uint32_t)((uintptr_t)src & 15);
+  const uint4 *v = reinterpret_cast<const uint4 *>(src - shift);
+  for (uint32_t i = threadIdx.x * 16; i < shift + bytes; i += kExpandThreads * 16)
+    *reinterpret_cast<uint4 *>(dst + i) = __ldg(v + (i >> 4));
+}
+
+static __device__ __forceinline__ void stage_out(uint8_t *dst, const uint8_t *src, uint32_t bytes, uint32_t shift) {
+  // dst[i] = src[shift + i], dst - shift 16-byte aligned: vectors inside the range, bytes at its ends
+  for (uint32_t i = threadIdx.x * 16; i < shift + bytes; i += kExpandThreads * 16) {
+    if (i >= shift && i + 16 <= shift + bytes) {
+      *reinterpret_cast<uint4 *>(dst - shift + i) = *reinterpret_cast<const uint4 *>(src + i);
+    } else {
+      const uint32_t lo = i > shift ? i : shift, hi = i + 16 < shift + bytes ? i + 16 : shift + bytes;
+      for (uint32_t j = lo; j < hi; ++j) dst[(size_t)j - shift] = src[j];
     }
   }
+}
+
+static __global__ void __launch_bounds__(kExpandThreads) trace_expand_kernel(TraceArgs a, const uint32_t *mvg,
+                                                                             const uint32_t *cxyg, uint32_t stride,
+                                                                             uint32_t G, uint32_t n, uint32_t m,
+                                                                             uint32_t nmw) {
+  extern __shared__ __align__(16) uint8_t sm_expand[];
+  auto r16 = [](uint32_t v) { return (v + 15u) / 16u * 16u; };
+  const uint32_t slot0 = blockIdx.x * G;
+  if (slot0 >= a.cv.count) return;
+  const uint32_t cnt = min(G, a.cv.count - slot0);
+  const uint32_t pair0 = a.cv.first + slot0;
+  uint32_t *s_len = reinterpret_cast<uint32_t *>(sm_expand);  // [G] aln_len
+  uint32_t *s_end = s_len + G;                                // [G] end of the alignment, relative to the block's range
+  uint8_t *q_in = sm_expand + r16(G * 8);
+  uint8_t *t_in = q_in + r16(G * n + 32);
+  uint8_t *q_out = t_in + r16(G * m + 32);
+  uint8_t *t_out = q_out + r16(G * (n + m + 1) + 32);
+  const uint64_t out0 = a.to.aln_off[pair0];
+  if (threadIdx.x < cnt) {
+    const uint32_t L = a.to.aln_len[pair0 + threadIdx.x];
+    s_len[threadIdx.x] = L;
+    s_end[threadIdx.x] = (uint32_t)(a.to.aln_off[pair0 + threadIdx.x] - out0) + L;
+  }
+  uint32_t shq, sht;
+  stage_in(q_in, a.cv.q + a.cv.q_off[pair0], cnt * n, shq);
+  stage_in(t_in, a.cv.t + a.cv.t_off[pair0], cnt * m, sht);
+  __syncthreads();
+  const uint32_t total = s_end[cnt - 1];
+  uint8_t *gq = a.to.q_aln + out0, *gt = a.to.t_aln + out0;
+  const uint32_t oq = (uint32_t)((uintptr_t)gq & 15), ot = (uint32_t)((uintptr_t)gt & 15);
+  for (uint32_t u = threadIdx.x; u < G * nmw; u += kExpandThreads) {
+    const uint32_t g = G == 32 ? (u & 31u) : u % G, w = G == 32 ? (u >> 5) : u / G;
+    if (g >= cnt) continue;
+    const uint32_t L = s_len[g];
+    if (L == 0 || (w != 0 && w * 16 >= L - 1)) continue;
+    const uint32_t cxy = cxyg[(size_t)w * stride + slot0 + g];
+    uint32_t cx = cxy & 0xffffu, cy = cxy >> 16;
+    const uint8_t *qs = q_in + shq + g * n - 1, *ts = t_in + sht + g * m - 1;  // qs[x] = symbol x (1-based)
+    const uint32_t e = s_end[g];
+    if (w == 0) { q_out[oq + e - 1] = qs[cx]; t_out[ot + e - 1] = ts[cy]; }
+    if (w * 16 >= L - 1) continue;
+    uint32_t mvw = mvg[(size_t)w * stride + slot0 + g];
+    const uint32_t steps = min(16u, L - 1 - w * 16);
+    uint32_t pos = e - 2 - w * 16;
+    for (uint32_t j = 0; j < steps; ++j, --pos, mvw >>= 2) {
+      const uint32_t code = mvw & 3u;
+      uint8_t bq = (uint8_t)kBlank, bt = (uint8_t)kBlank;
+      if (code != DIR_TOP) { bq = qs[cx]; --cx; }
+      if (code != DIR_LEFT) { bt = ts[cy]; --cy; }
+      q_out[oq + pos] = bq;
+      t_out[ot + pos] = bt;
+    }
+  }
+  __syncthreads();
+  stage_out(gq, q_out, total, oq);
+  stage_out(gt, t_out, total, ot);
 }
 
 }  // namespace alnr

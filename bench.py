@@ -103,6 +103,33 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+_ALL_CPUS = None
+
+
+def bind_to_gpu_node(props):
+    """Run this rank on the cores of the GPU's own NUMA node, so that the pinned buffers (first
+    touch) and the library's host threads sit next to the PCIe root the copies go through.
+    Best effort: sysfs may hide the topology inside a container; then nothing changes."""
+    try:
+        bdf = "%04x:%02x:%02x.0" % (props.pci_domain_id, props.pci_bus_id, props.pci_device_id)
+        base = "/sys/bus/pci/devices/" + bdf
+        node = int(open(base + "/numa_node").read())
+        cpus = set()
+        for part in open(base + "/local_cpulist").read().strip().split(","):
+            if part:
+                lo, _, hi = part.partition("-")
+                cpus.update(range(int(lo), int(hi or lo) + 1))
+        global _ALL_CPUS
+        _ALL_CPUS = os.sched_getaffinity(0)
+        cpus &= _ALL_CPUS
+        if node < 0 or len(cpus) < 4 or cpus == os.sched_getaffinity(0):
+            return {"node": node, "bound": False, "cpus": len(os.sched_getaffinity(0))}
+        os.sched_setaffinity(0, cpus)
+        return {"node": node, "bound": True, "cpus": len(cpus)}
+    except (OSError, ValueError, AttributeError):
+        return {"node": None, "bound": False, "cpus": len(os.sched_getaffinity(0))}
+
+
 def pinned_array(lib, shape, dtype):
     n = int(np.prod(shape)) * np.dtype(dtype).itemsize
     ptr = lib.alnr_host_alloc(max(n, 1))
@@ -176,6 +203,7 @@ def main():
     local = int(os.environ.get("LOCAL_RANK", "0"))
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the product has no CPU fallback")
+    numa = bind_to_gpu_node(torch.cuda.get_device_properties(local))
     torch.cuda.set_device(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
@@ -287,7 +315,7 @@ def main():
             "data": "synthetic",
             "config": {"workload": workload_name(a), "pairs_per_gpu": cnt, "cells_per_step_per_gpu": cells,
                        "l2": "inputs+scratch (>3 GB) exceed the 126 MB L2; no explicit flush",
-                       "parity_spot_check": okp, "speculation_reruns_per_step": reruns},
+                       "parity_spot_check": okp, "host_numa": numa, "speculation_reruns_per_step": reruns},
             "clocks": clocks, "gpu_launches": int(launches_per_step * a.steps),
             "e2e": {"value": e2e_val, "unit": "GCUPS", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "s_per_step": float(te[0]), "timer": "host wall clock around the synchronous C-ABI call"},
@@ -306,6 +334,8 @@ def main():
                                  "note": "2-bit direction matrix writes, 0.25 B/cell; peak of measured" if peaks else "of fallback"}},
         }
         if not a.no_cpu_baseline:
+            if _ALL_CPUS:
+                os.sched_setaffinity(0, _ALL_CPUS)  # the CPU arm gets every core of the box
             threads = os.cpu_count() or 1
             g, npairs, secs = cpu_baseline(a, threads, a.cpu_seconds)
             line["cpu_baseline"] = {"value": g, "unit": "GCUPS", "cores": threads, "kind": "port",
