@@ -1,0 +1,227 @@
+// kernels_tile.cuh — intra-pair fill for ONE long pair (BASELINE config 4), second generation of
+// the band pipeline of kernels_band.cuh: the same pipeline of 128-row bands (one warp per band,
+// lane l owns 4 consecutive rows and runs l steps behind lane l-1), but a lane's step is a
+// 4 x 4 TILE of cells instead of a 4 x 1 column:
+//   * the per-step overhead (4 shuffles for the tile's top row, the query load, the D store, the
+//     boundary-row hand-off) is paid once per 16 cells instead of once per 4;
+//   * the 16 cells of a tile form 7 anti-diagonals, so a lane has ~2.3 independent dependency
+//     chains in flight — the column kernel had one, and it was bound by single-warp latency;
+//   * a tile is exactly one word of the "blocked" 2-bit D layout (4 rows x 4 columns, common.cuh):
+//     one aligned 32-bit streaming store per lane per step, same traceback as before;
+//   * the substitution scores of the lane's 4 rows sit in shared memory as one int4 per query
+//     symbol ([symbol][lane], conflict-free 16-byte loads): 4 loads per tile instead of 16;
+//   * the pipeline is 4x shorter in steps: n/4 + 32 per band instead of n + 31.
+//
+// Band b takes its top boundary row from band b-1 through an L2-resident row buffer WITHOUT a
+// separate progress word: the buffer is preset to a sentinel that no score can take
+// (0x80808080; |H| < 2^30 is guaranteed by the numeric-domain test, batch.cu::classify), lane 31 of
+// the producer stores its tile's bottom row with one 16-byte st.cg, and the consumer prefetches the
+// 32 values of its next 8 steps one chunk ahead (ld.cg) and re-loads the lanes that still hold the
+// sentinel.  Data and flag are the same word, so no fence and no second round trip; in steady
+// state (producer far ahead) the consumer never waits, during the ramp it follows 8 + 31 steps
+// behind, the minimum a 32-lane skew allows.
+//
+// Static penalty only, exactly like kernels_band.cuh (global mode: cell (1,1) pays del, every
+// other cell ext, simple/mod.rs:72,88-92; local mode with del == ext).
+#pragma once
+#include "kernels_band.cuh"
+
+namespace alnr {
+
+constexpr int kTileSentinel = (int)0x80808080u;
+constexpr uint32_t kTileChunk = 8;  // steps per boundary chunk (8 steps x 4 columns = 32 values, one per lane)
+
+struct TileLane {
+  int h[4];         // H[yl0+1+r][c0]: the column left of the lane's next tile
+  int bot[4];       // bottom row of the lane's previous tile (lane+1 reads it by shuffle)
+  int diag0;        // H[yl0][c0]: corner above-left of the next tile
+  uint32_t qw;      // the 4 query symbols of the next tile
+  const uint8_t *qp;
+  uint32_t *dptr;   // D word of the next tile
+  int *rowp;        // &my_row[c0] of the next tile
+  int best_v;
+  uint32_t best_y, best_x;
+  int corner;
+  bool has_corner;
+};
+
+// 4 symbols starting at any byte address (two aligned words + funnel shift; the buffers carry 16
+// bytes of padding, batch.cu)
+__device__ __forceinline__ uint32_t tile_load_q4(const uint8_t *p) {
+  const uintptr_t a = reinterpret_cast<uintptr_t>(p);
+  const uint32_t *w = reinterpret_cast<const uint32_t *>(a & ~(uintptr_t)3);
+  return __funnelshift_r(w[0], w[1], (uint32_t)(a & 3) * 8u);
+}
+
+__device__ __forceinline__ int tile_ld_row(const int *p) {
+  int v;
+  asm volatile("ld.global.cg.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+// One step: lane l computes tile ti = s - l (columns 4 ti + 1 .. 4 ti + 4) of its 4 rows.
+// EDGE = true adds what only ramp-up / drain / the last columns need: the ti < ntiles test, the
+// masking of query symbols past column n (those cells are computed and never read), the one cell
+// that pays `del` in global mode and the capture of H[m][n].
+template <bool LOCAL, bool EDGE>
+__device__ __forceinline__ void tile_step(TileLane &L, const int4 *sm_sc, const int *sm_top, uint32_t s, uint32_t lane,
+                                          uint32_t yl0, uint32_t n, uint32_t m, uint32_t ntiles, int del, int ext,
+                                          bool store_d, bool row_out) {
+  int up[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) up[j] = __shfl_up_sync(0xffffffffu, L.bot[j], 1);
+  const int4 tp = *reinterpret_cast<const int4 *>(sm_top + 4 * (s & (kTileChunk - 1)));
+  if (lane == 0) { up[0] = tp.x; up[1] = tp.y; up[2] = tp.z; up[3] = tp.w; }
+  const uint32_t ti = s - lane;  // wraps for s < lane
+  if (EDGE && ti >= ntiles) return;
+  const uint32_t c0 = ti * 4;
+  const uint32_t qw = L.qw;
+  L.qp += 4;
+  L.qw = tile_load_q4(L.qp);
+  const int corner_in = L.diag0;
+  L.diag0 = up[3];
+  uint32_t word = 0;
+  bool hit = false;
+  int v[4][4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    uint32_t sym = (qw >> (8 * j)) & 0xffu;
+    if (EDGE && c0 + j >= n) sym = 0;
+    const int4 s4 = sm_sc[sym * 32 + lane];
+    const int sc[4] = {s4.x, s4.y, s4.z, s4.w};
+    int diag = j == 0 ? corner_in : up[j - 1];
+    int hup = up[j];
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      const int pen = (EDGE && !LOCAL && r == 0 && j == 0 && yl0 == 0 && c0 == 0) ? del : ext;
+      const int top = hup - pen, left = L.h[r] - pen, dg = diag + sc[r];
+      const int mx = max(max(top, left), dg);
+      uint32_t code = (mx == left) ? DIR_LEFT : DIR_DIAGONAL;  // enums.rs:23/:41
+      code = (mx == top) ? DIR_TOP : code;                     // enums.rs:21/:39
+      if (LOCAL) code = (mx == 0) ? DIR_BEGINNING : code;      // enums.rs:37
+      word |= code << (8 * j + 2 * r);
+      diag = L.h[r];
+      L.h[r] = mx;
+      hup = mx;
+      if (LOCAL) { hit |= mx >= L.best_v; v[r][j] = mx; }
+    }
+    L.bot[j] = hup;
+    if (EDGE && c0 + j + 1 == n) {
+#pragma unroll
+      for (int r = 0; r < 4; ++r)
+        if (yl0 + r + 1 == m) { L.corner = L.h[r]; L.has_corner = true; }
+    }
+  }
+  if (LOCAL && hit) {  // rare: first maximum in row-major order (simple/mod.rs:212)
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      const uint32_t y = yl0 + r + 1;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const uint32_t x = c0 + j + 1;
+        const int w = v[r][j];
+        if (y <= m && x <= n && (w > L.best_v || (w == L.best_v && y < L.best_y))) {
+          L.best_v = w; L.best_y = y; L.best_x = x;
+        }
+      }
+    }
+  }
+  if (store_d) __stcs(L.dptr, word);
+  ++L.dptr;
+  if (row_out) __stcg(reinterpret_cast<int4 *>(L.rowp), make_int4(L.bot[0], L.bot[1], L.bot[2], L.bot[3]));
+  L.rowp += 4;
+}
+
+// BandArgs as in kernels_band.cuh, except: rows = [nbands][npad] indexed by the 0-based column
+// (npad = n rounded up to 4, preset to kTileSentinel), prog unused.
+template <bool LOCAL>
+__global__ void __launch_bounds__(32) fill_tile_kernel(BandArgs a) {
+  extern __shared__ int4 tsm[];  // [V][32] score quadruples, then 32 ints of boundary values
+  const uint32_t lane = threadIdx.x;
+  const uint32_t V = (uint32_t)a.V;
+  int4 *sm_sc = tsm;
+  int *sm_top = reinterpret_cast<int *>(tsm + V * 32);
+  const uint32_t n = a.n, m = a.m;
+  const uint32_t ntiles = (n + 3) / 4, npad = ntiles * 4;
+  const int del = a.del, ext = a.ext;
+  TileLane L;
+  L.best_v = 0; L.best_y = 0; L.best_x = 0;
+
+  for (uint32_t band = blockIdx.x; band < a.nbands; band += gridDim.x) {
+    const uint32_t yl0 = band * 128u + lane * 4u;  // this lane's rows: yl0+1 .. yl0+4 (1-based)
+    uint32_t trow[4];
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      const uint32_t y = yl0 + r + 1;
+      const bool valid = y <= m;
+      trow[r] = (valid ? (uint32_t)a.t[y - 1] : 0u) * V;
+      int v = 0;
+      if (!LOCAL && valid) v = (y == m) ? -(int)(m + 1) * del : -(int)y * del;  // simple/mod.rs:64-67,:70
+      L.h[r] = v;
+    }
+    __syncwarp();
+    for (uint32_t sym = 0; sym < V; ++sym)
+      sm_sc[sym * 32 + lane] = make_int4(__ldg(a.matrix + trow[0] + sym), __ldg(a.matrix + trow[1] + sym),
+                                         __ldg(a.matrix + trow[2] + sym), __ldg(a.matrix + trow[3] + sym));
+    L.diag0 = (LOCAL || yl0 == 0) ? 0 : -(int)yl0 * del;  // H[yl0][0]
+#pragma unroll
+    for (int j = 0; j < 4; ++j) L.bot[j] = 0;
+    L.qp = a.q;
+    L.qw = tile_load_q4(L.qp);
+    L.corner = 0; L.has_corner = false;
+    const int *top_row = band ? a.rows + (size_t)(band - 1) * npad : nullptr;
+    const bool store_d = yl0 < m && a.D != nullptr;  // score-only calls pass no D scratch
+    const bool last_band = band + 1 == a.nbands;
+    const bool row_out = lane == 31 && !last_band;
+    L.dptr = a.D + (size_t)(yl0 / 4) * a.dcols;  // this lane's 4-row strip
+    L.rowp = a.rows + (size_t)band * npad;
+    const uint32_t steps = ntiles + 31;
+    int pre = band ? tile_ld_row(top_row + lane) : 0;  // npad >= 4 and the buffer is padded by 32
+
+    for (uint32_t s0 = 0; s0 < steps; s0 += kTileChunk) {
+      const uint32_t col = 4 * s0 + lane;  // 0-based column of this lane's boundary value, x = col + 1
+      if (4 * s0 < npad) {
+        if (band) {
+          // the producer's 16-byte stores land whole tiles; a lane that still sees the sentinel re-loads
+          for (;;) {
+            const bool need = col < npad && pre == kTileSentinel;
+            if (!__any_sync(0xffffffffu, need)) break;
+            if (need) { __nanosleep(20); pre = tile_ld_row(top_row + col); }
+          }
+        } else {  // H[0][x]: simple/mod.rs:59-62, :69
+          const uint32_t xx = col + 1;
+          pre = (LOCAL || xx > n) ? 0 : ((xx == n) ? -(int)(n + 1) * del : -(int)xx * del);
+        }
+        __syncwarp();
+        sm_top[lane] = pre;
+        __syncwarp();
+        const uint32_t ncol = col + 4 * kTileChunk;
+        pre = (band && ncol < npad) ? tile_ld_row(top_row + ncol) : 0;  // prefetch the next chunk
+      }
+      // steady: every lane is inside [1, ntiles) for all steps and nobody touches column n
+      const bool steady = s0 >= 32 && 4 * (s0 + kTileChunk) < n;
+      if (steady) {
+#pragma unroll
+        for (uint32_t j = 0; j < kTileChunk; ++j)
+          tile_step<LOCAL, false>(L, sm_sc, sm_top, s0 + j, lane, yl0, n, m, ntiles, del, ext, store_d, row_out);
+      } else {
+        const uint32_t jend = min(kTileChunk, steps - s0);
+        for (uint32_t j = 0; j < jend; ++j)
+          tile_step<LOCAL, true>(L, sm_sc, sm_top, s0 + j, lane, yl0, n, m, ntiles, del, ext, store_d, row_out);
+      }
+    }
+    if (last_band && L.has_corner) *a.corner_out = L.corner;
+    __syncwarp();
+  }
+  if (LOCAL) {
+    unsigned long long key = L.best_v > 0 ? band_key(L.best_v, L.best_y, L.best_x) : 0ull;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const unsigned long long other = __shfl_xor_sync(0xffffffffu, key, o);
+      key = other > key ? other : key;
+    }
+    if (lane == 0 && key) atomicMax(a.best, key);
+  }
+}
+
+}  // namespace alnr

@@ -3,7 +3,7 @@
 #include <algorithm>
 #include <cstdlib>
 
-#include "kernels_band.cuh"
+#include "kernels_tile.cuh"
 #include "strip_launch.h"
 #include "wave_launch.h"
 
@@ -22,6 +22,45 @@ bool wave_eligible(const alnr_batch_impl &B, uint32_t m, uint32_t n) {
   for (double v : B.matrix) mag = std::max(mag, v);
   if (B.mode == ALNR_LOCAL && mag * std::min(m, n) >= 16777216.0) return false;  // 24-bit value field
   return true;
+}
+
+// Tile pipeline (kernels_tile.cuh): 4 x 4 cells per lane and step, sentinel hand-off of the band rows.
+static int tile_run_pair(alnr_batch_impl &B, const Chunk &c, const DLayout &dl, const FillOut &fo) {
+  BandArgs a;
+  a.q = B.d_q.p + c.q0; a.t = B.d_t.p + c.t0;
+  a.n = c.n_max; a.m = c.m_max; a.V = B.V; a.matrix = B.d_mati.p;
+  a.del = (int)B.del; a.ext = (int)B.ext;
+  a.nbands = (a.m + 127) / 128;
+  const bool local = B.mode == ALNR_LOCAL;
+  const size_t npad = ((size_t)a.n + 3) / 4 * 4;
+  // scratch: [best (8 B)][corner][pad][rows nbands * npad][32 ints of slack for the first prefetch]
+  const size_t row_words = (size_t)a.nbands * npad + 32;
+  const size_t words = 4 + row_words;
+  if (B.d_band.n < words) ALNR_CUDA(B.d_band.alloc(words));
+  int *base = B.d_band.p;
+  a.best = reinterpret_cast<unsigned long long *>(base);
+  a.corner_out = base + 2;
+  a.prog = nullptr;
+  a.rows = base + 4;
+  a.D = B.Dp();
+  a.dcols = dl.ncols;
+  const size_t smem = (size_t)B.V * 32 * sizeof(int4) + 32 * sizeof(int);
+  int occ0 = 0, occ1 = 0, sms = 0, dev = 0;
+  ALNR_CUDA(cudaGetDevice(&dev));
+  ALNR_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  ALNR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ0, fill_tile_kernel<false>, 32, smem));
+  ALNR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ1, fill_tile_kernel<true>, 32, smem));
+  const unsigned resident = (unsigned)std::max(1, std::min(occ0, occ1)) * (unsigned)std::max(1, sms);
+  ALNR_CUDA(cudaMemsetAsync(a.best, 0, 16, B.stream));
+  if (a.nbands > 1)  // every word of the boundary rows starts as "not produced yet" (0x80808080)
+    ALNR_CUDA(cudaMemsetAsync(a.rows, 0x80, (size_t)(a.nbands - 1) * npad * sizeof(int), B.stream));
+  const unsigned grid = std::min<unsigned>(a.nbands, resident);  // every block must be resident
+  if (local) fill_tile_kernel<true><<<grid, 32, smem, B.stream>>>(a);
+  else fill_tile_kernel<false><<<grid, 32, smem, B.stream>>>(a);
+  ALNR_LAUNCHED();
+  band_finish_kernel<<<1, 1, 0, B.stream>>>(a, local ? 1 : 0, fo, c.wave_pair);
+  ALNR_LAUNCHED();
+  return ALNR_OK;
 }
 
 // Band pipeline (kernels_band.cuh): one persistent launch for the whole pair.
@@ -73,13 +112,16 @@ static int band_run_pair(alnr_batch_impl &B, const Chunk &c, const DLayout &dl, 
 // rows per lane of the band pipeline: thinner bands = more warps in flight (ALNR_BAND_R overrides)
 uint32_t wave_band_rows(uint32_t m) {
   static const int env = std::getenv("ALNR_BAND_R") ? std::atoi(std::getenv("ALNR_BAND_R")) : 0;
-  if (env == 2 || env == 4) return (uint32_t)env;
+  if (env == 2) return 2u;  // first-generation column kernel with 64-row bands
   (void)m;
   return 4u;  // measured: 128-row bands beat 64-row bands at 3 x 10^4 and at 10^5 (pipeline fill dominates)
 }
 
 int wave_run_pair(alnr_batch_impl &B, const Chunk &c, const DLayout &dl, const FillOut &fo) {
-  return band_run_pair(B, c, dl, fo);
+  // ALNR_BAND_COLUMN=1 / ALNR_BAND_R=2: the first-generation column-per-step kernel (A/B runs)
+  static const bool column = std::getenv("ALNR_BAND_COLUMN") != nullptr;
+  if (column || dl.rows_per_word != 4) return band_run_pair(B, c, dl, fo);
+  return tile_run_pair(B, c, dl, fo);
 }
 
 }  // namespace alnr
