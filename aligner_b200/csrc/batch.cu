@@ -343,6 +343,8 @@ int alnr_batch_impl::init(const alnr_params *p, const alnr_batch *b, bool want_m
     for (const Chunk &c : chunks)
       if (chunk_compact(c) && !score_only)
         mwords = std::max<uint64_t>(mwords, (uint64_t)((c.count + 31) / 32 * 32) * ((c.n_max + c.m_max + 1 + 15) / 16));
+      else if (c.wave && !score_only)  // long pair: move words, (cy, cx) per word, 3 tail words
+        mwords = std::max<uint64_t>(mwords, 2 * (uint64_t)((c.n_max + c.m_max + 1 + 15) / 16) + 8);
     ALNR_CUDA(d_moves.alloc(2 * mwords));  // move words, then the start cell of every word
   }
 
@@ -529,6 +531,12 @@ int alnr_batch_impl::phase2(size_t ci) {
     const uint32_t G = trace_expand_group(c.n_max, c.m_max);
     trace_expand_kernel<<<(c.count + G - 1) / G, kExpandThreads, trace_expand_smem(G, c.n_max, c.m_max), s2>>>(
         ta, d_moves.p, cxy, stride, G, c.n_max, c.m_max, nmw);
+  } else if (dl.blocked == 4 && c.count == 1 && !getenv("ALNR_TRACE_LOCKSTEP")) {
+    // long pair, 4 x 4 tiles: window walk that emits moves, then a parallel expansion
+    LongTrace lt{d_moves.p, d_moves.p + nmw, d_moves.p + 3 * (size_t)nmw};
+    trace_walk_window_kernel<<<1, 32, 0, s2>>>(ta, lt);
+    ALNR_LAUNCHED();
+    trace_expand_long_kernel<<<(nmw + 255) / 256, 256, 0, s2>>>(ta, lt);
   } else if (dl.blocked) {
     traceback_warp_kernel<<<c.count, 32, 0, s2>>>(ta);
   } else if ((size_t)nmw * kTraceBlock * 4 <= 44 * 1024 && to.freq == nullptr) {

@@ -85,7 +85,7 @@ struct DLayout {
     const uint32_t C = 16 / R;
     d.rows_per_word = R;
     d.nstrips = (m_max + R - 1) / R;
-    d.ncols = (n_max + C - 1) / C;
+    d.ncols = ((n_max + C - 1) / C + 3) / 4 * 4;  // multiple of 4: strips start on 16-byte boundaries
     d.contiguous = 1;
     d.planes = 0;
     d.skewed = 0;

@@ -29,7 +29,11 @@
 namespace alnr {
 
 constexpr int kTileSentinel = (int)0x80808080u;
-constexpr uint32_t kTileChunk = 8;  // steps per boundary chunk (8 steps x 4 columns = 32 values, one per lane)
+#ifndef ALNR_TILE_CHUNK
+#define ALNR_TILE_CHUNK 4
+#endif
+// steps per boundary chunk: a chunk's 4 * kTileChunk boundary values are fetched by its first lanes
+constexpr uint32_t kTileChunk = ALNR_TILE_CHUNK;
 
 struct TileLane {
   int h[4];         // H[yl0+1+r][c0]: the column left of the lane's next tile
@@ -50,8 +54,19 @@ struct TileLane {
 __device__ __forceinline__ uint32_t tile_load_q4(const uint8_t *p) {
   const uintptr_t a = reinterpret_cast<uintptr_t>(p);
   const uint32_t *w = reinterpret_cast<const uint32_t *>(a & ~(uintptr_t)3);
-  return __funnelshift_r(w[0], w[1], (uint32_t)(a & 3) * 8u);
+  return __funnelshift_r(__ldg(w), __ldg(w + 1), (uint32_t)(a & 3) * 8u);
 }
+
+__device__ __forceinline__ unsigned long long tile_now() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+#ifdef ALNR_TILE_DEBUG
+#define TILE_STAMP(k) do { if (lane == 0 && a.prog) reinterpret_cast<unsigned long long *>(a.prog)[(size_t)band * 8 + (k)] = tile_now(); } while (0)
+#else
+#define TILE_STAMP(k) do { } while (0)
+#endif
 
 __device__ __forceinline__ int tile_ld_row(const int *p) {
   int v;
@@ -60,10 +75,11 @@ __device__ __forceinline__ int tile_ld_row(const int *p) {
 }
 
 // One step: lane l computes tile ti = s - l (columns 4 ti + 1 .. 4 ti + 4) of its 4 rows.
-// EDGE = true adds what only ramp-up / drain / the last columns need: the ti < ntiles test, the
-// masking of query symbols past column n (those cells are computed and never read), the one cell
-// that pays `del` in global mode and the capture of H[m][n].
-template <bool LOCAL, bool EDGE>
+// EDGE = 1 (ramp-up: the first 32 steps of a band, which every band below waits for) adds the
+// ti < ntiles test and the one cell that pays `del` in global mode; EDGE = 2 (last columns and
+// drain) also masks the query symbols past column n (those cells are computed and never read)
+// and captures H[m][n].
+template <bool LOCAL, int EDGE>
 __device__ __forceinline__ void tile_step(TileLane &L, const int4 *sm_sc, const int *sm_top, uint32_t s, uint32_t lane,
                                           uint32_t yl0, uint32_t n, uint32_t m, uint32_t ntiles, int del, int ext,
                                           bool store_d, bool row_out) {
@@ -86,7 +102,7 @@ __device__ __forceinline__ void tile_step(TileLane &L, const int4 *sm_sc, const 
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
     uint32_t sym = (qw >> (8 * j)) & 0xffu;
-    if (EDGE && c0 + j >= n) sym = 0;
+    if (EDGE == 2 && c0 + j >= n) sym = 0;
     const int4 s4 = sm_sc[sym * 32 + lane];
     const int sc[4] = {s4.x, s4.y, s4.z, s4.w};
     int diag = j == 0 ? corner_in : up[j - 1];
@@ -106,7 +122,7 @@ __device__ __forceinline__ void tile_step(TileLane &L, const int4 *sm_sc, const 
       if (LOCAL) { hit |= mx >= L.best_v; v[r][j] = mx; }
     }
     L.bot[j] = hup;
-    if (EDGE && c0 + j + 1 == n) {
+    if (EDGE == 2 && c0 + j + 1 == n) {
 #pragma unroll
       for (int r = 0; r < 4; ++r)
         if (yl0 + r + 1 == m) { L.corner = L.h[r]; L.has_corner = true; }
@@ -176,6 +192,20 @@ __global__ void __launch_bounds__(32) fill_tile_kernel(BandArgs a) {
     L.dptr = a.D + (size_t)(yl0 / 4) * a.dcols;  // this lane's 4-row strip
     L.rowp = a.rows + (size_t)band * npad;
     const uint32_t steps = ntiles + 31;
+    // A band cannot start before the band above has finished its first chunk, i.e. ~39 steps per
+    // band after the launch.  All bands are resident from the start, so a waiting band must not
+    // take issue slots from the working band on its scheduler: sleep in 1 us quanta until band
+    // b - kTileWake has handed on its first tile (that happens >= kTileWake x 39 steps before this
+    // band's own turn), and only then poll the own boundary row tightly.
+    constexpr uint32_t kTileWake = 4;
+    TILE_STAMP(0);
+    if (band > kTileWake) {
+      const int *far = a.rows + (size_t)(band - kTileWake) * npad;
+      if (lane == 0)
+        while (tile_ld_row(far) == kTileSentinel) __nanosleep(1000);
+      __syncwarp();
+    }
+    TILE_STAMP(1);
     int pre = band ? tile_ld_row(top_row + lane) : 0;  // npad >= 4 and the buffer is padded by 32
 
     for (uint32_t s0 = 0; s0 < steps; s0 += kTileChunk) {
@@ -184,7 +214,7 @@ __global__ void __launch_bounds__(32) fill_tile_kernel(BandArgs a) {
         if (band) {
           // the producer's 16-byte stores land whole tiles; a lane that still sees the sentinel re-loads
           for (;;) {
-            const bool need = col < npad && pre == kTileSentinel;
+            const bool need = lane < 4 * kTileChunk && col < npad && pre == kTileSentinel;
             if (!__any_sync(0xffffffffu, need)) break;
             if (need) { __nanosleep(20); pre = tile_ld_row(top_row + col); }
           }
@@ -193,23 +223,31 @@ __global__ void __launch_bounds__(32) fill_tile_kernel(BandArgs a) {
           pre = (LOCAL || xx > n) ? 0 : ((xx == n) ? -(int)(n + 1) * del : -(int)xx * del);
         }
         __syncwarp();
-        sm_top[lane] = pre;
+        if (s0 == 0) TILE_STAMP(2);
+        if (s0 == 32) TILE_STAMP(3);
+        if (s0 == 64) TILE_STAMP(4);
+        if (lane < 4 * kTileChunk) sm_top[lane] = pre;
         __syncwarp();
         const uint32_t ncol = col + 4 * kTileChunk;
-        pre = (band && ncol < npad) ? tile_ld_row(top_row + ncol) : 0;  // prefetch the next chunk
+        pre = (band && lane < 4 * kTileChunk && ncol < npad) ? tile_ld_row(top_row + ncol) : 0;  // prefetch the next chunk
       }
-      // steady: every lane is inside [1, ntiles) for all steps and nobody touches column n
-      const bool steady = s0 >= 32 && 4 * (s0 + kTileChunk) < n;
-      if (steady) {
+      // steady (EDGE = 0): every lane is inside [1, ntiles) for all steps and nobody touches column n
+      const bool inner = 4 * (s0 + kTileChunk) < n;  // the chunk stays left of column n for every lane
+      if (inner && s0 >= 32) {
 #pragma unroll
         for (uint32_t j = 0; j < kTileChunk; ++j)
-          tile_step<LOCAL, false>(L, sm_sc, sm_top, s0 + j, lane, yl0, n, m, ntiles, del, ext, store_d, row_out);
+          tile_step<LOCAL, 0>(L, sm_sc, sm_top, s0 + j, lane, yl0, n, m, ntiles, del, ext, store_d, row_out);
+      } else if (inner) {
+#pragma unroll
+        for (uint32_t j = 0; j < kTileChunk; ++j)
+          tile_step<LOCAL, 1>(L, sm_sc, sm_top, s0 + j, lane, yl0, n, m, ntiles, del, ext, store_d, row_out);
       } else {
         const uint32_t jend = min(kTileChunk, steps - s0);
         for (uint32_t j = 0; j < jend; ++j)
-          tile_step<LOCAL, true>(L, sm_sc, sm_top, s0 + j, lane, yl0, n, m, ntiles, del, ext, store_d, row_out);
+          tile_step<LOCAL, 2>(L, sm_sc, sm_top, s0 + j, lane, yl0, n, m, ntiles, del, ext, store_d, row_out);
       }
     }
+    TILE_STAMP(5);
     if (last_band && L.has_corner) *a.corner_out = L.corner;
     __syncwarp();
   }

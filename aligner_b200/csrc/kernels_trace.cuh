@@ -543,6 +543,197 @@ static __global__ void __launch_bounds__(32) traceback_warp_kernel(TraceArgs a) 
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Two-phase traceback of ONE long pair through the "blocked" D layout with 4 x 4 tiles per word
+// (tile pipeline kernel).  The walk is one dependent chain of n + m steps; everything that is not
+// on that chain is moved off it:
+//   phase W (trace_walk_window_kernel, one warp): lane 0 walks inside a WINDOW of 32 strips x 64
+//     words (128 rows x 256 columns, 8 KB) held in shared memory and emits only 2-bit moves (16 per
+//     word) plus the cell at which every move word starts; no sequence loads, no alignment
+//     stores.  All 32 lanes fetch a window with 16-byte cp.async; while lane 0 walks, the window
+//     the path is predicted to enter next (straight up the diagonal, 16 words of slack to the
+//     right, 47 to the left) is already in flight into the second buffer.  A path that leaves a
+//     window elsewhere (long gap runs) gets a window loaded at its cell.
+//   phase E (trace_expand_long_kernel, one thread per move word): re-walks its 16 moves from the
+//     recorded cell and writes the two aligned strings, right-aligned in the pair's slot exactly
+//     as traceback_kernel does (seed pair first: simple/mod.rs:102-105, :213-216).
+// ---------------------------------------------------------------------------------------------
+constexpr uint32_t kWinStrips = 32, kWinWords = 64;
+
+struct LongTrace {
+  uint32_t *moves;  // [nmw] 2-bit moves, move i at bits 2 * (i % 16) of word i / 16
+  uint32_t *cell;   // [2 * nmw] (cy, cx) before the first move of every word
+  uint32_t *tail;   // [0] number of moves, [1] cy and [2] cx where the walk ended
+};
+
+__device__ __forceinline__ void win_cp16(uint32_t smem_addr, const void *g) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr), "l"(g) : "memory");
+}
+
+// window with bottom strip s_bot and rightmost word w_hi: strips s_bot - 31 .. s_bot (row r of the
+// buffer = strip s_bot - r), words w_lo .. w_lo + 63 with w_lo a multiple of 4 (ncols is one too)
+__device__ __forceinline__ uint32_t win_lo(uint32_t w_hi) {
+  const int lo = ((int)w_hi - (int)kWinWords + 1 + 3) & ~3;
+  return lo > 0 ? (uint32_t)lo : 0u;
+}
+
+__device__ __forceinline__ void win_fetch(uint32_t *buf, const uint32_t *D, const DLayout &dl, uint32_t s_bot,
+                                          uint32_t w_lo, uint32_t lane) {
+  const uint32_t piece = lane & 15, half = lane >> 4;
+  const uint32_t w = w_lo + 4 * piece;
+#pragma unroll 4
+  for (uint32_t r2 = 0; r2 < kWinStrips / 2; ++r2) {
+    const uint32_t r = 2 * r2 + half;
+    if (r <= s_bot && w < dl.ncols)
+      win_cp16((uint32_t)__cvta_generic_to_shared(buf + r * kWinWords + 4 * piece),
+               D + (uint64_t)(s_bot - r) * dl.ncols + w);
+  }
+  asm volatile("cp.async.commit_group;" ::: "memory");
+}
+
+static __global__ void __launch_bounds__(32) trace_walk_window_kernel(TraceArgs a, LongTrace lt) {
+  __shared__ __align__(16) uint32_t win[2][kWinStrips * kWinWords];
+  const uint32_t lane = threadIdx.x;
+  const uint32_t pair = a.cv.order ? a.cv.order[a.cv.first] : a.cv.first;
+  if (a.fo.status[pair] != 0) {
+    if (lane == 0) { lt.tail[0] = 0; lt.tail[1] = 0; lt.tail[2] = 0; }
+    return;
+  }
+  const bool glob = a.mode == 0;
+  uint32_t cy = a.fo.start[2 * (size_t)pair], cx = a.fo.start[2 * (size_t)pair + 1];
+  uint32_t cnt = 0, acc = 0;
+  int cur = 0;
+  if (lane == 0) { lt.cell[0] = cy; lt.cell[1] = cx; }
+  // current window: (s_bot, w_lo) in buffer `cur`; valid strips max(0, s_bot - 31) .. s_bot
+  uint32_t s_bot = 0, w_lo = 0;
+  bool have = false, done = false;
+  while (!done) {
+    const bool inside = cy && cx;
+    const uint32_t strip = inside ? (cy - 1) >> 2 : 0, wc = inside ? (cx - 1) >> 2 : 0;
+    if (inside && !have) {  // no usable window: fetch one at the current cell
+      s_bot = strip; w_lo = win_lo(wc);
+      win_fetch(win[cur], a.D, a.dl, s_bot, w_lo, lane);
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+      __syncwarp();
+      have = true;
+    }
+    // predicted next window: the path climbs the rest of this window along the diagonal
+    const uint32_t s_top = s_bot >= kWinStrips - 1 ? s_bot - (kWinStrips - 1) : 0;
+    bool pre = false;
+    uint32_t ns_bot = 0, nw_lo = 0, nw_hi = 0;
+    if (inside && s_top > 0) {
+      const uint32_t climb = strip - s_top + 1;
+      if (wc > climb) {
+        ns_bot = s_top - 1;
+        nw_hi = min(wc - climb + 16, a.dl.ncols - 1);
+        nw_lo = win_lo(nw_hi);
+        win_fetch(win[cur ^ 1], a.D, a.dl, ns_bot, nw_lo, lane);
+        pre = true;
+      }
+    }
+    if (lane == 0) {
+      const uint32_t *wb = win[cur];
+      // one move: append its 2 bits; a full word goes out together with the cell the next word starts at
+      auto put = [&](uint32_t d, uint32_t ny, uint32_t nx) {
+        acc |= d << (2 * (cnt & 15));
+        ++cnt;
+        if ((cnt & 15) == 0) {
+          lt.moves[(cnt >> 4) - 1] = acc; acc = 0;
+          lt.cell[2 * (cnt >> 4)] = ny; lt.cell[2 * (cnt >> 4) + 1] = nx;
+        }
+      };
+      for (;;) {
+        if (cy == 0 || cx == 0) {  // border: Beginning in local mode, a run to (0, 0) in global mode
+          if (glob) {              // simple/mod.rs:59-67
+            while (cx) { --cx; put(DIR_LEFT, cy, cx); }
+            while (cy) { --cy; put(DIR_TOP, cy, cx); }
+          }
+          done = true;
+          break;
+        }
+        const uint32_t st = (cy - 1) >> 2, ww = (cx - 1) >> 2;
+        if (st < s_top || ww < w_lo) break;  // left the window
+        const uint32_t w = wb[(s_bot - st) * kWinWords + (ww - w_lo)];
+        // walk inside the 4 x 4 tile on local coordinates; only (w >> sh) -> d -> (ly, lx) -> sh is a chain
+        int ly = (int)((cy - 1) & 3), lx = (int)((cx - 1) & 3);
+        const uint32_t y0 = st * 4 + 1, x0 = ww * 4 + 1;
+        bool begin = false;
+        do {
+          const uint32_t d = (w >> (8 * lx + 2 * ly)) & 3u;
+          if (d == DIR_BEGINNING) { begin = true; break; }
+          ly -= (d != DIR_LEFT);
+          lx -= (d != DIR_TOP);
+          put(d, y0 + ly, x0 + lx);
+        } while (ly >= 0 && lx >= 0);
+        cy = y0 + ly; cx = x0 + lx;
+        if (begin) { done = true; break; }
+      }
+    }
+    cy = __shfl_sync(0xffffffffu, cy, 0);
+    cx = __shfl_sync(0xffffffffu, cx, 0);
+    done = __shfl_sync(0xffffffffu, (int)done, 0) != 0;
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncwarp();
+    have = false;
+    if (!done && pre && cy && cx) {
+      const uint32_t st = (cy - 1) >> 2, ww = (cx - 1) >> 2;
+      const uint32_t ns_top = ns_bot >= kWinStrips - 1 ? ns_bot - (kWinStrips - 1) : 0;
+      if (st <= ns_bot && st >= ns_top && ww >= nw_lo && ww <= nw_hi) {
+        cur ^= 1; s_bot = ns_bot; w_lo = nw_lo; have = true;
+      }
+    }
+  }
+  if (lane == 0) {
+    if (cnt & 15) lt.moves[cnt >> 4] = acc;
+    lt.tail[0] = cnt; lt.tail[1] = cy; lt.tail[2] = cx;
+  }
+}
+
+static __global__ void __launch_bounds__(256) trace_expand_long_kernel(TraceArgs a, LongTrace lt) {
+  const uint32_t pair = a.cv.order ? a.cv.order[a.cv.first] : a.cv.first;
+  const uint32_t sp = a.cv.seq(pair);
+  const uint64_t qo = a.cv.q_off[sp], to = a.cv.t_off[sp];
+  const uint32_t n = (uint32_t)(a.cv.q_off[sp + 1] - qo);
+  const uint32_t m = (uint32_t)(a.cv.t_off[sp + 1] - to);
+  const uint64_t slot_end = qo + to + pair + n + m + 1;
+  const uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
+  if (a.fo.status[pair] != 0) {
+    if (gid == 0) {
+      if (a.to.aln_len) a.to.aln_len[pair] = 0;
+      if (a.to.aln_off) a.to.aln_off[pair] = slot_end;
+      if (a.to.coords) for (int k = 0; k < 4; ++k) a.to.coords[4 * (size_t)pair + k] = 0;
+    }
+    return;
+  }
+  const uint8_t *q = a.cv.q + qo, *t = a.cv.t + to;
+  const uint32_t cnt = lt.tail[0];
+  const uint32_t sy = a.fo.start[2 * (size_t)pair], sx = a.fo.start[2 * (size_t)pair + 1];
+  const bool wr = a.to.q_aln != nullptr && a.to.t_aln != nullptr;
+  if (gid == 0) {
+    if (wr) { a.to.q_aln[slot_end - 1] = q[sx - 1]; a.to.t_aln[slot_end - 1] = t[sy - 1]; }  // seed pair
+    if (a.to.aln_len) a.to.aln_len[pair] = cnt + 1;
+    if (a.to.aln_off) a.to.aln_off[pair] = slot_end - 1 - cnt;
+    if (a.to.coords) {
+      uint64_t *c = a.to.coords + 4 * (size_t)pair;
+      if (a.mode == 0) { c[0] = 1; c[1] = n; c[2] = 1; c[3] = m; }                          // simple/mod.rs:137
+      else { c[0] = lt.tail[2] + 1; c[1] = sx + 1; c[2] = lt.tail[1] + 1; c[3] = sy + 1; }  // :254-257
+    }
+  }
+  const uint32_t first = gid * 16;
+  if (first >= cnt || !wr) return;
+  uint32_t w = lt.moves[gid];
+  uint32_t cy = lt.cell[2 * gid], cx = lt.cell[2 * gid + 1];
+  const uint32_t k_end = min(16u, cnt - first);
+  uint64_t pos = slot_end - 2 - first;  // move i lands at slot_end - 2 - i
+  for (uint32_t k = 0; k < k_end; ++k, --pos, w >>= 2) {
+    const uint32_t d = w & 3u;
+    a.to.q_aln[pos] = d == DIR_TOP ? (uint8_t)kBlank : q[cx - 1];
+    a.to.t_aln[pos] = d == DIR_LEFT ? (uint8_t)kBlank : t[cy - 1];
+    cy -= (d != DIR_LEFT);
+    cx -= (d != DIR_TOP);
+  }
+}
+
 // Traceback of the matrix search (heur.cu): one WARP per item through the "skewed" D layout of the
 // warp fill kernel; only the coords and the frequency matrix of the alignment (alignment.rs:13-23)
 // are produced.  Every lane holds the same (cy, cx); before each stretch the 32 lanes fetch a

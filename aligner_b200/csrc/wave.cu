@@ -1,7 +1,9 @@
 // wave.cu — host side of the intra-pair wavefront path for one long pair: the band pipeline
 // kernel (kernels_band.cuh).
 #include <algorithm>
+#include <cstdio>
 #include <cstdlib>
+#include <vector>
 
 #include "kernels_tile.cuh"
 #include "strip_launch.h"
@@ -35,13 +37,21 @@ static int tile_run_pair(alnr_batch_impl &B, const Chunk &c, const DLayout &dl, 
   const size_t npad = ((size_t)a.n + 3) / 4 * 4;
   // scratch: [best (8 B)][corner][pad][rows nbands * npad][32 ints of slack for the first prefetch]
   const size_t row_words = (size_t)a.nbands * npad + 32;
-  const size_t words = 4 + row_words;
+#ifdef ALNR_TILE_DEBUG
+  const size_t dbg_words = (size_t)a.nbands * 16 + 4;
+#else
+  const size_t dbg_words = 0;
+#endif
+  const size_t words = 4 + row_words + dbg_words;
   if (B.d_band.n < words) ALNR_CUDA(B.d_band.alloc(words));
   int *base = B.d_band.p;
   a.best = reinterpret_cast<unsigned long long *>(base);
   a.corner_out = base + 2;
   a.prog = nullptr;
   a.rows = base + 4;
+#ifdef ALNR_TILE_DEBUG
+  a.prog = reinterpret_cast<uint32_t *>(base + 4 + (row_words + 3) / 4 * 4);
+#endif
   a.D = B.Dp();
   a.dcols = dl.ncols;
   const size_t smem = (size_t)B.V * 32 * sizeof(int4) + 32 * sizeof(int);
@@ -60,6 +70,20 @@ static int tile_run_pair(alnr_batch_impl &B, const Chunk &c, const DLayout &dl, 
   ALNR_LAUNCHED();
   band_finish_kernel<<<1, 1, 0, B.stream>>>(a, local ? 1 : 0, fo, c.wave_pair);
   ALNR_LAUNCHED();
+#ifdef ALNR_TILE_DEBUG
+  {  // per-band time stamps (ns since the first band's entry): entry, woken, first chunk, step 32, step 64, end
+    std::vector<unsigned long long> ts((size_t)a.nbands * 8);
+    cudaStreamSynchronize(B.stream);
+    cudaMemcpy(ts.data(), a.prog, ts.size() * 8, cudaMemcpyDeviceToHost);
+    const unsigned long long t0 = ts[0];
+    for (uint32_t b = 0; b < a.nbands; b += (a.nbands > 40 ? a.nbands / 20 : 1)) {
+      fprintf(stderr, "band %4u:", b);
+      for (int k = 0; k < 6; ++k) fprintf(stderr, " %10.1f", (double)(ts[(size_t)b * 8 + k] - t0) / 1000.0);
+      if (b) fprintf(stderr, "  | first chunk after the band above: %.1f us", (double)(ts[(size_t)b * 8 + 2] - ts[(size_t)(b - 1) * 8 + 2]) / 1000.0);
+      fprintf(stderr, "\n");
+    }
+  }
+#endif
   return ALNR_OK;
 }
 
