@@ -654,17 +654,35 @@ static __global__ void __launch_bounds__(32) trace_walk_window_kernel(TraceArgs 
         const uint32_t st = (cy - 1) >> 2, ww = (cx - 1) >> 2;
         if (st < s_top || ww < w_lo) break;  // left the window
         const uint32_t w = wb[(s_bot - st) * kWinWords + (ww - w_lo)];
-        // walk inside the 4 x 4 tile on local coordinates; only (w >> sh) -> d -> (ly, lx) -> sh is a chain
-        int ly = (int)((cy - 1) & 3), lx = (int)((cx - 1) & 3);
+        // walk inside the 4 x 4 tile on local coordinates: only (w >> sh) -> d -> (ly, lx) -> sh is a
+        // chain; the tile's <= 7 moves are collected in `tm` and appended to the move string once
+        const int ly0 = (int)((cy - 1) & 3), lx0 = (int)((cx - 1) & 3);
+        int ly = ly0, lx = lx0;
         const uint32_t y0 = st * 4 + 1, x0 = ww * 4 + 1;
         bool begin = false;
+        uint32_t tm = 0, tc = 0;
         do {
           const uint32_t d = (w >> (8 * lx + 2 * ly)) & 3u;
-          if (d == DIR_BEGINNING) { begin = true; break; }
+          if (d == DIR_BEGINNING) { begin = true; break; }  // local mode only (enums.rs:37)
           ly -= (d != DIR_LEFT);
           lx -= (d != DIR_TOP);
-          put(d, y0 + ly, x0 + lx);
+          tm |= d << (2 * tc);
+          ++tc;
         } while (ly >= 0 && lx >= 0);
+        const uint32_t fill = cnt & 15;
+        const unsigned long long wide = (unsigned long long)acc | ((unsigned long long)tm << (2 * fill));
+        cnt += tc;
+        acc = (uint32_t)wide;
+        if (fill + tc >= 16) {  // a move word is complete: it goes out with the cell the next word starts at
+          int py = ly0, px = lx0;
+          for (uint32_t k = 0, mm = tm; k < 16 - fill; ++k, mm >>= 2) {
+            py -= ((mm & 3u) != DIR_LEFT);
+            px -= ((mm & 3u) != DIR_TOP);
+          }
+          lt.moves[(cnt >> 4) - 1] = acc;
+          lt.cell[2 * (cnt >> 4)] = y0 + py; lt.cell[2 * (cnt >> 4) + 1] = x0 + px;
+          acc = (uint32_t)(wide >> 32);
+        }
         cy = y0 + ly; cx = x0 + lx;
         if (begin) { done = true; break; }
       }

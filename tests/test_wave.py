@@ -57,3 +57,45 @@ def test_wavefront_protein_matrix():
     r = ab.SimpleGlobalAligner.from_seqs(q, t).perform_alignment(11, 1, M, want_matrices=False)
     assert r.corner_score == ref["corner"]
     assert (r.alignment.query == ref["q_aln"]).all() and (r.alignment.target == ref["t_aln"]).all()
+
+
+@pytest.mark.parametrize("m,n", [(300, 5000), (5000, 300), (40000, 33), (33, 40000), (1500, 1501), (4097, 1023)])
+@pytest.mark.parametrize("mode,d", [("global", 8), ("local", 6)])
+def test_tile_pipeline_extreme_shapes(m, n, mode, d):
+    """Shapes that stress the 4 x 4 tile pipeline and the window traceback: fewer tile columns than
+    lanes, a single band, n not a multiple of 4, unrelated sequences (long gap runs leave the
+    predicted window, global paths end on the border rows)."""
+    rng = np.random.default_rng(m * 7 + n)
+    q = rng.integers(0, 4, n).astype(np.uint8)
+    t = rng.integers(0, 4, m).astype(np.uint8)
+    if min(m, n) > 1000:  # a related stretch so that local mode has a long path
+        k = min(m, n) // 2
+        t[m - k:] = q[n - k:]
+        t[m - k + 7] ^= 1
+    M = ab.dna_matrix(5, -4)
+    ref = O.align_pair(mode, q, t, float(d), float(d), M, lean=True)
+    cls = ab.SimpleGlobalAligner if mode == "global" else ab.SimpleLocalAligner
+    if ref["status"] != 0:
+        with pytest.raises(Exception):
+            cls.from_seqs(q, t, symbols=ab.DNA).perform_alignment(d, d, M, want_matrices=False)
+        return
+    r = cls.from_seqs(q, t, symbols=ab.DNA).perform_alignment(d, d, M, want_matrices=False)
+    assert r.numeric == N.NUM_I32
+    assert r.alignment.f == ref["f"] and r.corner_score == ref["corner"]
+    assert r.alignment.coords == ref["coords"]
+    assert (r.alignment.query == ref["q_aln"]).all() and (r.alignment.target == ref["t_aln"]).all()
+
+
+def test_tile_pipeline_equals_column_kernel_and_lockstep_traceback(monkeypatch):
+    """The first-generation kernels stay selectable; all three paths give the same alignment."""
+    import subprocess, sys, os, json
+    code = ("import sys, json, hashlib; sys.path.insert(0, %r); import aligner_b200 as ab; "
+            "from aligner_b200 import workloads as W; q, t = W.dna_long_pair(6000, seed=11); "
+            "r = ab.SimpleGlobalAligner.from_seqs(q, t, symbols=ab.DNA).perform_alignment(8, 8, ab.dna_matrix(5, -4), want_matrices=False); "
+            "print(json.dumps([r.corner_score, hashlib.sha256(r.alignment.query.tobytes() + r.alignment.target.tobytes()).hexdigest()]))"
+            % os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    outs = []
+    for extra in ({}, {"ALNR_BAND_COLUMN": "1"}, {"ALNR_TRACE_LOCKSTEP": "1"}):
+        env = dict(os.environ, **extra)
+        outs.append(json.loads(subprocess.check_output([sys.executable, "-c", code], env=env).decode().strip().splitlines()[-1]))
+    assert outs[0] == outs[1] == outs[2]
