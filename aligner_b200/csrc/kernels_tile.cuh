@@ -30,10 +30,14 @@ namespace alnr {
 
 constexpr int kTileSentinel = (int)0x80808080u;
 #ifndef ALNR_TILE_CHUNK
-#define ALNR_TILE_CHUNK 4
+#define ALNR_TILE_CHUNK 8
 #endif
 // steps per boundary chunk: a chunk's 4 * kTileChunk boundary values are fetched by its first lanes
 constexpr uint32_t kTileChunk = ALNR_TILE_CHUNK;
+#ifndef ALNR_TILE_PREFETCH_AT
+#define ALNR_TILE_PREFETCH_AT (ALNR_TILE_CHUNK * 5 / 8)
+#endif
+constexpr uint32_t kTilePrefetchAt = ALNR_TILE_PREFETCH_AT;  // step of a chunk at which the next chunk is requested
 
 struct TileLane {
   int h[4];         // H[yl0+1+r][c0]: the column left of the lane's next tile
@@ -228,21 +232,30 @@ __global__ void __launch_bounds__(32) fill_tile_kernel(BandArgs a) {
         if (s0 == 64) TILE_STAMP(4);
         if (lane < 4 * kTileChunk) sm_top[lane] = pre;
         __syncwarp();
-        const uint32_t ncol = col + 4 * kTileChunk;
-        pre = (band && lane < 4 * kTileChunk && ncol < npad) ? tile_ld_row(top_row + ncol) : 0;  // prefetch the next chunk
       }
+      // The next chunk's boundary values are requested in the MIDDLE of this chunk: a band that
+      // follows its producer at the minimum distance finds them only if the load is issued after
+      // the producer has stored them, i.e. as late as the L2 round trip allows (kTilePrefetchAt).
+      const uint32_t ncol = col + 4 * kTileChunk;
+      const int *pf = (band && lane < 4 * kTileChunk && ncol < npad) ? top_row + ncol : nullptr;
+      pre = 0;
       // steady (EDGE = 0): every lane is inside [1, ntiles) for all steps and nobody touches column n
       const bool inner = 4 * (s0 + kTileChunk) < n;  // the chunk stays left of column n for every lane
       if (inner && s0 >= 32) {
 #pragma unroll
-        for (uint32_t j = 0; j < kTileChunk; ++j)
+        for (uint32_t j = 0; j < kTileChunk; ++j) {
+          if (j == kTilePrefetchAt && pf) pre = tile_ld_row(pf);
           tile_step<LOCAL, 0>(L, sm_sc, sm_top, s0 + j, lane, yl0, n, m, ntiles, del, ext, store_d, row_out);
+        }
       } else if (inner) {
 #pragma unroll
-        for (uint32_t j = 0; j < kTileChunk; ++j)
+        for (uint32_t j = 0; j < kTileChunk; ++j) {
+          if (j == kTilePrefetchAt && pf) pre = tile_ld_row(pf);
           tile_step<LOCAL, 1>(L, sm_sc, sm_top, s0 + j, lane, yl0, n, m, ntiles, del, ext, store_d, row_out);
+        }
       } else {
         const uint32_t jend = min(kTileChunk, steps - s0);
+        if (pf) pre = tile_ld_row(pf);
         for (uint32_t j = 0; j < jend; ++j)
           tile_step<LOCAL, 2>(L, sm_sc, sm_top, s0 + j, lane, yl0, n, m, ntiles, del, ext, store_d, row_out);
       }
