@@ -55,6 +55,16 @@ __device__ __forceinline__ double wmax3(double a, double b, double c) {
 }
 constexpr double kWarpFiniteBound = 1e290;
 
+// "this cell may reach the running maximum": a conservative test that only triggers the ordered
+// rescan (which compares exactly).  FP64: the running maximum is never negative, so mx >= best
+// implies hi32(mx) >= hi32(best) as signed integers (a negative mx has a negative high word) — one
+// ISETP per cell.  Written as `mx >= best`, nvcc turns the OR over a lane's rows into an fmax chain
+// (DSETP.MAX + 2 selects + NaN fix-up + moves, ~8 instructions per cell).
+__device__ __forceinline__ bool may_hit(int mx, int best) { return mx >= best; }
+__device__ __forceinline__ bool may_hit(double mx, double best) {
+  return __double2hiint(mx) >= __double2hiint(best);
+}
+
 // MODE: 0 global; 1 local with del == ext (static penalty, FP64 only: saves two selects per cell in
 // the matrix search); 2 local, any del / ext (a.stateful says whether the speculation is needed).
 // The INT32 instantiation of MODE 1 gave wrong scores on B200 (nvcc 12.9, cause not found; caught by
@@ -237,7 +247,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) fill_warp_kernel(WarpArgs
             diag = h[r];
             h[r] = mx;
             hup = mx;
-            if (LOCAL) hit |= mx >= best;
+            if (LOCAL) hit |= may_hit(mx, best);
             if (MATS) {
               const uint32_t y = yb + r + 1;
               if (y <= m) { a.H_out[y * W + x] = (double)mx; a.D_out[y * W + x] = (uint8_t)d; }
