@@ -152,6 +152,29 @@ def test_config4_full_size_global_path():
     assert M[lt[both].astype(np.intp), lq[both].astype(np.intp)].sum() - 8.0 * float((~both).sum()) == loc.alignment.f
 
 
+def test_tile_pipeline_more_bands_than_resident_warps():
+    """600 000 target rows = 4688 bands, more than the grid holds at once (148 SMs x 28 blocks):
+    blocks take a second band after their first.  Checked through the size-independent properties
+    (the path covers both sequences, re-scores to the corner score) and against the score-only call."""
+    rng = np.random.default_rng(77)
+    m, n = 600000, 1800
+    t = rng.integers(0, 4, m).astype(np.uint8)
+    q = t[rng.integers(0, m - 2 * n)::333][:n].copy()
+    M = ab.dna_matrix(5, -4)
+    r = ab.SimpleGlobalAligner.from_seqs(q, t, symbols=ab.DNA).perform_alignment(8, 8, M, want_matrices=False)
+    qa, ta = r.alignment.query, r.alignment.target
+    assert (qa[qa != BLANK] == np.append(q, q[-1])).all()
+    assert (ta[ta != BLANK] == np.append(t, t[-1])).all()
+    bq, bt = qa[:-1], ta[:-1]
+    both = (bq != BLANK) & (bt != BLANK)
+    # cell (1, 1) pays del == ext here, and the corner rows use -(k+1)*del (simple/mod.rs:59-70): with
+    # del == ext a path that never runs along row 0 / column 0 to the corner re-scores exactly
+    s = M[bt[both].astype(np.intp), bq[both].astype(np.intp)].sum() - 8.0 * float((~both).sum())
+    sc = ab.score_batch(N.GLOBAL, ab.PackedPairs.from_lists([q], [t]), M, 8, 8)
+    assert sc.corner[0] == r.corner_score
+    assert s == r.corner_score or s - 8.0 == r.corner_score  # -(m+1)*del corner quirk when the path ends on column 0
+
+
 def test_config5_full_size_fitness_is_the_blocked_sum():
     P, K = 2000, 100
     pairs = W.protein_pairs(0, P, 270, 330)
