@@ -534,7 +534,15 @@ int alnr_batch_impl::phase2(size_t ci) {
   } else if (dl.blocked == 4 && c.count == 1 && !getenv("ALNR_TRACE_LOCKSTEP")) {
     // long pair, 4 x 4 tiles: window walk that emits moves, then a parallel expansion
     LongTrace lt{d_moves.p, d_moves.p + nmw, d_moves.p + 3 * (size_t)nmw};
-    trace_walk_window_kernel<<<1, 32, 0, s2>>>(ta, lt);
+    // ALNR_TRACE_SEQ=1: the one-lane window walk (it records the cells itself; A/B runs)
+    static const bool seq_walk = getenv("ALNR_TRACE_SEQ") != nullptr;
+    if (seq_walk) {
+      trace_walk_window_kernel<<<1, 32, 0, s2>>>(ta, lt);
+    } else {
+      trace_walk_coop_kernel<<<1, 32, 0, s2>>>(ta, lt);
+      ALNR_LAUNCHED();
+      trace_cells_kernel<<<1, 1024, 0, s2>>>(ta, lt);
+    }
     ALNR_LAUNCHED();
     trace_expand_long_kernel<<<(nmw + 255) / 256, 256, 0, s2>>>(ta, lt);
   } else if (dl.blocked) {

@@ -707,6 +707,260 @@ static __global__ void __launch_bounds__(32) trace_walk_window_kernel(TraceArgs 
   }
 }
 
+// Cooperative window walk: the same windows and the same move string as trace_walk_window_kernel,
+// but the 32 strips of a window are walked by the 32 lanes AT ONCE.  Lane l takes strip s_bot - l
+// and starts on the bottom row of its strip at a GUESSED column — where the path would arrive if
+// it kept climbing the diagonal from the last known cell.  The guesses are then stitched: lane l's
+// walk is the real path iff lane l-1's walk is and leaves its strip at the column lane l started
+// from.  The first lane whose guess was wrong gets the true column, the lanes above it are
+// re-guessed from there, and only those walk again; an indel costs one more round instead of
+// making the walk sequential.  (A round confirms at least one more strip, so the worst case is
+// the sequential walk.)  A strip walk stops after 32 moves, at Beginning, or at the window's left
+// edge; the chain then ends at that cell and the outer loop fetches a window there.
+// Moves only: the start cells of the move words come from trace_cells_kernel.
+constexpr uint32_t kStripMoves = 32;  // longest walk of a strip entered at a known cell
+constexpr uint32_t kGuessMoves = 8;   // longest walk from a guessed cell (it is repeated in full once the cell is confirmed)
+
+static __global__ void __launch_bounds__(32) trace_walk_coop_kernel(TraceArgs a, LongTrace lt) {
+  __shared__ __align__(16) uint32_t win[2][kWinStrips * kWinWords];
+  __shared__ uint32_t stage[72];  // move bits being appended; stage[0] starts as the open move word
+  const uint32_t lane = threadIdx.x;
+  const uint32_t pair = a.cv.order ? a.cv.order[a.cv.first] : a.cv.first;
+  if (a.fo.status[pair] != 0) {
+    if (lane == 0) { lt.tail[0] = 0; lt.tail[1] = 0; lt.tail[2] = 0; }
+    return;
+  }
+  const bool glob = a.mode == 0;
+  uint32_t cy = a.fo.start[2 * (size_t)pair], cx = a.fo.start[2 * (size_t)pair + 1];
+  uint32_t cnt = 0;
+  int cur = 0;
+  for (uint32_t i = lane; i < 72; i += 32) stage[i] = 0;
+  __syncwarp();
+  uint32_t s_bot = 0, w_lo = 0, seq_left = 0;
+  uint32_t ns_bot = 0, nw_lo = 0, nw_hi = 0;  // the prefetched window (pf_have)
+  bool have = false, done = false, pf_have = false;
+  while (!done) {
+    const bool inside = cy && cx;
+    if (!inside) {  // border: Beginning in local mode, a run to (0, 0) in global mode (simple/mod.rs:59-67)
+      if (lane == 0 && glob) {
+        uint32_t acc = stage[0];
+        auto put = [&](uint32_t d) {
+          acc |= d << (2 * (cnt & 15));
+          ++cnt;
+          if ((cnt & 15) == 0) { lt.moves[(cnt >> 4) - 1] = acc; acc = 0; }
+        };
+        while (cx) { --cx; put(DIR_LEFT); }
+        while (cy) { --cy; put(DIR_TOP); }
+        stage[0] = acc;
+      }
+      cnt = __shfl_sync(0xffffffffu, cnt, 0);
+      cy = __shfl_sync(0xffffffffu, cy, 0);
+      cx = __shfl_sync(0xffffffffu, cx, 0);
+      __syncwarp();
+      break;
+    }
+    const uint32_t strip = (cy - 1) >> 2, wc = (cx - 1) >> 2;
+    if (!have) {  // no usable window: fetch one at the current cell
+      s_bot = strip; w_lo = win_lo(wc);
+      win_fetch(win[cur], a.D, a.dl, s_bot, w_lo, lane);
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+      __syncwarp();
+      have = true;
+    }
+    const uint32_t s_top = s_bot >= kWinStrips - 1 ? s_bot - (kWinStrips - 1) : 0;
+    // predicted next window: the path climbs the rest of this window along the diagonal
+    // (kept across iterations that stay in the same window)
+    if (!pf_have && s_top > 0) {
+      const uint32_t climb = strip - s_top + 1;
+      if (wc > climb) {
+        ns_bot = s_top - 1;
+        nw_hi = min(wc - climb + 16, a.dl.ncols - 1);
+        nw_lo = win_lo(nw_hi);
+        win_fetch(win[cur ^ 1], a.D, a.dl, ns_bot, nw_lo, lane);
+        pf_have = true;
+      }
+    }
+    // ---- the window's strips, one per lane -------------------------------------------------
+    const uint32_t *wb = win[cur];
+    const uint32_t lmax = strip - s_top;          // lanes 0 .. lmax have a strip (strip, not s_bot: the
+    const bool mine = lane <= lmax;               //  path may enter a prefetched window below its top)
+    const uint32_t my_strip = strip - (mine ? lane : 0);
+    const uint32_t ybase = my_strip * 4;          // the walk of this lane ends when y == ybase
+    uint32_t ey = lane == 0 ? cy : ybase + 4;     // entry cell of the lane
+    uint32_t ex = lane == 0 ? cx : (cx > cy - ey ? cx - (cy - ey) : 0u);
+    uint32_t confirmed = 0;                       // lanes <= confirmed start from the true cell
+    bool redo = true;                             // this lane has to walk (again)
+    unsigned long long mv = 0;
+    // st: 0 left the strip at the top, 1 Beginning, 2 window edge / 32 moves, 3 a guessed walk cut short
+    uint32_t k = 0, oy = 0, ox = 0, st = 0;
+    uint32_t c_end = 0, rounds = 0;
+    if (seq_left) {  // speculation kept failing (unrelated sequences): lane 0 walks this window alone
+      --seq_left;
+      if (lane == 0) {
+        uint32_t acc = stage[0];
+        uint32_t y = cy, x = cx;
+        st = 0;
+        for (;;) {
+          if (y == 0 || x == 0) break;  // the border run is the outer loop's
+          const uint32_t sy = (y - 1) >> 2, ww = (x - 1) >> 2;
+          if (sy < s_top || ww < w_lo) break;
+          const uint32_t w = wb[(s_bot - sy) * kWinWords + (ww - w_lo)];
+          int ly = (int)((y - 1) & 3), lx = (int)((x - 1) & 3);
+          bool begin = false;
+          do {
+            const uint32_t d = (w >> (8 * lx + 2 * ly)) & 3u;
+            if (d == DIR_BEGINNING) { begin = true; break; }
+            ly -= (d != DIR_LEFT);
+            lx -= (d != DIR_TOP);
+            acc |= d << (2 * (cnt & 15));
+            ++cnt;
+            if ((cnt & 15) == 0) { lt.moves[(cnt >> 4) - 1] = acc; acc = 0; }
+          } while (ly >= 0 && lx >= 0);
+          y = sy * 4 + 1 + ly; x = ww * 4 + 1 + lx;
+          if (begin) { st = 1; break; }
+        }
+        stage[0] = acc;
+        oy = y; ox = x;
+      }
+      cnt = __shfl_sync(0xffffffffu, cnt, 0);
+      cy = __shfl_sync(0xffffffffu, oy, 0);
+      cx = __shfl_sync(0xffffffffu, ox, 0);
+      done = __shfl_sync(0xffffffffu, st, 0) == 1 || (!glob && (cy == 0 || cx == 0));
+    } else {
+    for (;;) {
+      ++rounds;
+      if (mine && redo) {
+        uint32_t y = ey, x = ex;
+        mv = 0; k = 0;
+        const uint32_t cap = lane <= confirmed ? kStripMoves : kGuessMoves;
+        for (;;) {
+          uint32_t d;
+          if (x == 0) {
+            if (!glob) { st = 1; break; }
+            d = DIR_TOP;
+          } else {
+            const uint32_t ww = (x - 1) >> 2;
+            if (ww < w_lo) { st = 2; break; }
+            const uint32_t w = wb[(s_bot - my_strip) * kWinWords + (ww - w_lo)];
+            d = (w >> (8 * ((x - 1) & 3) + 2 * ((y - 1) & 3))) & 3u;
+            if (d == DIR_BEGINNING) { st = 1; break; }
+          }
+          if (k == cap) { st = cap == kStripMoves ? 2 : 3; break; }
+          mv |= (unsigned long long)d << (2 * k);
+          ++k;
+          y -= (d != DIR_LEFT);
+          x -= (d != DIR_TOP);
+          if (y == ybase) { st = 0; break; }
+        }
+        oy = y; ox = x;
+      }
+      __syncwarp();
+      // stitch: lane l is on the path iff lane l-1 is, left its strip at the top, and did so at lane l's entry column
+      const uint32_t pox = __shfl_up_sync(0xffffffffu, ox, 1), pst = __shfl_up_sync(0xffffffffu, st, 1);
+      const bool bad = mine && lane > confirmed && (pst != 0 || pox != ex || st == 3);
+      const uint32_t badmask = __ballot_sync(0xffffffffu, bad);
+      const uint32_t first_bad = badmask ? (uint32_t)__ffs(badmask) - 1 : lmax + 1;
+      confirmed = first_bad - 1;
+      const uint32_t cst = __shfl_sync(0xffffffffu, st, confirmed);
+      if (first_bad > lmax || cst != 0) {
+        c_end = confirmed;
+        if (cst == 2 && confirmed < 2) seq_left = 32;  // a gap run longer than a strip walk: no diagonal to guess along
+        break;
+      }
+      if (rounds > 8) {  // one strip per round: the guesses are not paying (unrelated sequences) — lane 0
+        c_end = confirmed; seq_left = 32; break;  // walks the rest of this window and the next 31 alone
+      }
+      // lane first_bad starts from the true column, the lanes above it from the diagonal through it
+      const uint32_t tx = __shfl_sync(0xffffffffu, ox, confirmed), ty = __shfl_sync(0xffffffffu, oy, confirmed);
+      redo = mine && lane >= first_bad;
+      if (redo) ex = tx > ty - ey ? tx - (ty - ey) : 0u;
+      confirmed = first_bad;
+    }
+    // ---- append the moves of lanes 0 .. c_end ----------------------------------------------
+    {
+      const uint32_t kk = (mine && lane <= c_end) ? k : 0u;
+      uint32_t incl = kk;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+        if ((int)lane >= o) incl += v;
+      }
+      const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+      if (kk) {
+        const uint32_t bitpos = 2 * ((cnt & 15) + incl - kk);
+        const uint32_t wi = bitpos >> 5, sh = bitpos & 31;
+        const uint32_t lo = (uint32_t)mv, hi = (uint32_t)(mv >> 32);
+        atomicOr(&stage[wi], lo << sh);
+        atomicOr(&stage[wi + 1], sh ? ((lo >> (32 - sh)) | (hi << sh)) : hi);
+        if (sh) atomicOr(&stage[wi + 2], hi >> (32 - sh));
+      }
+      __syncwarp();
+      const uint32_t full = ((cnt & 15) + total) >> 4;
+      for (uint32_t i = lane; i < full; i += 32) lt.moves[(cnt >> 4) + i] = stage[i];
+      const uint32_t open = stage[full];
+      __syncwarp();
+      for (uint32_t i = lane; i < 72; i += 32) stage[i] = 0;
+      __syncwarp();
+      if (lane == 0) stage[0] = open;
+      __syncwarp();
+      cnt += total;
+    }
+    cy = __shfl_sync(0xffffffffu, oy, c_end);
+    cx = __shfl_sync(0xffffffffu, ox, c_end);
+    done = __shfl_sync(0xffffffffu, st, c_end) == 1;
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncwarp();
+    have = false;
+    if (!done && cy && cx) {
+      const uint32_t s2 = (cy - 1) >> 2, w2 = (cx - 1) >> 2;
+      const uint32_t ns_top = ns_bot >= kWinStrips - 1 ? ns_bot - (kWinStrips - 1) : 0;
+      if (s2 >= s_top && s2 <= s_bot && w2 >= w_lo) {
+        have = true;  // a walk cut short (32 moves, speculation given up) continues in the same window
+      } else if (pf_have && s2 <= ns_bot && s2 >= ns_top && w2 >= nw_lo && w2 <= nw_hi) {
+        cur ^= 1; s_bot = ns_bot; w_lo = nw_lo; have = true; pf_have = false;
+      }
+    }
+    if (!have) pf_have = false;
+  }
+  if (lane == 0) {
+    if (cnt & 15) lt.moves[cnt >> 4] = stage[0];
+    lt.tail[0] = cnt; lt.tail[1] = cy; lt.tail[2] = cx;
+  }
+}
+
+// Start cell of every 16-move word by a prefix sum over the move string (one block): a word with
+// L Left and G Diagonal moves among its c moves climbs c - L rows and G + L columns.
+static __global__ void __launch_bounds__(1024) trace_cells_kernel(TraceArgs a, LongTrace lt) {
+  __shared__ uint32_t sy[1024], sx[1024];
+  const uint32_t pair = a.cv.order ? a.cv.order[a.cv.first] : a.cv.first;
+  if (a.fo.status[pair] != 0) return;
+  const uint32_t cnt = lt.tail[0], nw = (cnt + 15) >> 4;
+  const uint32_t per = (nw + 1023) / 1024, w0 = threadIdx.x * per, w1 = min(nw, w0 + per);
+  auto climb = [&](uint32_t i, uint32_t &dy, uint32_t &dx) {
+    const uint32_t w = lt.moves[i], c = min(16u, cnt - 16 * i);
+    const uint32_t L = __popc(w & 0x55555555u), G = __popc((w >> 1) & 0x55555555u);
+    dy = c - L; dx = G + L;
+  };
+  uint32_t ty = 0, tx = 0;
+  for (uint32_t i = w0; i < w1; ++i) { uint32_t dy, dx; climb(i, dy, dx); ty += dy; tx += dx; }
+  sy[threadIdx.x] = ty; sx[threadIdx.x] = tx;
+  __syncthreads();
+  for (uint32_t o = 1; o < 1024; o <<= 1) {
+    const uint32_t vy = threadIdx.x >= o ? sy[threadIdx.x - o] : 0, vx = threadIdx.x >= o ? sx[threadIdx.x - o] : 0;
+    __syncthreads();
+    sy[threadIdx.x] += vy; sx[threadIdx.x] += vx;
+    __syncthreads();
+  }
+  uint32_t cy = a.fo.start[2 * (size_t)pair] - (sy[threadIdx.x] - ty);
+  uint32_t cx = a.fo.start[2 * (size_t)pair + 1] - (sx[threadIdx.x] - tx);
+  for (uint32_t i = w0; i < w1; ++i) {
+    lt.cell[2 * i] = cy; lt.cell[2 * i + 1] = cx;
+    uint32_t dy, dx; climb(i, dy, dx);
+    cy -= dy; cx -= dx;
+  }
+}
+
 static __global__ void __launch_bounds__(256) trace_expand_long_kernel(TraceArgs a, LongTrace lt) {
   const uint32_t pair = a.cv.order ? a.cv.order[a.cv.first] : a.cv.first;
   const uint32_t sp = a.cv.seq(pair);
