@@ -36,11 +36,11 @@ struct WarpArgs {
   uint8_t *D_out;
 };
 
-// Rows per lane for targets of up to m_max rows: the smallest even R <= 16 with 32 * R >= m_max
-// (one band), else 16 (several bands).
+// Rows per lane for targets of up to m_max rows: the smallest R in 2..16 with 32 * R >= m_max
+// (one band, as few idle rows as possible: 330-row targets take R = 11, 352 rows), else 16
+// (several bands).
 inline uint32_t warp_pick_rows(uint32_t m_max) {
-  uint32_t r = (m_max + 31) / 32;
-  r = (r + 1) / 2 * 2;
+  const uint32_t r = (m_max + 31) / 32;
   return r < 2 ? 2 : (r > 16 ? 16 : r);
 }
 

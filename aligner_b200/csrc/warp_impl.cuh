@@ -45,8 +45,9 @@ static int warp_launch_any(cudaStream_t stream, const WarpArgs<T> &a, bool local
     }                                                                             \
     return warp_launch_one<T, RR, 2, false>(stream, a);
   switch (a.dl.rows_per_word) {
-    ALNR_WARP_CASE(2) ALNR_WARP_CASE(4) ALNR_WARP_CASE(6) ALNR_WARP_CASE(8)
-    ALNR_WARP_CASE(10) ALNR_WARP_CASE(12) ALNR_WARP_CASE(14) ALNR_WARP_CASE(16)
+    ALNR_WARP_CASE(2) ALNR_WARP_CASE(3) ALNR_WARP_CASE(4) ALNR_WARP_CASE(5) ALNR_WARP_CASE(6)
+    ALNR_WARP_CASE(7) ALNR_WARP_CASE(8) ALNR_WARP_CASE(9) ALNR_WARP_CASE(10) ALNR_WARP_CASE(11)
+    ALNR_WARP_CASE(12) ALNR_WARP_CASE(13) ALNR_WARP_CASE(14) ALNR_WARP_CASE(15) ALNR_WARP_CASE(16)
     default: return ALNR_INVALID_ARGUMENT;
   }
 #undef ALNR_WARP_CASE

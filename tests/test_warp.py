@@ -32,9 +32,9 @@ def _ragged(rng, count, lo, hi, V, related=True):
     return ab.PackedPairs.from_lists(qs, ts)
 
 
-@pytest.mark.parametrize("hi", [40, 100, 180, 250, 310, 380, 440, 512])
+@pytest.mark.parametrize("hi", [40, 90, 100, 150, 180, 220, 250, 280, 310, 340, 380, 410, 440, 470, 512])
 def test_every_rows_per_lane_int(hi):
-    """max target length picks R = 2, 4, ..., 16 (one band)."""
+    """max target length picks R = 2, 3, ..., 16 (one band)."""
     rng = np.random.default_rng(hi)
     pairs = _ragged(rng, 96, max(24, hi - 60), hi, 24)
     for mode, d, e in [("local", 11, 2), ("local", 5, 5), ("global", 11, 1)]:
@@ -42,7 +42,7 @@ def test_every_rows_per_lane_int(hi):
         assert (res.status == 0).all()
 
 
-@pytest.mark.parametrize("hi", [60, 200, 330, 520])
+@pytest.mark.parametrize("hi", [60, 90, 150, 200, 220, 280, 330, 410, 470, 520])
 def test_every_rows_per_lane_f64(hi):
     rng = np.random.default_rng(1000 + hi)
     pairs = _ragged(rng, 48, max(24, hi - 60), hi, 24)
