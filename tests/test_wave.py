@@ -99,3 +99,41 @@ def test_tile_pipeline_equals_column_kernel_and_lockstep_traceback(monkeypatch):
         env = dict(os.environ, **extra)
         outs.append(json.loads(subprocess.check_output([sys.executable, "-c", code], env=env).decode().strip().splitlines()[-1]))
     assert outs[0] == outs[1] == outs[2]
+
+
+@pytest.mark.parametrize("seed", range(24))
+def test_tile_pipeline_and_cooperative_walk_fuzz(seed):
+    """Random shapes, scoring schemes and degrees of relatedness (cheap gaps give long gap runs and
+    paths far from the diagonal: wrong guesses, cut walks, windows left through the side, the
+    one-lane fallback) against the lean oracle."""
+    rng = np.random.default_rng(9000 + seed)
+    m, n = (int(v) for v in rng.integers(1030, 3200, 2))
+    q = rng.integers(0, 4, n).astype(np.uint8)
+    t = rng.integers(0, 4, m).astype(np.uint8)
+    kind = seed % 4
+    if kind != 0:  # related stretches with substitutions and indels of growing length
+        src, out, i = q, [], 0
+        indel = [0.0, 0.01, 0.05, 0.15][kind]
+        while i < len(src) and len(out) < m:
+            r = rng.random()
+            if r < indel / 2:
+                i += int(rng.integers(1, 40))
+            elif r < indel:
+                out.extend(rng.integers(0, 4, int(rng.integers(1, 40))).tolist())
+            else:
+                out.append(int(src[i]) if rng.random() > 0.1 else int(rng.integers(0, 4)))
+                i += 1
+        t = np.array((out + rng.integers(0, 4, m).tolist())[:m], dtype=np.uint8)
+    match, mis, d = [(5, -4, 8), (2, -3, 1), (1, -1, 2), (7, -5, 3)][(seed // 4) % 4]
+    mode = "global" if seed % 3 else "local"
+    M = ab.dna_matrix(match, mis)
+    ref = O.align_pair(mode, q, t, float(d), float(d), M, lean=True)
+    cls = ab.SimpleGlobalAligner if mode == "global" else ab.SimpleLocalAligner
+    if ref["status"] != 0:
+        with pytest.raises(Exception):
+            cls.from_seqs(q, t, symbols=ab.DNA).perform_alignment(d, d, M, want_matrices=False)
+        return
+    r = cls.from_seqs(q, t, symbols=ab.DNA).perform_alignment(d, d, M, want_matrices=False)
+    assert r.alignment.f == ref["f"] and r.corner_score == ref["corner"]
+    assert r.alignment.coords == ref["coords"]
+    assert (r.alignment.query == ref["q_aln"]).all() and (r.alignment.target == ref["t_aln"]).all()
