@@ -256,7 +256,9 @@ int alnr_batch_impl::init(const alnr_params *p, const alnr_batch *b, bool want_m
   {
     // offsets sweep (monotone, < 2^31 per sequence, uniform or ragged): 10^7 pairs are 160 MB of
     // offsets, so it runs on a few host threads
-    const unsigned nt = count >= (1u << 20) ? 8u : 1u;
+    // (memory-bound: up to 16 threads, as many as the host has)
+    const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+    const unsigned nt = count >= (1u << 20) ? std::min(16u, hw) : 1u;
     struct Part { uint32_t n_max = 0, m_max = 0; bool uniform = true, bad = false; };
     std::vector<Part> parts(nt);
     const uint64_t n0 = count ? b->q_off[1] - b->q_off[0] : 0, m0 = count ? b->t_off[1] - b->t_off[0] : 0;
