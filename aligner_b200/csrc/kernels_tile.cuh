@@ -15,11 +15,12 @@
 // Band b takes its top boundary row from band b-1 through an L2-resident row buffer WITHOUT a
 // separate progress word: the buffer is preset to a sentinel that no score can take
 // (0x80808080; |H| < 2^30 is guaranteed by the numeric-domain test, batch.cu::classify), lane 31 of
-// the producer stores its tile's bottom row with one 16-byte st.cg, and the consumer prefetches the
-// 32 values of its next 8 steps one chunk ahead (ld.cg) and re-loads the lanes that still hold the
-// sentinel.  Data and flag are the same word, so no fence and no second round trip; in steady
-// state (producer far ahead) the consumer never waits, during the ramp it follows 8 + 31 steps
-// behind, the minimum a 32-lane skew allows.
+// the producer stores its tile's bottom row with one 16-byte st.cg, and the consumer requests the
+// 32 values of its next 8 steps in the middle of the current chunk (ld.cg) and re-loads the lanes
+// that still hold the sentinel.  Data and flag are the same word, so no fence and no second round
+// trip.  Every band runs at the speed of the band above, so it keeps following it at the distance
+// it started with: 31 steps of lane skew + one chunk + the hand-off slack (measured 47 steps,
+// DESIGN.md 4.4) — the critical path of the whole fill is bands x that distance + n / 4 steps.
 //
 // Static penalty only, exactly like kernels_band.cuh (global mode: cell (1,1) pays del, every
 // other cell ext, simple/mod.rs:72,88-92; local mode with del == ext).
