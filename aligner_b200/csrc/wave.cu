@@ -43,7 +43,11 @@ static int tile_run_pair(alnr_batch_impl &B, const Chunk &c, const DLayout &dl, 
   const size_t dbg_words = 0;
 #endif
   const size_t words = 4 + row_words + dbg_words;
-  if (B.d_band.n < words) ALNR_CUDA(B.d_band.alloc(words));
+  if (B.d_band.n < words) {
+    // a longer pair than the previous one of this batch: its fill may still be running on the old rows
+    if (B.d_band.p) ALNR_CUDA(cudaStreamSynchronize(B.stream));
+    ALNR_CUDA(B.d_band.alloc(words));
+  }
   int *base = B.d_band.p;
   a.best = reinterpret_cast<unsigned long long *>(base);
   a.corner_out = base + 2;
@@ -98,7 +102,11 @@ static int band_run_pair(alnr_batch_impl &B, const Chunk &c, const DLayout &dl, 
   const bool local = B.mode == ALNR_LOCAL;
   // scratch: [best (8 B)][corner][pad][prog nbands][rows nbands * (n + 1)]
   const size_t words = 4 + (size_t)a.nbands + (size_t)a.nbands * (a.n + 1);
-  if (B.d_band.n < words) ALNR_CUDA(B.d_band.alloc(words));
+  if (B.d_band.n < words) {
+    // a longer pair than the previous one of this batch: its fill may still be running on the old rows
+    if (B.d_band.p) ALNR_CUDA(cudaStreamSynchronize(B.stream));
+    ALNR_CUDA(B.d_band.alloc(words));
+  }
   int *base = B.d_band.p;
   a.best = reinterpret_cast<unsigned long long *>(base);
   a.corner_out = base + 2;

@@ -137,3 +137,23 @@ def test_tile_pipeline_and_cooperative_walk_fuzz(seed):
     assert r.alignment.f == ref["f"] and r.corner_score == ref["corner"]
     assert r.alignment.coords == ref["coords"]
     assert (r.alignment.query == ref["q_aln"]).all() and (r.alignment.target == ref["t_aln"]).all()
+
+
+def test_several_long_pairs_of_growing_size_in_one_batch():
+    """Each long pair is its own chunk; the band-row scratch grows from pair to pair."""
+    rng = np.random.default_rng(21)
+    qs, ts = [], []
+    for n in (1100, 1700, 2600, 1300):
+        q = rng.integers(0, 4, n).astype(np.uint8)
+        t = np.where(rng.random(n) < 0.85, q, rng.integers(0, 4, n)).astype(np.uint8)[: n - 37]
+        qs.append(q)
+        ts.append(t)
+    pairs = ab.PackedPairs.from_lists(qs, ts)
+    M = ab.dna_matrix(5, -4)
+    for mode in ("global", "local"):
+        res = ab.align_batch(N.GLOBAL if mode == "global" else N.LOCAL, pairs, M, 7, 7)
+        for i in range(len(qs)):
+            ref = O.align_pair(mode, qs[i], ts[i], 7.0, 7.0, M, lean=True)
+            assert res.status[i] == 0 and res.f[i] == ref["f"] and res.corner[i] == ref["corner"]
+            qa, ta = res.alignment(i)
+            assert (qa == ref["q_aln"]).all() and (ta == ref["t_aln"]).all()
