@@ -87,7 +87,7 @@ def test_tile_pipeline_extreme_shapes(m, n, mode, d):
 
 
 def test_tile_pipeline_equals_column_kernel_and_lockstep_traceback(monkeypatch):
-    """The first-generation kernels stay selectable; all three paths give the same alignment."""
+    """The first-generation kernels and the one-lane window walk stay selectable; all paths give the same alignment."""
     import subprocess, sys, os, json
     code = ("import sys, json, hashlib; sys.path.insert(0, %r); import aligner_b200 as ab; "
             "from aligner_b200 import workloads as W; q, t = W.dna_long_pair(6000, seed=11); "
@@ -95,10 +95,10 @@ def test_tile_pipeline_equals_column_kernel_and_lockstep_traceback(monkeypatch):
             "print(json.dumps([r.corner_score, hashlib.sha256(r.alignment.query.tobytes() + r.alignment.target.tobytes()).hexdigest()]))"
             % os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
     outs = []
-    for extra in ({}, {"ALNR_BAND_COLUMN": "1"}, {"ALNR_TRACE_LOCKSTEP": "1"}):
+    for extra in ({}, {"ALNR_BAND_COLUMN": "1"}, {"ALNR_TRACE_LOCKSTEP": "1"}, {"ALNR_TRACE_SEQ": "1"}):
         env = dict(os.environ, **extra)
         outs.append(json.loads(subprocess.check_output([sys.executable, "-c", code], env=env).decode().strip().splitlines()[-1]))
-    assert outs[0] == outs[1] == outs[2]
+    assert outs[0] == outs[1] == outs[2] == outs[3]
 
 
 @pytest.mark.parametrize("seed", range(24))
