@@ -9,6 +9,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <numeric>
+#include <mutex>
 #include <thread>
 #include <type_traits>
 
@@ -25,13 +26,43 @@ static thread_local std::string t_detail;
 void set_error_detail(const std::string &s) { t_detail = s; }
 const char *get_error_detail() { return t_detail.c_str(); }
 
+// The two streams and three events of a call are kept for the next call on the same device: the
+// reference's callers align pair after pair (statistics/mod.rs:270-278), and creating / destroying
+// them was ~0.1 ms of a 0.36 ms single-pair call.  Work queued on a returned stream has been
+// waited for by the call that queued it (run / download synchronise), so reuse is in order.
+namespace {
+struct StreamSet { int device; cudaStream_t s1, s2; cudaEvent_t e0, e1, e2; };
+std::mutex g_sets_mutex;
+std::vector<StreamSet> g_sets;  // at most kMaxSets idle sets
+constexpr size_t kMaxSets = 32;
+}  // namespace
+
+static bool take_stream_set(int device, StreamSet &out) {
+  std::lock_guard<std::mutex> lk(g_sets_mutex);
+  for (size_t i = 0; i < g_sets.size(); ++i)
+    if (g_sets[i].device == device) {
+      out = g_sets[i];
+      g_sets[i] = g_sets.back();
+      g_sets.pop_back();
+      return true;
+    }
+  return false;
+}
+
 alnr_batch_impl::~alnr_batch_impl() {
-  if (ev0) cudaEventDestroy(ev0);
-  if (ev1) cudaEventDestroy(ev1);
-  if (ev2) cudaEventDestroy(ev2);
   for (cudaEvent_t e : fill_events) cudaEventDestroy(e);
   for (cudaEvent_t e : ev_p1) cudaEventDestroy(e);
   for (cudaEvent_t e : ev_p2) cudaEventDestroy(e);
+  if (stream && stream2 && ev0 && ev1 && ev2) {
+    std::lock_guard<std::mutex> lk(g_sets_mutex);
+    if (g_sets.size() < kMaxSets) {
+      g_sets.push_back(StreamSet{device, stream, stream2, ev0, ev1, ev2});
+      return;
+    }
+  }
+  if (ev0) cudaEventDestroy(ev0);
+  if (ev1) cudaEventDestroy(ev1);
+  if (ev2) cudaEventDestroy(ev2);
   if (stream2) cudaStreamDestroy(stream2);
   if (stream) cudaStreamDestroy(stream);
 }
@@ -243,11 +274,16 @@ int alnr_batch_impl::init(const alnr_params *p, const alnr_batch *b, bool want_m
     return ALNR_CUDA_ERROR;
   }
   ALNR_CUDA(cudaSetDevice(device));
-  ALNR_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
-  ALNR_CUDA(cudaStreamCreateWithFlags(&stream2, cudaStreamNonBlocking));
-  ALNR_CUDA(cudaEventCreate(&ev0));
-  ALNR_CUDA(cudaEventCreate(&ev1));
-  ALNR_CUDA(cudaEventCreate(&ev2));
+  StreamSet ss;
+  if (take_stream_set(device, ss)) {
+    stream = ss.s1; stream2 = ss.s2; ev0 = ss.e0; ev1 = ss.e1; ev2 = ss.e2;
+  } else {
+    ALNR_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+    ALNR_CUDA(cudaStreamCreateWithFlags(&stream2, cudaStreamNonBlocking));
+    ALNR_CUDA(cudaEventCreate(&ev0));
+    ALNR_CUDA(cudaEventCreate(&ev1));
+    ALNR_CUDA(cudaEventCreate(&ev2));
+  }
 
   q_total = count ? b->q_off[count] : 0;
   t_total = count ? b->t_off[count] : 0;
