@@ -103,7 +103,15 @@ int alnr_batch_impl::classify() {
   if (!all_int || bound >= 1073741824.0) best = ALNR_NUM_F64;
   else if (strip_eligible(*this, bound)) best = ALNR_NUM_I16X2;
   else best = ALNR_NUM_I32;
-  if (numeric == ALNR_NUM_AUTO) { numeric = best; return ALNR_OK; }
+  if (numeric == ALNR_NUM_AUTO) {
+    numeric = best;
+    // The packed strip kernel runs two pairs per THREAD: below ~16 k pairs it cannot fill the device
+    // and one warp per pair is faster (measured on 150 bp reads: 8 k pairs 4.0 against 4.3 ms, 32 k
+    // pairs 8.8 against 8.0 ms; a single 600 x 600 DNA pair 5.5 ms on one thread).  A forced
+    // ALNR_NUM_I16X2 is still honoured (tests).
+    if (best == ALNR_NUM_I16X2 && count < 16384) numeric = ALNR_NUM_I32;
+    return ALNR_OK;
+  }
   // a forced domain must still be exact
   if (numeric == ALNR_NUM_F64) return ALNR_OK;
   if (numeric == ALNR_NUM_I32 && best != ALNR_NUM_F64) return ALNR_OK;

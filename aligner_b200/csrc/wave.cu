@@ -11,9 +11,14 @@
 
 namespace alnr {
 
-// One pair at a time on the band pipeline pays off from ~10^6 cells for single-pair calls; in a
-// batch the warp-per-pair kernel runs many pairs side by side, so only very long pairs qualify.
-static const uint64_t kWaveMinCellsSingle = 1ull << 20, kWaveMinCellsBatch = 1ull << 24;
+// One pair at a time on the tile pipeline pays off from ~3 x 10^4 cells for single-pair calls
+// (scripts/pair_sizes.py, global DNA pairs: 200 x 200 0.22 against 0.29 ms on the warp kernel,
+// 600 x 600 0.29 against 0.74 ms, 1000 x 1000 0.35 against 1.22 ms); in a batch the warp-per-pair
+// kernel runs many pairs side by side, so only very long pairs qualify.  ALNR_WAVE_MIN_CELLS
+// overrides the single-call threshold (A/B runs).
+static const uint64_t kWaveMinCellsSingle =
+    std::getenv("ALNR_WAVE_MIN_CELLS") ? std::strtoull(std::getenv("ALNR_WAVE_MIN_CELLS"), nullptr, 10) : 1ull << 15;
+static const uint64_t kWaveMinCellsBatch = 1ull << 24;
 
 bool wave_eligible(const alnr_batch_impl &B, uint32_t m, uint32_t n) {
   if (B.numeric != ALNR_NUM_I32 || B.want_matrices) return false;

@@ -122,7 +122,8 @@ def _check_batch(mode, pairs, d, e, M, numeric=N.NUM_AUTO, threads=8):
 def test_config3_batch_subsample(mode, d, e):
     """BASELINE config 3 on a subsample: 150 bp DNA read pairs, +5/-4."""
     pairs = W.dna_read_batch(0, 3000, n=150)
-    _check_batch(mode, pairs, d, e, ab.dna_matrix(5, -4))
+    _check_batch(mode, pairs, d, e, ab.dna_matrix(5, -4), numeric=N.NUM_I16X2)  # the kernel of the full-size run
+    _check_batch(mode, pairs, d, e, ab.dna_matrix(5, -4))                        # what AUTO picks for 3000 pairs
 
 
 def test_ragged_batch_with_bad_pairs():
@@ -212,7 +213,11 @@ def test_strip_matches_exact_domains_on_asymmetric_matrix():
 
 
 def test_auto_selects_strip_for_config3():
-    pairs = W.dna_read_batch(0, 256, n=150)
+    """Packed strip kernel from 16384 uniform DNA pairs on; smaller batches run one warp per pair."""
+    pairs = W.dna_read_batch(0, 16384, n=150)
     db = ab.DeviceBatch(N.LOCAL, pairs, ab.dna_matrix(), 10, 2)
     assert db.numeric == N.NUM_I16X2
+    db.close()
+    db = ab.DeviceBatch(N.LOCAL, W.dna_read_batch(0, 256, n=150), ab.dna_matrix(), 10, 2)
+    assert db.numeric == N.NUM_I32
     db.close()

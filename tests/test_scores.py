@@ -39,7 +39,7 @@ def test_strip_kernel_scores(mode, d, e):
     rng = np.random.default_rng(5)
     for n, m in [(150, 150), (64, 96), (33, 17)]:
         pairs = _rand_uniform_pairs(rng, 700, n, m)
-        res = _check_scores(mode, pairs, d, e, ab.dna_matrix(5, -4))
+        res = _check_scores(mode, pairs, d, e, ab.dna_matrix(5, -4), numeric=N.NUM_I16X2)
         assert res.status.shape == (700,)
 
 
@@ -47,7 +47,7 @@ def test_strip_kernel_scores_speculation_leftovers():
     """+1/-1, del 2, ext 1 on unrelated reads: re-run passes and the exact kernel, all without D."""
     rng = np.random.default_rng(6)
     pairs = _rand_uniform_pairs(rng, 900, 100, 100, related=False)
-    _check_scores("local", pairs, 2, 1, ab.dna_matrix(1, -1))
+    _check_scores("local", pairs, 2, 1, ab.dna_matrix(1, -1), numeric=N.NUM_I16X2)
 
 
 def test_scores_equal_alignment_call_on_config3_sample():
