@@ -639,8 +639,24 @@ int alnr_batch_impl::stream_all(const alnr_batch *b, alnr_batch_out *out) {
   // chunk totals of the compact alignment output come back through pinned memory; the host waits
   // for chunk k's total only after chunk k+1 has been enqueued, so the device never idles
   uint64_t *h_tot = nullptr;
+  bool h_tot_owned = true;
   if (!st) {
-    cudaError_t e = cudaMallocHost(&h_tot, (chunks.size() + 1) * sizeof(uint64_t));
+    // pinned words for the chunk totals: one small buffer per calling thread, kept (cudaMallocHost
+    // takes about a millisecond, which is most of a small batch's call)
+    struct PinnedWords {
+      uint64_t *p = nullptr;
+      ~PinnedWords() { if (p) { cudaFreeHost(p); (void)cudaGetLastError(); } }
+    };
+    static thread_local PinnedWords cached;
+    constexpr size_t kCachedWords = 4096;
+    cudaError_t e = cudaSuccess;
+    if (chunks.size() + 1 <= kCachedWords) {
+      if (!cached.p) e = cudaMallocHost(&cached.p, kCachedWords * sizeof(uint64_t));
+      h_tot = cached.p;
+      h_tot_owned = false;
+    } else {
+      e = cudaMallocHost(&h_tot, (chunks.size() + 1) * sizeof(uint64_t));
+    }
     if (e != cudaSuccess) fail(e, "cudaMallocHost totals");
   }
   auto drain = [&](size_t ci) {  // device -> host copies of chunk ci on s_out
@@ -733,7 +749,7 @@ int alnr_batch_impl::stream_all(const alnr_batch *b, alnr_batch_out *out) {
   }
   cudaStreamDestroy(s_in);
   cudaStreamDestroy(s_out);
-  if (h_tot) cudaFreeHost(h_tot);
+  if (h_tot && h_tot_owned) cudaFreeHost(h_tot);
   return st;
 }
 
