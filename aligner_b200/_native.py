@@ -40,12 +40,14 @@ class PairResult(C.Structure):
 
 
 class Batch(C.Structure):
-    _fields_ = [("q", u8p), ("q_off", u64p), ("t", u8p), ("t_off", u64p), ("count", C.c_uint64)]
+    _fields_ = [("q", u8p), ("q_off", u64p), ("t", u8p), ("t_off", u64p), ("count", C.c_uint64),
+                ("q2", u32p), ("t2", u32p)]
 
 
 class BatchOut(C.Structure):
     _fields_ = [("f", f64p), ("corner", f64p), ("coords", u64p), ("aln_off", u64p),
-                ("aln_len", u32p), ("q_aln", u8p), ("t_aln", u8p), ("status", i32p)]
+                ("aln_len", u32p), ("q_aln", u8p), ("t_aln", u8p), ("status", i32p),
+                ("end_yx", u32p), ("moves_off", u64p), ("moves", u32p)]
 
 
 class HeuristicItems(C.Structure):
@@ -86,6 +88,10 @@ SIGNATURES = {
     "alnr_free_pair_result": (None, [C.POINTER(PairResult)]),
     "alnr_align_batch": (C.c_int, [C.POINTER(Params), C.POINTER(Batch), C.POINTER(BatchOut)]),
     "alnr_batch_create": (C.c_int, [C.POINTER(Params), C.POINTER(Batch), C.POINTER(C.c_void_p)]),
+    "alnr_batch_create_compact": (C.c_int, [C.POINTER(Params), C.POINTER(Batch), C.POINTER(C.c_void_p)]),
+    "alnr_moves_capacity": (C.c_uint64, [C.POINTER(Batch)]),
+    "alnr_expand_alignments": (C.c_int, [C.c_int, C.c_int, C.POINTER(Batch), C.POINTER(BatchOut), C.c_uint64,
+                                         C.c_uint64, C.POINTER(BatchOut), f64p, C.c_int]),
     "alnr_batch_run": (C.c_int, [C.c_void_p]),
     "alnr_batch_sync": (C.c_int, [C.c_void_p]),
     "alnr_batch_download": (C.c_int, [C.c_void_p, C.POINTER(BatchOut)]),

@@ -57,7 +57,52 @@ class PackedPairs:
 
     def c_struct(self):
         return N.Batch(self.q.ctypes.data_as(N.u8p), self.q_off.ctypes.data_as(N.u64p),
-                       self.t.ctypes.data_as(N.u8p), self.t_off.ctypes.data_as(N.u64p), self.count)
+                       self.t.ctypes.data_as(N.u8p), self.t_off.ctypes.data_as(N.u64p), self.count,
+                       N.u32p(), N.u32p())
+
+    def pack2bit(self):
+        """The same batch in the compact input format (alnr_batch.q2 / .t2; DNA codes 0..3)."""
+        return Packed2Pairs(pack2bit(self.q, self.q_off), self.q_off, pack2bit(self.t, self.t_off), self.t_off)
+
+
+def pack2bit(codes, off):
+    """2-bit packing of concatenated DNA codes: 16 codes per uint32, code k of a sequence at bits
+    [2*(k%16), +2) of its word k//16, every sequence on a word boundary, sequences densely one
+    after the other (include/aligner_b200.h, alnr_batch.q2)."""
+    codes = np.asarray(codes, dtype=np.uint8)
+    off = np.asarray(off, dtype=np.uint64).astype(np.int64)
+    lens = np.diff(off)
+    nw = (lens + 15) // 16
+    woff = np.zeros(len(off), dtype=np.int64)
+    woff[1:] = np.cumsum(nw)
+    padded = np.zeros(int(woff[-1]) * 16, dtype=np.uint32)
+    if len(codes):
+        seq = np.repeat(np.arange(len(lens)), lens)            # sequence of every symbol
+        k = np.arange(len(codes), dtype=np.int64) - off[seq]    # its index inside the sequence
+        padded[woff[seq] * 16 + k] = codes & 3
+    sh = (2 * np.arange(16, dtype=np.uint32))[None, :]
+    return np.ascontiguousarray((padded.reshape(-1, 16) << sh).sum(axis=1, dtype=np.uint32))
+
+
+class Packed2Pairs:
+    """A batch in the compact input format: 2-bit DNA words + the symbol offsets (lengths)."""
+
+    def __init__(self, q2, q_off, t2, t_off):
+        self.q2 = np.ascontiguousarray(q2, dtype=np.uint32)
+        self.t2 = np.ascontiguousarray(t2, dtype=np.uint32)
+        self.q_off = np.ascontiguousarray(q_off, dtype=np.uint64)
+        self.t_off = np.ascontiguousarray(t_off, dtype=np.uint64)
+        self.count = len(self.q_off) - 1
+
+    cells = PackedPairs.cells
+    aln_capacity = PackedPairs.aln_capacity
+
+    def c_struct(self):
+        return N.Batch(N.u8p(), self.q_off.ctypes.data_as(N.u64p), N.u8p(), self.t_off.ctypes.data_as(N.u64p),
+                       self.count, self.q2.ctypes.data_as(N.u32p), self.t2.ctypes.data_as(N.u32p))
+
+    def bytes_in(self):
+        return int(self.q2.nbytes + self.t2.nbytes)
 
 
 class BatchResult:
@@ -75,12 +120,13 @@ class BatchResult:
         cap = pairs.aln_capacity() if want_alignments else 0
         self.q_aln = np.zeros(cap, dtype=np.uint8) if want_alignments else None
         self.t_aln = np.zeros(cap, dtype=np.uint8) if want_alignments else None
+        self.end_yx = None
 
     def c_struct(self):
-        ptr = lambda a, ty: a.ctypes.data_as(ty) if a is not None else ty()
-        return N.BatchOut(ptr(self.f, N.f64p), ptr(self.corner, N.f64p), ptr(self.coords, N.u64p),
-                          ptr(self.aln_off, N.u64p), ptr(self.aln_len, N.u32p),
-                          ptr(self.q_aln, N.u8p), ptr(self.t_aln, N.u8p), ptr(self.status, N.i32p))
+        return N.BatchOut(_ptr(self.f, N.f64p), _ptr(self.corner, N.f64p), _ptr(self.coords, N.u64p),
+                          _ptr(self.aln_off, N.u64p), _ptr(self.aln_len, N.u32p),
+                          _ptr(self.q_aln, N.u8p), _ptr(self.t_aln, N.u8p), _ptr(self.status, N.i32p),
+                          _ptr(getattr(self, "end_yx", None), N.u32p), N.u64p(), N.u32p())
 
     def alignment(self, i):
         o, l = int(self.aln_off[i]), int(self.aln_len[i])
@@ -92,6 +138,71 @@ class BatchResult:
         return int(sum(a.nbytes for a in arrs if a is not None))
 
 
+def _ptr(a, ty):
+    return a.ctypes.data_as(ty) if a is not None else ty()
+
+
+class CompactResult:
+    """Outputs of a batched call in the compact result format (alnr_batch_out.moves): per pair the
+    traceback's start cell, its length and one 2-bit Direction per step instead of two byte strings.
+    ``Alignment.query`` / ``.target`` are private to aligner-core (alignment.rs:6-7); what callers
+    can see — coords, f, the frequency matrix, the consensus line — is derived on demand by
+    ``alignment`` / ``expand`` (alnr_expand_alignments on the host cores)."""
+
+    def __init__(self, pairs, mode, volume=4, want_corner=False, want_coords=False, alloc=None):
+        alloc = alloc or (lambda shape, dt: np.zeros(shape, dtype=dt))
+        c = pairs.count
+        self.pairs, self.mode, self.volume, self.count = pairs, mode, volume, c
+        self.f = alloc((c,), np.float64)
+        self.corner = alloc((c,), np.float64) if want_corner else None
+        self.coords = alloc((c, 4), np.uint64) if want_coords else None
+        self.end_yx = alloc((c, 2), np.uint32)
+        self.aln_len = alloc((c,), np.uint32)
+        self.status = alloc((c,), np.int32)
+        self.moves_off = alloc((c,), np.uint64)
+        b = pairs.c_struct()
+        self.moves = alloc((int(N.lib().alnr_moves_capacity(C.byref(b))),), np.uint32)
+
+    def c_struct(self):
+        return N.BatchOut(_ptr(self.f, N.f64p), _ptr(self.corner, N.f64p), _ptr(self.coords, N.u64p), N.u64p(),
+                          _ptr(self.aln_len, N.u32p), N.u8p(), N.u8p(), _ptr(self.status, N.i32p),
+                          _ptr(self.end_yx, N.u32p), _ptr(self.moves_off, N.u64p), _ptr(self.moves, N.u32p))
+
+    def move_words(self):
+        """uint32 words of move strings actually used (what crossed PCIe)."""
+        return int(((self.aln_len.astype(np.int64) + 14) >> 4).sum())
+
+    def bytes_out(self):
+        arrs = [self.f, self.corner, self.coords, self.end_yx, self.aln_len, self.status, self.moves_off]
+        return int(sum(a.nbytes for a in arrs if a is not None)) + 4 * self.move_words()
+
+    def expand(self, first=0, count=None, want_freq=False, threads=0):
+        """BatchResult of the pairs [first, first+count): strings, coords, aln_off / aln_len exactly
+        as the string format returns them (alignments back to back from offset 0)."""
+        count = self.count - first if count is None else count
+        res = BatchResult.__new__(BatchResult)
+        res.count = count
+        res.f = self.f[first:first + count]
+        res.corner = self.corner[first:first + count] if self.corner is not None else None
+        res.status = self.status[first:first + count]
+        res.end_yx = self.end_yx[first:first + count]
+        res.coords = np.zeros((count, 4), dtype=np.uint64)
+        res.aln_off = np.zeros(count, dtype=np.uint64)
+        res.aln_len = np.zeros(count, dtype=np.uint32)
+        total = int(self.aln_len[first:first + count].astype(np.int64).sum())
+        res.q_aln = np.zeros(max(total, 1), dtype=np.uint8)
+        res.t_aln = np.zeros(max(total, 1), dtype=np.uint8)
+        res.freq = np.zeros((count, self.volume, self.volume)) if want_freq else None
+        b, c, e = self.pairs.c_struct(), self.c_struct(), res.c_struct()
+        N.check(N.lib().alnr_expand_alignments(self.mode, self.volume, C.byref(b), C.byref(c), first, count,
+                                               C.byref(e), _ptr(res.freq, N.f64p), threads))
+        return res
+
+    def alignment(self, i):
+        """(query, target) aligned code arrays of pair i, expanded on demand."""
+        return self.expand(i, 1).alignment(0)
+
+
 def make_params(mode, matrix, del_, ext, device=-1, numeric=N.NUM_AUTO):
     mat = np.ascontiguousarray(matrix, dtype=np.float64)
     assert mat.ndim == 2 and mat.shape[0] == mat.shape[1]
@@ -101,10 +212,16 @@ def make_params(mode, matrix, del_, ext, device=-1, numeric=N.NUM_AUTO):
 
 
 def align_batch(mode, pairs, matrix, del_, ext, device=-1, numeric=N.NUM_AUTO, want_alignments=True,
-                out=None):
-    """Host buffers in -> host buffers out (alnr_align_batch)."""
+                out=None, compact=False):
+    """Host buffers in -> host buffers out (alnr_align_batch).  ``pairs``: PackedPairs (byte codes)
+    or Packed2Pairs (2-bit DNA).  ``compact``: return a CompactResult (move strings)."""
     p = make_params(mode, matrix, del_, ext, device, numeric)
-    res = out if out is not None else BatchResult(pairs, want_alignments)
+    if out is not None:
+        res = out
+    elif compact:
+        res = CompactResult(pairs, mode, np.asarray(matrix).shape[0], want_corner=True, want_coords=True)
+    else:
+        res = BatchResult(pairs, want_alignments)
     b = pairs.c_struct()
     o = res.c_struct()
     N.check(N.lib().alnr_align_batch(C.byref(p), C.byref(b), C.byref(o)))
@@ -145,13 +262,17 @@ class DeviceBatch:
     """Device-resident batch: upload once, run many times (alnr_batch_*).  ``score_only`` builds
     the handle with alnr_batch_create_scores; read it with ``download_scores``."""
 
-    def __init__(self, mode, pairs, matrix, del_, ext, device=-1, numeric=N.NUM_AUTO, score_only=False):
+    def __init__(self, mode, pairs, matrix, del_, ext, device=-1, numeric=N.NUM_AUTO, score_only=False,
+                 compact=False):
         self.pairs = pairs
         self.score_only = score_only
+        self.compact = compact
+        self.mode, self.volume = mode, np.asarray(matrix).shape[0]
         self._p = make_params(mode, matrix, del_, ext, device, numeric)
         self._h = C.c_void_p()
         b = pairs.c_struct()
-        create = N.lib().alnr_batch_create_scores if score_only else N.lib().alnr_batch_create
+        create = (N.lib().alnr_batch_create_scores if score_only else
+                  N.lib().alnr_batch_create_compact if compact else N.lib().alnr_batch_create)
         N.check(create(C.byref(self._p), C.byref(b), C.byref(self._h)))
 
     def download_scores(self, out=None):
@@ -173,7 +294,12 @@ class DeviceBatch:
         return ms.value, fill.value
 
     def download(self, want_alignments=True, out=None):
-        res = out if out is not None else BatchResult(self.pairs, want_alignments)
+        if out is not None:
+            res = out
+        elif self.compact:
+            res = CompactResult(self.pairs, self.mode, self.volume, want_corner=True, want_coords=True)
+        else:
+            res = BatchResult(self.pairs, want_alignments)
         o = res.c_struct()
         N.check(N.lib().alnr_batch_download(self._h, C.byref(o)))
         return res

@@ -62,6 +62,26 @@ int alnr_batch_create(const alnr_params *p, const alnr_batch *b, alnr_batch_hand
   return ALNR_OK;
 }
 
+int alnr_batch_create_compact(const alnr_params *p, const alnr_batch *b, alnr_batch_handle **h) {
+  if (!h) return ALNR_INVALID_ARGUMENT;
+  *h = nullptr;
+  alnr_batch_handle *hh = new (std::nothrow) alnr_batch_handle();
+  if (!hh) return ALNR_OUT_OF_MEMORY;
+  hh->impl.moves_out = true;
+  int st = hh->impl.init(p, b, false);
+  if (st) { delete hh; return st; }
+  *h = hh;
+  return ALNR_OK;
+}
+
+uint64_t alnr_moves_capacity(const alnr_batch *b) {
+  if (!b || !b->q_off || !b->t_off) return 0;
+  uint64_t w = 0;
+  for (uint64_t i = 0; i < b->count; ++i)
+    w += (b->q_off[i + 1] - b->q_off[i] + b->t_off[i + 1] - b->t_off[i] + 15) >> 4;
+  return w + 4;
+}
+
 int alnr_batch_create_scores(const alnr_params *p, const alnr_batch *b, alnr_batch_handle **h) {
   if (!h) return ALNR_INVALID_ARGUMENT;
   *h = nullptr;
@@ -142,9 +162,12 @@ void alnr_batch_destroy(alnr_batch_handle *h) {
 
 int alnr_align_batch(const alnr_params *p, const alnr_batch *b, alnr_batch_out *out) {
   if (!out) return ALNR_INVALID_ARGUMENT;
+  if (out->moves && (out->q_aln || out->t_aln || out->aln_off)) return ALNR_INVALID_ARGUMENT;
   alnr_batch_handle *hh = new (std::nothrow) alnr_batch_handle();
   if (!hh) return ALNR_OUT_OF_MEMORY;
   alnr_batch_impl &B = hh->impl;
+  B.moves_out = out->moves != nullptr;
+  B.want_coords = out->coords != nullptr;
   // uniform batches stream chunk by chunk (copies overlap compute); init() finds out which
   B.resident = false;
   B.ramp = true;
@@ -155,7 +178,7 @@ int alnr_align_batch(const alnr_params *p, const alnr_batch *b, alnr_batch_out *
   int st = B.init(p, b, false);
   const auto t1 = std::chrono::steady_clock::now();
   if (!st) {
-    if (B.uniform) {
+    if (B.uniform && (!B.moves_out || B.moves_direct)) {
       st = B.stream_all(b, out);
       if (timing)
         std::fprintf(stderr, "[alnr] align_batch: init %.1f ms, stream_all %.1f ms, %zu chunks\n",
@@ -164,7 +187,10 @@ int alnr_align_batch(const alnr_params *p, const alnr_batch *b, alnr_batch_out *
                      B.chunks.size());
     } else {
       cudaError_t e = cudaSuccess;
-      if (B.count) {
+      if (B.count && B.packed_in) {
+        e = cudaMemcpyAsync(B.d_q2raw.p, b->q2, B.q2_words * 4, cudaMemcpyHostToDevice, B.stream);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(B.d_t2raw.p, b->t2, B.t2_words * 4, cudaMemcpyHostToDevice, B.stream);
+      } else if (B.count) {
         e = cudaMemcpyAsync(B.d_q.p, b->q, B.q_total, cudaMemcpyHostToDevice, B.stream);
         if (e == cudaSuccess) e = cudaMemcpyAsync(B.d_t.p, b->t, B.t_total, cudaMemcpyHostToDevice, B.stream);
       }

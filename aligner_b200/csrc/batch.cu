@@ -50,6 +50,14 @@ static bool take_stream_set(int device, StreamSet &out) {
 }
 
 alnr_batch_impl::~alnr_batch_impl() {
+  // Early returns (a failed init / run) get here with work possibly still queued: the device buffers
+  // go back to the pool and the stream set to the next caller only after both streams have drained.
+  if (stream || stream2) {
+    (void)cudaSetDevice(device);
+    if (stream) (void)cudaStreamSynchronize(stream);
+    if (stream2) (void)cudaStreamSynchronize(stream2);
+    (void)cudaGetLastError();
+  }
   for (cudaEvent_t e : fill_events) cudaEventDestroy(e);
   for (cudaEvent_t e : ev_p1) cudaEventDestroy(e);
   for (cudaEvent_t e : ev_p2) cudaEventDestroy(e);
@@ -126,7 +134,7 @@ static __global__ void uniform_offsets_kernel(uint64_t *qo, uint64_t *to, uint64
   if (i < n_off) { qo[i] = i * n; to[i] = i * m; }
 }
 
-static uint64_t scratch_budget_bytes() {
+static uint64_t scratch_budget_bytes(double scale) {
   // cudaMemGetInfo was seen to take 0.1 - 60 ms per call: ask at most every few seconds per device
   struct Cached { uint64_t free_b = 0; std::chrono::steady_clock::time_point at; bool valid = false; };
   static thread_local Cached cache[16];
@@ -140,7 +148,10 @@ static uint64_t scratch_budget_bytes() {
     if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) return 1ull << 30;
     cd.free_b = free_b; cd.at = now; cd.valid = true;
   }
-  uint64_t b = free_b / 3;
+  // blocks the library's own pool holds are available to this call (pool_alloc hands them out or
+  // gives them back to the driver on demand); `scale` halves after an out-of-memory (other host
+  // threads plan against the same free bytes at the same time)
+  uint64_t b = (uint64_t)((double)((free_b + pool_cached_bytes(dev)) / 3) * scale);
   const uint64_t cap = 24ull << 30;
   return std::max<uint64_t>(std::min<uint64_t>(b, cap), 64ull << 20);
 }
@@ -175,7 +186,7 @@ int alnr_batch_impl::plan_chunks(const uint64_t *q_off, const uint64_t *t_off) {
     uint32_t mx = 0;
     for (uint64_t s = count; s-- > 0;) { uint32_t m, n; dims(s, m, n); mx = std::max(mx, n); nsuf[s] = mx; }
   }
-  const uint64_t budget = scratch_budget_bytes() / 2;  // two parity copies of the chunk scratch
+  const uint64_t budget = scratch_budget_bytes(budget_scale) / 2;  // two parity copies of the chunk scratch
   const uint64_t kStripWavePairs = numeric == ALNR_NUM_I16X2 ? strip_wave_pairs() : 1;
   const size_t num_sz = numeric == ALNR_NUM_F64 ? 8 : 4;
   uint64_t s = 0;
@@ -270,6 +281,14 @@ int alnr_batch_impl::init(const alnr_params *p, const alnr_batch *b, bool want_m
   if (p->volume < 1 || p->volume > 32) return ALNR_MATRIX_SHAPE_ERROR;
   if (b->count >= (1ull << 31)) return ALNR_INVALID_ARGUMENT;
   if (b->count && (!b->q_off || !b->t_off)) return ALNR_INVALID_ARGUMENT;
+  if ((b->q2 != nullptr) != (b->t2 != nullptr)) return ALNR_INVALID_ARGUMENT;
+  packed_in = b->q2 != nullptr;
+  if (packed_in && p->volume != 4) {
+    set_error_detail("2-bit packed input needs volume == 4 (DNA)");
+    return ALNR_INVALID_ARGUMENT;
+  }
+  if (b->count && !packed_in && (!b->q || !b->t)) return ALNR_INVALID_ARGUMENT;
+  if (packed_in && want_mats) return ALNR_INVALID_ARGUMENT;
   mode = p->mode; V = p->volume; del = p->del; ext = p->ext; numeric = p->numeric;
   device = p->device < 0 ? 0 : p->device;
   want_matrices = want_mats;
@@ -303,21 +322,23 @@ int alnr_batch_impl::init(const alnr_params *p, const alnr_batch *b, bool want_m
     // (memory-bound: up to 16 threads, as many as the host has)
     const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
     const unsigned nt = count >= (1u << 20) ? std::min(16u, hw) : 1u;
-    struct Part { uint32_t n_max = 0, m_max = 0; bool uniform = true, bad = false; };
+    struct Part { uint32_t n_max = 0, m_max = 0; bool uniform = true, bad = false; uint64_t mvw = 0; };
     std::vector<Part> parts(nt);
     const uint64_t n0 = count ? b->q_off[1] - b->q_off[0] : 0, m0 = count ? b->t_off[1] - b->t_off[0] : 0;
     auto sweep = [&](unsigned k) {
       Part &pt = parts[k];
       const uint64_t lo = count * k / nt, hi = count * (k + 1) / nt;
-      uint64_t nmx = 0, mmx = 0, diff = 0, neg = 0;
+      uint64_t nmx = 0, mmx = 0, diff = 0, neg = 0, mvw = 0;
       for (uint64_t i = lo; i < hi; ++i) {
         const uint64_t n = b->q_off[i + 1] - b->q_off[i], m = b->t_off[i + 1] - b->t_off[i];
         neg |= (n | m) >> 31;  // covers offsets that go backwards (the difference wraps)
+        mvw += (n + m + 15) >> 4;
         diff |= (n ^ n0) | (m ^ m0);
         nmx = n > nmx ? n : nmx;
         mmx = m > mmx ? m : mmx;
       }
       pt.bad = neg != 0; pt.uniform = diff == 0; pt.n_max = (uint32_t)nmx; pt.m_max = (uint32_t)mmx;
+      pt.mvw = mvw;
     };
     if (nt == 1) sweep(0);
     else {
@@ -325,8 +346,10 @@ int alnr_batch_impl::init(const alnr_params *p, const alnr_batch *b, bool want_m
       for (unsigned k = 0; k < nt; ++k) th.emplace_back(sweep, k);
       for (auto &t : th) t.join();
     }
+    mv_capacity = 0;
     for (const Part &pt : parts) {
       if (pt.bad) return ALNR_INVALID_ARGUMENT;
+      mv_capacity += pt.mvw;
       uniform = uniform && pt.uniform;
       n_max = std::max(n_max, pt.n_max);
       m_max = std::max(m_max, pt.m_max);
@@ -335,13 +358,44 @@ int alnr_batch_impl::init(const alnr_params *p, const alnr_batch *b, bool want_m
   lap("streams+sweep");
   int st = classify();
   if (st) return st;
-
-  ALNR_CUDA(d_q.alloc(q_total + 16));
-  ALNR_CUDA(d_t.alloc(t_total + 16));
+  if (packed_in) {
+    // sequence i starts at word sum_{j<i} ceil(len_j / 16); uniform lengths need no table
+    const uint64_t nwq = (n_max + 15) / 16, nwt = (m_max + 15) / 16;
+    q2_words = count * nwq; t2_words = count * nwt;
+    h_qwoff.clear(); h_twoff.clear();
+    if (!uniform) {
+      h_qwoff.resize(count + 1); h_twoff.resize(count + 1);
+      uint64_t wq = 0, wt = 0;
+      for (uint64_t i = 0; i < count; ++i) {
+        h_qwoff[i] = wq; h_twoff[i] = wt;
+        wq += (b->q_off[i + 1] - b->q_off[i] + 15) >> 4;
+        wt += (b->t_off[i + 1] - b->t_off[i] + 15) >> 4;
+      }
+      h_qwoff[count] = q2_words = wq; h_twoff[count] = t2_words = wt;
+    }
+  }
+  // byte codes on the device: not needed when the packed words feed the strip kernel directly and
+  // no strings are expanded
+  const bool need_bytes = !(packed_in && moves_out && numeric == ALNR_NUM_I16X2);
+  ALNR_CUDA(d_q.alloc(need_bytes ? q_total + 16 : 16));
+  ALNR_CUDA(d_t.alloc(need_bytes ? t_total + 16 : 16));
   ALNR_CUDA(d_qoff.alloc(count + 1));
   ALNR_CUDA(d_toff.alloc(count + 1));
+  if (packed_in) {
+    ALNR_CUDA(d_q2raw.alloc(q2_words + 4));
+    ALNR_CUDA(d_t2raw.alloc(t2_words + 4));
+    if (!uniform) {
+      ALNR_CUDA(d_qwoff.alloc(count + 1));
+      ALNR_CUDA(d_twoff.alloc(count + 1));
+      ALNR_CUDA(cudaMemcpyAsync(d_qwoff.p, h_qwoff.data(), (count + 1) * 8, cudaMemcpyHostToDevice, stream));
+      ALNR_CUDA(cudaMemcpyAsync(d_twoff.p, h_twoff.data(), (count + 1) * 8, cudaMemcpyHostToDevice, stream));
+    }
+  }
   if (count) {
-    if (resident) {
+    if (resident && packed_in) {
+      ALNR_CUDA(cudaMemcpyAsync(d_q2raw.p, b->q2, q2_words * 4, cudaMemcpyHostToDevice, stream));
+      ALNR_CUDA(cudaMemcpyAsync(d_t2raw.p, b->t2, t2_words * 4, cudaMemcpyHostToDevice, stream));
+    } else if (resident) {
       ALNR_CUDA(cudaMemcpyAsync(d_q.p, b->q, q_total, cudaMemcpyHostToDevice, stream));
       ALNR_CUDA(cudaMemcpyAsync(d_t.p, b->t, t_total, cudaMemcpyHostToDevice, stream));
     }
@@ -365,9 +419,25 @@ int alnr_batch_impl::init(const alnr_params *p, const alnr_batch *b, bool want_m
   ALNR_CUDA(cudaStreamSynchronize(stream));
 
   lap("inputs");
-  st = plan_chunks(b->q_off, b->t_off);
+  // Scratch planned against the free memory; when an allocation still fails (several host threads
+  // planning at once, fragmentation) the cached blocks are returned and the plan is redone with half
+  // the budget — smaller chunks instead of ALNR_OUT_OF_MEMORY.
+  for (int attempt = 0;; ++attempt) {
+    st = plan_and_alloc(b);
+    if (st != ALNR_OUT_OF_MEMORY || attempt == 4) break;
+    pool_release_all();
+    budget_scale *= 0.5;
+  }
+  if (timing) std::fprintf(stderr, "[alnr] init:%s ms\n", t_log.c_str());
+  return st;
+}
+
+int alnr_batch_impl::plan_and_alloc(const alnr_batch *b) {
+  for (cudaEvent_t e : ev_p1) cudaEventDestroy(e);
+  for (cudaEvent_t e : ev_p2) cudaEventDestroy(e);
+  ev_p1.clear(); ev_p2.clear();
+  int st = plan_chunks(b->q_off, b->t_off);
   if (st) return st;
-  lap("plan");
 
   ALNR_CUDA(d_f.alloc(count));
   ALNR_CUDA(d_corner.alloc(count));
@@ -376,14 +446,24 @@ int alnr_batch_impl::init(const alnr_params *p, const alnr_batch *b, bool want_m
   ALNR_CUDA(d_coords.alloc(count * 4));
   ALNR_CUDA(d_alnoff.alloc(count));
   ALNR_CUDA(d_alnlen.alloc(count));
-  ALNR_CUDA(d_qaln.alloc(score_only ? 1 : q_total + t_total + count));
-  ALNR_CUDA(d_taln.alloc(score_only ? 1 : q_total + t_total + count));
+  if (score_only) moves_out = false;
+  moves_direct = moves_out && !chunks.empty();
+  for (const Chunk &c : chunks) moves_direct = moves_direct && chunk_compact(c);
+  if (moves_out) {
+    ALNR_CUDA(d_mvout.alloc(mv_capacity + 4));
+    ALNR_CUDA(d_mvoff.alloc(count));
+    ALNR_CUDA(d_mvbase.alloc(chunks.size() + 2));
+  }
+  const bool no_strings = score_only || moves_direct;
+  ALNR_CUDA(d_qaln.alloc(no_strings ? 1 : q_total + t_total + count));
+  ALNR_CUDA(d_taln.alloc(no_strings ? 1 : q_total + t_total + count));
   ALNR_CUDA(d_flags.alloc(4));
   ALNR_CUDA(d_rerun.alloc(count + 1));
   {
     uint32_t cmax = 0;
     for (const Chunk &c : chunks) cmax = std::max(cmax, c.count);
-    ALNR_CUDA(d_desc.alloc((size_t)cmax / (kScanBlock * kScanItems) + 4));
+    // scan descriptors: a chunk's tiles, or (compact results derived from strings) the whole batch's
+    ALNR_CUDA(d_desc.alloc((size_t)((moves_out && !moves_direct) ? count : cmax) / (kScanBlock * kScanItems) + 4));
     ALNR_CUDA(d_ctotal.alloc(chunks.size() + 1));
     uint64_t mwords = 1;
     for (const Chunk &c : chunks)
@@ -416,8 +496,6 @@ int alnr_batch_impl::init(const alnr_params *p, const alnr_batch *b, bool want_m
     ALNR_CUDA(d_Hout.alloc(((size_t)m_max + 1) * ((size_t)n_max + 1)));
     ALNR_CUDA(d_Dout.alloc(((size_t)m_max + 1) * ((size_t)n_max + 1)));
   }
-  lap("buffers");
-  if (timing) std::fprintf(stderr, "[alnr] init:%s ms\n", t_log.c_str());
   if (numeric == ALNR_NUM_I16X2) {
     st = strip_prepare(*this);
     if (st) return st;
@@ -478,7 +556,11 @@ int alnr_batch_impl::run() {
   ALNR_CUDA(cudaSetDevice(device));
   if (count == 0) return ALNR_OK;
   ALNR_CUDA(cudaMemsetAsync(d_flags.p, 0, 4 * sizeof(int), stream));
-  if (!uniform) {  // sorted order: chunks are not contiguous symbol ranges, sweep everything first
+  if (moves_out) ALNR_CUDA(cudaMemsetAsync(d_mvbase.p, 0, (chunks.size() + 2) * 8, stream));
+  if (!uniform && packed_in) {
+    int st = unpack_all();  // 2-bit codes are in range by construction: no symbol sweep
+    if (st) return st;
+  } else if (!uniform) {  // sorted order: chunks are not contiguous symbol ranges, sweep everything first
     any_symbol_out_of_range_kernel<<<148 * 8, 256, 0, stream>>>(d_q.p, q_total, V, d_flags.p);
     ALNR_LAUNCHED();
     any_symbol_out_of_range_kernel<<<148 * 8, 256, 0, stream>>>(d_t.p, t_total, V, d_flags.p);
@@ -489,6 +571,50 @@ int alnr_batch_impl::run() {
     int st = run_chunk(ci);
     if (st) return st;
   }
+  if (moves_out && !moves_direct) return moves_from_strings();
+  return ALNR_OK;
+}
+
+// Compact input: byte codes of one chunk's sequences (uniform batches: a chunk is a contiguous
+// range of sequences and of packed words).  Skipped when nothing downstream reads bytes.
+int alnr_batch_impl::unpack_chunk(const Chunk &c) {
+  if (packed_in && moves_out && numeric == ALNR_NUM_I16X2) return ALNR_OK;
+  const uint32_t nwq = (n_max + 15) / 16, nwt = (m_max + 15) / 16;
+  if (nwq) {
+    unpack2bit_kernel<<<(unsigned)(((uint64_t)c.count * nwq + 255) / 256), 256, 0, stream>>>(
+        d_q2raw.p, nullptr, nwq, d_qoff.p, c.first, c.count, d_q.p);
+    ALNR_LAUNCHED();
+  }
+  if (nwt) {
+    unpack2bit_kernel<<<(unsigned)(((uint64_t)c.count * nwt + 255) / 256), 256, 0, stream>>>(
+        d_t2raw.p, nullptr, nwt, d_toff.p, c.first, c.count, d_t.p);
+    ALNR_LAUNCHED();
+  }
+  return ALNR_OK;
+}
+
+int alnr_batch_impl::unpack_all() {
+  const unsigned blocks = (unsigned)((count * 32 + 255) / 256);
+  unpack2bit_kernel<<<blocks, 256, 0, stream>>>(d_q2raw.p, d_qwoff.p, 0, d_qoff.p, 0, count, d_q.p);
+  ALNR_LAUNCHED();
+  unpack2bit_kernel<<<blocks, 256, 0, stream>>>(d_t2raw.p, d_twoff.p, 0, d_toff.p, 0, count, d_t.p);
+  ALNR_LAUNCHED();
+  return ALNR_OK;
+}
+
+// Compact results for batches whose chunks ran a string traceback (ragged batches, long pairs, tiny
+// batches): one scan of the word counts in PAIR order over the whole batch, then the move words are
+// read off the aligned strings.  On `stream`, after the last chunk's second phase.
+int alnr_batch_impl::moves_from_strings() {
+  const uint32_t tiles = (uint32_t)((count + kScanBlock * kScanItems - 1) / (kScanBlock * kScanItems));
+  ALNR_CUDA(cudaMemsetAsync(d_desc.p, 0, ((size_t)tiles + 1) * 8, stream));
+  scan_lengths_kernel<true><<<tiles, kScanBlock, 0, stream>>>(d_alnlen.p, d_mvoff.p, 0, (uint32_t)count, 0,
+                                                              reinterpret_cast<unsigned long long *>(d_desc.p),
+                                                              d_mvbase.p + chunks.size());
+  ALNR_LAUNCHED();
+  strings_to_moves_kernel<<<(unsigned)((count * 32 + 127) / 128), 128, 0, stream>>>(
+      d_qaln.p, d_taln.p, d_alnoff.p, d_alnlen.p, d_mvoff.p, count, d_mvout.p);
+  ALNR_LAUNCHED();
   return ALNR_OK;
 }
 
@@ -522,8 +648,13 @@ int alnr_batch_impl::phase1(size_t ci) {
   FillOut fo{d_f.p, d_corner.p, d_start.p, d_status.p};
   ChunkView cv{d_q.p, d_t.p, d_qoff.p, d_toff.p, uniform ? nullptr : d_order.p, c.first, c.count};
   const DLayout dl = layout_for(c);
+  if (packed_in && uniform) {
+    int stu = unpack_chunk(c);
+    if (stu) return stu;
+  }
   // symbol validation: one coalesced sweep; the per-pair scan only runs if it found something
-  if (uniform || c.wave) {
+  // (2-bit packed input is in range by construction)
+  if ((uniform || c.wave) && !packed_in) {
     const unsigned gq = (unsigned)std::min<uint64_t>(148 * 8, (c.q1 - c.q0) / 4096 + 1);
     const unsigned gt = (unsigned)std::min<uint64_t>(148 * 8, (c.t1 - c.t0) / 4096 + 1);
     any_symbol_out_of_range_kernel<<<gq, 256, 0, stream>>>(d_q.p + c.q0, c.q1 - c.q0, V, d_flags.p);
@@ -549,7 +680,7 @@ int alnr_batch_impl::phase1(size_t ci) {
 int alnr_batch_impl::phase2(size_t ci) {
   const Chunk &c = chunks[ci];
   FillOut fo{d_f.p, d_corner.p, d_start.p, d_status.p};
-  TraceOut to{d_coords.p, d_alnoff.p, d_alnlen.p, d_qaln.p, d_taln.p, nullptr};
+  TraceOut to{want_coords ? d_coords.p : nullptr, d_alnoff.p, d_alnlen.p, d_qaln.p, d_taln.p, nullptr};
   ChunkView cv{d_q.p, d_t.p, d_qoff.p, d_toff.p, uniform ? nullptr : d_order.p, c.first, c.count};
   const DLayout dl = layout_for(c);
   if (numeric == ALNR_NUM_I16X2 && !c.wave && mode == ALNR_LOCAL && del != ext) {
@@ -561,7 +692,21 @@ int alnr_batch_impl::phase2(size_t ci) {
   if (score_only) return ALNR_OK;  // f, corner and the arg-max cell are final after the fill
   TraceArgs ta{cv, mode, V, Dp(), dl, fo, to};
   const uint32_t nmw = (c.n_max + c.m_max + 1 + 15) / 16;  // 2-bit move words per pair
-  if (chunk_compact(c)) {
+  if (chunk_compact(c) && moves_direct) {
+    // compact result format: move strings (A), scan of the word counts continuing the running total
+    // of the earlier chunks (S), dense move words in pair order (G) — no strings are expanded
+    const uint32_t stride = (c.count + 31) / 32 * 32;
+    const uint32_t tiles = (c.count + kScanBlock * kScanItems - 1) / (kScanBlock * kScanItems);
+    trace_moves_kernel<<<(c.count + 127) / 128, 128, 0, s2>>>(ta, d_moves.p, nullptr, stride);
+    ALNR_LAUNCHED();
+    ALNR_CUDA(cudaMemsetAsync(d_desc.p, 0, ((size_t)tiles + 1) * 8, s2));
+    scan_lengths_kernel<true><<<tiles, kScanBlock, 0, s2>>>(d_alnlen.p, d_mvoff.p, c.first, c.count, 0,
+                                                            reinterpret_cast<unsigned long long *>(d_desc.p),
+                                                            d_mvbase.p + ci + 1, d_mvbase.p + ci);
+    ALNR_LAUNCHED();
+    moves_gather_kernel<<<(c.count + 127) / 128, 128, 0, s2>>>(d_moves.p, stride, d_alnlen.p, d_mvoff.p, c.first,
+                                                               c.count, d_mvout.p);
+  } else if (chunk_compact(c)) {
     // alignments of the chunk back to back from the start of its region (kernels_trace.cuh A/S/B)
     const uint32_t stride = (c.count + 31) / 32 * 32;
     const uint32_t tiles = (c.count + kScanBlock * kScanItems - 1) / (kScanBlock * kScanItems);
@@ -569,7 +714,7 @@ int alnr_batch_impl::phase2(size_t ci) {
     trace_moves_kernel<<<(c.count + 127) / 128, 128, 0, s2>>>(ta, d_moves.p, cxy, stride);
     ALNR_LAUNCHED();
     ALNR_CUDA(cudaMemsetAsync(d_desc.p, 0, ((size_t)tiles + 1) * 8, s2));
-    scan_lengths_kernel<<<tiles, kScanBlock, 0, s2>>>(d_alnlen.p, d_alnoff.p, c.first, c.count,
+    scan_lengths_kernel<false><<<tiles, kScanBlock, 0, s2>>>(d_alnlen.p, d_alnoff.p, c.first, c.count,
                                                       c.q0 + c.t0 + c.first,
                                                       reinterpret_cast<unsigned long long *>(d_desc.p),
                                                       d_ctotal.p + ci);
@@ -622,6 +767,7 @@ int alnr_batch_impl::stream_all(const alnr_batch *b, alnr_batch_out *out) {
   }
   if (!st) {
     cudaError_t e = cudaMemsetAsync(d_flags.p, 0, 4 * sizeof(int), stream);
+    if (e == cudaSuccess && moves_out) e = cudaMemsetAsync(d_mvbase.p, 0, (chunks.size() + 2) * 8, stream);
     if (e != cudaSuccess) fail(e, "memset flags");
   }
   rerun_total = 0;
@@ -679,11 +825,19 @@ int alnr_batch_impl::stream_all(const alnr_batch *b, alnr_batch_out *out) {
     cp(out->f, d_f.p, f0 * 8, fc * 8);
     cp(out->corner, d_corner.p, f0 * 8, fc * 8);
     cp(out->coords, d_coords.p, f0 * 32, fc * 32);
-    cp(out->aln_off, d_alnoff.p, f0 * 8, fc * 8);
+    cp(out->end_yx, d_start.p, f0 * 8, fc * 8);
     cp(out->aln_len, d_alnlen.p, f0 * 4, fc * 4);
     cp(out->status, d_status.p, f0 * 4, fc * 4);
-    cp(out->q_aln, d_qaln.p, a0, abytes);
-    cp(out->t_aln, d_taln.p, a0, abytes);
+    if (moves_out) {
+      // h_tot[ci] = move words up to and including this chunk (running total kept on the device)
+      const size_t w0 = ci ? (size_t)h_tot[ci - 1] : 0, w1 = (size_t)h_tot[ci];
+      cp(out->moves_off, d_mvoff.p, f0 * 8, fc * 8);
+      cp(out->moves, d_mvout.p, w0 * 4, (w1 - w0) * 4);
+    } else {
+      cp(out->aln_off, d_alnoff.p, f0 * 8, fc * 8);
+      cp(out->q_aln, d_qaln.p, a0, abytes);
+      cp(out->t_aln, d_taln.p, a0, abytes);
+    }
     if (e != cudaSuccess) fail(e, "D2H chunk");
     mark(s_out);
   };
@@ -695,8 +849,16 @@ int alnr_batch_impl::stream_all(const alnr_batch *b, alnr_batch_out *out) {
   auto upload = [&](size_t ci) {
     if (ci >= chunks.size() || st) return;
     const Chunk &c = chunks[ci];
-    cudaError_t e = cudaMemcpyAsync(d_q.p + c.q0, b->q + c.q0, c.q1 - c.q0, cudaMemcpyHostToDevice, s_in);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(d_t.p + c.t0, b->t + c.t0, c.t1 - c.t0, cudaMemcpyHostToDevice, s_in);
+    cudaError_t e;
+    if (packed_in) {  // uniform lengths: the chunk's sequences are a contiguous range of packed words
+      const size_t nwq = (n_max + 15) / 16, nwt = (m_max + 15) / 16;
+      e = cudaMemcpyAsync(d_q2raw.p + c.first * nwq, b->q2 + c.first * nwq, c.count * nwq * 4, cudaMemcpyHostToDevice, s_in);
+      if (e == cudaSuccess)
+        e = cudaMemcpyAsync(d_t2raw.p + c.first * nwt, b->t2 + c.first * nwt, c.count * nwt * 4, cudaMemcpyHostToDevice, s_in);
+    } else {
+      e = cudaMemcpyAsync(d_q.p + c.q0, b->q + c.q0, c.q1 - c.q0, cudaMemcpyHostToDevice, s_in);
+      if (e == cudaSuccess) e = cudaMemcpyAsync(d_t.p + c.t0, b->t + c.t0, c.t1 - c.t0, cudaMemcpyHostToDevice, s_in);
+    }
     if (e == cudaSuccess) e = cudaEventRecord(ev_in[ci], s_in);
     if (e != cudaSuccess) fail(e, "H2D chunk");
   };
@@ -713,7 +875,8 @@ int alnr_batch_impl::stream_all(const alnr_batch *b, alnr_batch_out *out) {
     mark(s2);
     // s2 = the stream phase 2 of this chunk ran on: its results are complete there
     if (chunk_compact(c))
-      e = cudaMemcpyAsync(h_tot + ci, d_ctotal.p + ci, sizeof(uint64_t), cudaMemcpyDeviceToHost, s2);
+      e = cudaMemcpyAsync(h_tot + ci, moves_out ? d_mvbase.p + ci + 1 : d_ctotal.p + ci, sizeof(uint64_t),
+                          cudaMemcpyDeviceToHost, s2);
     if (e == cudaSuccess) e = cudaEventRecord(ev_done[ci], s2);
     if (e != cudaSuccess) { fail(e, "chunk events"); break; }
     // drain() blocks the host until its chunk is complete: draining chunk ci-2 here keeps the
@@ -774,6 +937,11 @@ int alnr_batch_impl::download(alnr_batch_out *out) {
     if (out->q_aln || out->t_aln || out->coords || out->aln_off || out->aln_len) return ALNR_INVALID_ARGUMENT;
     return download_scores(out->f, out->corner, nullptr, out->status);
   }
+  if (out->moves && !moves_out) {
+    set_error_detail("compact results need a handle made by alnr_batch_create_compact");
+    return ALNR_INVALID_ARGUMENT;
+  }
+  if (moves_out) return download_moves(out);
   ALNR_CUDA(cudaSetDevice(device));
   if (count == 0) return ALNR_OK;
   auto cp = [&](void *dst, const void *src, size_t bytes) -> cudaError_t {
@@ -783,6 +951,7 @@ int alnr_batch_impl::download(alnr_batch_out *out) {
   ALNR_CUDA(cp(out->f, d_f.p, count * 8));
   ALNR_CUDA(cp(out->corner, d_corner.p, count * 8));
   ALNR_CUDA(cp(out->coords, d_coords.p, count * 32));
+  ALNR_CUDA(cp(out->end_yx, d_start.p, count * 8));
   ALNR_CUDA(cp(out->aln_off, d_alnoff.p, count * 8));
   ALNR_CUDA(cp(out->aln_len, d_alnlen.p, count * 4));
   ALNR_CUDA(cp(out->status, d_status.p, count * 4));
@@ -799,6 +968,32 @@ int alnr_batch_impl::download(alnr_batch_out *out) {
       std::fprintf(stderr, "[alnr] speculation lists: %llu %llu %llu %llu of %llu pairs\n", (unsigned long long)fc[0],
                    (unsigned long long)fc[1], (unsigned long long)fc[2], (unsigned long long)fc[3], (unsigned long long)count);
   }
+  return ALNR_OK;
+}
+
+int alnr_batch_impl::download_moves(alnr_batch_out *out) {
+  if (out->q_aln || out->t_aln || out->aln_off) {
+    set_error_detail("compact results: q_aln / t_aln / aln_off must be NULL (alnr_expand_alignments makes them)");
+    return ALNR_INVALID_ARGUMENT;
+  }
+  ALNR_CUDA(cudaSetDevice(device));
+  if (count == 0) return ALNR_OK;
+  uint64_t words = 0;  // running total after the last chunk (or after the whole-batch scan)
+  ALNR_CUDA(cudaMemcpyAsync(&words, d_mvbase.p + chunks.size(), 8, cudaMemcpyDeviceToHost, stream));
+  ALNR_CUDA(cudaStreamSynchronize(stream));
+  auto cp = [&](void *dst, const void *src, size_t bytes) -> cudaError_t {
+    if (!dst || !bytes) return cudaSuccess;
+    return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, stream);
+  };
+  ALNR_CUDA(cp(out->f, d_f.p, count * 8));
+  ALNR_CUDA(cp(out->corner, d_corner.p, count * 8));
+  ALNR_CUDA(cp(out->coords, d_coords.p, count * 32));
+  ALNR_CUDA(cp(out->end_yx, d_start.p, count * 8));
+  ALNR_CUDA(cp(out->aln_len, d_alnlen.p, count * 4));
+  ALNR_CUDA(cp(out->status, d_status.p, count * 4));
+  ALNR_CUDA(cp(out->moves_off, d_mvoff.p, count * 8));
+  ALNR_CUDA(cp(out->moves, d_mvout.p, words * 4));
+  ALNR_CUDA(cudaStreamSynchronize(stream));
   return ALNR_OK;
 }
 

@@ -25,6 +25,16 @@ struct alnr_batch_impl {
   // score-only calls (alnr_score_batch; statistics/mod.rs:255-292 keeps only alignment.f): no D
   // scratch, no traceback, no alignment buffers
   bool score_only = false;
+  // compact result format (alnr_batch_out.moves): the traceback stops at the 2-bit move strings
+  bool moves_out = false;
+  // every chunk takes the move-string traceback (uniform short pairs): moves are gathered chunk by
+  // chunk; otherwise one pass over the whole batch derives them from the aligned strings
+  bool moves_direct = false;
+  bool want_coords = true;      // false: the caller passed no coords array (host -> host call)
+  // compact input format (alnr_batch.q2 / .t2): 2-bit DNA, 16 codes per word, pair-major
+  bool packed_in = false;
+  uint64_t q2_words = 0, t2_words = 0, mv_capacity = 0;
+  std::vector<uint64_t> h_qwoff, h_twoff;  // ragged packed input: word offset of every sequence
 
   // shape
   uint64_t count = 0, q_total = 0, t_total = 0;
@@ -64,6 +74,15 @@ struct alnr_batch_impl {
   DevBuf<uint32_t> d_brow;      // strip kernel: kept bottom rows of strip 0 (incremental re-run), per parity
   uint64_t brow_words = 0;
   DevBuf<uint32_t> d_wz;        // warp kernel: [8 counters][fail list][z bits 2*nzw per slot]
+  DevBuf<uint32_t> d_q2raw, d_t2raw;  // packed input as it crossed the ABI (pair-major words)
+  DevBuf<uint64_t> d_qwoff, d_twoff;  // ragged packed input: word offsets (count + 1)
+  DevBuf<uint32_t> d_mvout;     // compact results: dense move words in pair order
+  DevBuf<uint64_t> d_mvoff;     // [count] word offset of every pair's move string
+  DevBuf<uint64_t> d_mvbase;    // [chunks + 1] move words before each chunk (running total)
+  int unpack_chunk(const Chunk &c);      // packed input -> byte codes of one chunk (uniform batches)
+  int unpack_all();                      // ... of the whole batch
+  int moves_from_strings();              // !moves_direct: scan + strings -> dense move words
+  int download_moves(alnr_batch_out *out);
   uint64_t rerun_total = 0;
   bool profile = false;                 // record events around every fill launch
   std::vector<cudaEvent_t> fill_events; // pairs (begin, end), filled when profile is set
@@ -89,6 +108,8 @@ struct alnr_batch_impl {
   bool chunk_compact(const Chunk &c) const;  // alignments of the chunk are written back to back
   bool use_warp(uint32_t m) const;  // warp-per-pair kernel instead of one pair per thread
   int plan_chunks(const uint64_t *q_off, const uint64_t *t_off);
+  int plan_and_alloc(const alnr_batch *b);  // chunks + every per-chunk scratch buffer
+  double budget_scale = 1.0;                // halved after an out-of-memory, then re-planned
 };
 
 }  // namespace alnr

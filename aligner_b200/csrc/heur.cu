@@ -10,6 +10,7 @@
 #include <algorithm>
 #include <cfloat>
 #include <cmath>
+#include <cstdlib>
 #include <vector>
 
 #include "host_util.h"
@@ -86,6 +87,16 @@ static __global__ void heur_update_kernel(HeurState h, const uint32_t *list, uin
   }
 }
 
+// items still improving when the round cap is reached: per-item status, the last pass as result
+static __global__ void heur_mark_unconverged_kernel(HeurState h, const uint32_t *list, uint32_t n_active) {
+  const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n_active) return;
+  const uint32_t i = list[k];
+  if (h.status[i] != 0) return;
+  h.status[i] = ALNR_CALCULATION_ERROR;
+  h.fout[i] = h.maxf[i];
+}
+
 }  // namespace alnr
 
 using namespace alnr;
@@ -104,6 +115,7 @@ extern "C" int alnr_transform_matrix(const double *matrix, int rows, int cols, d
 extern "C" int alnr_heuristic_batch(const alnr_params *p, const alnr_batch *b,
                                     const alnr_heuristic_items *it, alnr_heuristic_out *out) {
   if (!p || !b || !it || !out || !it->matrices || !it->frequencies) return ALNR_INVALID_ARGUMENT;
+  if (b->count && (!b->q || !b->t || !b->q_off || !b->t_off)) return ALNR_INVALID_ARGUMENT;  // byte codes only
   if (p->volume < 1 || p->volume > 32) return ALNR_MATRIX_SHAPE_ERROR;
   if (!(std::fabs(p->del) < 1e290 && std::fabs(p->ext) < 1e290)) return ALNR_INVALID_ARGUMENT;  // NaN / inf penalties
   const int V = p->volume, VV = V * V;
@@ -152,6 +164,9 @@ extern "C" int alnr_heuristic_batch(const alnr_params *p, const alnr_batch *b,
   DevBuf<int32_t> d_pst, d_st, d_passes;
   DevBuf<int> d_flag;
   DevBuf<double> d_mats, d_freqs, d_T, d_L, d_F, d_maxf, d_fcur, d_fout, d_corner, d_hcol;
+  // declared after the buffers, so destroyed first: nothing returns to the pool while kernels of an
+  // early return are still queued
+  struct SyncGuard { cudaStream_t s; ~SyncGuard() { cudaStreamSynchronize(s); (void)cudaGetLastError(); } } sync_guard{stream};
   ALNR_CUDA(d_q.alloc(q_total + 16)); ALNR_CUDA(d_t.alloc(t_total + 16));
   ALNR_CUDA(d_qoff.alloc(P + 1)); ALNR_CUDA(d_toff.alloc(P + 1));
   ALNR_CUDA(d_mats.alloc(K * VV)); ALNR_CUDA(d_freqs.alloc(P * V));
@@ -202,8 +217,22 @@ extern "C" int alnr_heuristic_batch(const alnr_params *p, const alnr_batch *b,
     uint32_t n_active = 0;
     ALNR_CUDA(cudaMemcpyAsync(&n_active, d_cnt.p, 4, cudaMemcpyDeviceToHost, stream));
     ALNR_CUDA(cudaStreamSynchronize(stream));
+    // The reference loops until f stops improving with no cap (heuristic/mod.rs:58-77); f is bounded
+    // above, so it ends, but a cap keeps a pathological item from holding the batch: items still
+    // active after max_rounds passes get the per-item status ALNR_CALCULATION_ERROR, every other
+    // item keeps its result and the call returns ALNR_OK.  ALNR_HEUR_MAX_ROUNDS (default 60; the
+    // round counters limit it to 62).  Deviation from the reference, documented in DESIGN.md.
+    static const int max_rounds = [] {
+      const char *e = getenv("ALNR_HEUR_MAX_ROUNDS");
+      const int v = e ? atoi(e) : 60;
+      return v < 1 ? 1 : (v > 62 ? 62 : v);
+    }();
     for (int round = 0; n_active > 0; ++round) {
-      if (round >= 60) { set_error_detail("heuristic loop did not converge in 60 passes"); return ALNR_CALCULATION_ERROR; }
+      if (round >= max_rounds) {
+        heur_mark_unconverged_kernel<<<(n_active + 127) / 128, 128, 0, stream>>>(hs, lists[round & 1], n_active);
+        ALNR_LAUNCHED();
+        break;
+      }
       const uint32_t *cur = lists[round & 1];
       uint32_t *nxt = lists[(round + 1) & 1];
       uint32_t *cnt_next = d_cnt.p + 1 + round;

@@ -42,6 +42,7 @@ inline int cuda_fail(cudaError_t e, const char *what, const char *file, int line
 cudaError_t pool_alloc(void **p, size_t bytes, size_t *granted);
 void pool_free(void *p, size_t granted);
 void pool_release_all();
+size_t pool_cached_bytes(int device);  // bytes of idle blocks the pool holds for `device`
 
 // RAII device buffer backed by the pool.
 template <typename T>

@@ -179,7 +179,17 @@ int strip_main_pass(alnr_batch_impl &B, const Chunk &c, const ChunkView &cv, con
   StripPlan P = strip_plan(B, c, cv, dl, fo);
   cudaStream_t stream = B.stream;
   // pack this chunk's sequences (2 bits per symbol, coalesced layout)
-  {
+  if (B.packed_in) {  // compact input format: the words are there, only their order changes
+    const uint64_t lg = (c.count + 31) / 32;
+    uint64_t threads = lg * 32 * P.a.nwq;
+    interleave2bit_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, stream>>>(
+        B.d_q2raw.p, c.first, c.count, P.a.nwq, B.n_max, const_cast<uint32_t *>(P.a.qpk));
+    ALNR_LAUNCHED();
+    threads = lg * 32 * P.a.nwt;
+    interleave2bit_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, stream>>>(
+        B.d_t2raw.p, c.first, c.count, P.a.nwt, B.m_max, const_cast<uint32_t *>(P.a.tpk));
+    ALNR_LAUNCHED();
+  } else {
     const uint64_t lg = (c.count + 31) / 32;
     uint64_t threads = lg * 32 * P.a.nwq;
     pack2bit_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, stream>>>(

@@ -486,4 +486,21 @@ static __global__ void pack2bit_kernel(const uint8_t *seq, const uint64_t *off, 
   out[((slot >> 5) * nw + w) * 32 + lane] = word;
 }
 
+// Compact input format: the pair-major 2-bit words of the chunk's slots, as they crossed the ABI
+// (in[slot * nw + w]), into the same coalesced layout.  len = symbols per sequence.
+static __global__ void interleave2bit_kernel(const uint32_t *in, uint32_t first, uint32_t count, uint32_t nw,
+                                             uint32_t len, uint32_t *out) {
+  const uint64_t gid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t lane = gid & 31;
+  const uint64_t rest = gid >> 5;
+  const uint32_t w = (uint32_t)(rest % nw);
+  const uint64_t local = rest / nw * 32 + lane;
+  if (local >= count) return;
+  const uint64_t slot = first + local;
+  uint32_t word = in[slot * nw + w];
+  const uint32_t left = len - w * 16;  // > 0: nw = ceil(len / 16)
+  if (left < 16) word &= (1u << (2 * left)) - 1u;
+  out[((slot >> 5) * nw + w) * 32 + lane] = word;
+}
+
 }  // namespace alnr

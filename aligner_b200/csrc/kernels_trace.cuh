@@ -255,7 +255,7 @@ static __global__ void __launch_bounds__(128) trace_moves_kernel(TraceArgs a, ui
   uint32_t cy = sy, cx = sx, acc = 0, K = 0;
   uint32_t *mv = mvg + slot, *cw = cxyg + slot;
   for (;;) {
-    if ((K & 15) == 0) cw[(size_t)(K >> 4) * stride] = cx | (cy << 16);
+    if (cxyg && (K & 15) == 0) cw[(size_t)(K >> 4) * stride] = cx | (cy << 16);
     int d;
     if (cy == 0 || cx == 0) {
       if (!glob || (cy == 0 && cx == 0)) d = DIR_BEGINNING;
@@ -284,11 +284,16 @@ static __global__ void __launch_bounds__(128) trace_moves_kernel(TraceArgs a, ui
 // Single pass: tiles of 1024 pairs are taken in arrival order (ticket), every tile publishes a
 // 64-bit descriptor (flag 1 = its own sum, 2 = inclusive prefix; low 62 bits = value) and warp 0
 // looks back 32 descriptors at a time.  desc[0] is the ticket, desc[1..] the tiles; all zeroed.
+// WORDS: the scanned quantity is the number of 2-bit move words of an alignment, ceil((len - 1) / 16)
+// (compact result format), `base` comes from *base_ptr (the running total of the chunks before this
+// one) and *total continues it.
 constexpr int kScanBlock = 256, kScanItems = 4;
 
+template <bool WORDS>
 static __global__ void __launch_bounds__(kScanBlock) scan_lengths_kernel(const uint32_t *len, uint64_t *off,
                                                                          uint32_t first, uint32_t count, uint64_t base,
-                                                                         unsigned long long *descbuf, uint64_t *total) {
+                                                                         unsigned long long *descbuf, uint64_t *total,
+                                                                         const uint64_t *base_ptr = nullptr) {
   __shared__ uint32_t s_wsum[kScanBlock / 32], s_tile;
   __shared__ unsigned long long s_excl;
   const uint32_t tid = threadIdx.x, lane = tid & 31;
@@ -299,7 +304,11 @@ static __global__ void __launch_bounds__(kScanBlock) scan_lengths_kernel(const u
   const uint32_t i0 = (tile * kScanBlock + tid) * kScanItems;
   uint32_t v[kScanItems], tsum = 0;
 #pragma unroll
-  for (int k = 0; k < kScanItems; ++k) { v[k] = (i0 + k < count) ? len[first + i0 + k] : 0u; tsum += v[k]; }
+  for (int k = 0; k < kScanItems; ++k) {
+    v[k] = (i0 + k < count) ? len[first + i0 + k] : 0u;
+    if (WORDS) v[k] = (v[k] + 14u) >> 4;  // len = moves + 1 (0: no alignment)
+    tsum += v[k];
+  }
   uint32_t inc = tsum;
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
@@ -334,11 +343,11 @@ static __global__ void __launch_bounds__(kScanBlock) scan_lengths_kernel(const u
     if (tid == 0) {
       desc[tile] = (2ull << 62) | (excl + T);
       s_excl = excl;
-      if (tile + 1 == gridDim.x) *total = excl + T;
+      if (tile + 1 == gridDim.x) *total = (base_ptr ? *base_ptr : 0ull) + excl + T;
     }
   }
   __syncthreads();
-  uint64_t o = base + s_excl + woff + (inc - tsum);
+  uint64_t o = base + (base_ptr ? *base_ptr : 0ull) + s_excl + woff + (inc - tsum);
 #pragma unroll
   for (int k = 0; k < kScanItems; ++k) {
     if (i0 + k < count) off[first + i0 + k] = o;
@@ -444,6 +453,83 @@ static __global__ void __launch_bounds__(kExpandThreads) trace_expand_kernel(Tra
   __syncthreads();
   stage_out(gq, q_out, total, oq);
   stage_out(gt, t_out, total, ot);
+}
+
+// ---- compact result format (alnr_batch_out.moves) ------------------------------------------------
+// (G) after (A) and the word scan: the move words of every pair, [w * stride + slot] in the scratch,
+// become one dense run per pair at mvoff[pair].  A warp takes 32 slots; lane <-> slot, so the reads
+// are coalesced and the 4-byte stores of consecutive w fall into the same sectors of L2.
+static __global__ void __launch_bounds__(128) moves_gather_kernel(const uint32_t *mvg, uint32_t stride,
+                                                                  const uint32_t *aln_len, const uint64_t *mvoff,
+                                                                  uint32_t first, uint32_t count, uint32_t *out) {
+  const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+  uint32_t nw = 0;
+  uint64_t o = 0;
+  if (slot < count) {
+    nw = (aln_len[first + slot] + 14u) >> 4;
+    o = mvoff[first + slot];
+  }
+  uint32_t wmax = nw;
+#pragma unroll
+  for (int k = 16; k > 0; k >>= 1) wmax = max(wmax, __shfl_xor_sync(0xffffffffu, wmax, k));
+  for (uint32_t w = 0; w < wmax; ++w)
+    if (w < nw) out[o + w] = mvg[(size_t)w * stride + slot];
+}
+
+// Move words from aligned strings (every traceback that is not the move-string one): one warp per
+// pair, a lane builds one word from 16 columns read backwards from the column before the seed.
+static __global__ void __launch_bounds__(128) strings_to_moves_kernel(const uint8_t *q_aln, const uint8_t *t_aln,
+                                                                      const uint64_t *aln_off, const uint32_t *aln_len,
+                                                                      const uint64_t *mvoff, uint64_t count,
+                                                                      uint32_t *out) {
+  const uint64_t pair = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const uint32_t lane = threadIdx.x & 31;
+  if (pair >= count) return;
+  const uint32_t L = aln_len[pair];
+  if (L < 2) return;
+  const uint32_t K = L - 1, nw = (K + 15) >> 4;
+  const uint64_t last = aln_off[pair] + L - 2;  // column of move 0
+  for (uint32_t w = lane; w < nw; w += 32) {
+    uint32_t word = 0;
+    for (uint32_t j = 0; j < 16 && w * 16 + j < K; ++j) {
+      const uint64_t pos = last - (w * 16 + j);
+      const uint32_t code = q_aln[pos] == kBlank ? DIR_TOP : (t_aln[pos] == kBlank ? DIR_LEFT : DIR_DIAGONAL);
+      word |= code << (2 * j);
+    }
+    out[mvoff[pair] + w] = word;
+  }
+}
+
+// ---- compact input format (alnr_batch.q2 / .t2) ---------------------------------------------------
+// 2-bit codes -> byte codes for the sequences [first, first + count).  woff == nullptr: every
+// sequence has nw words (uniform lengths) and one thread expands one word; else one warp per sequence.
+static __device__ __forceinline__ void unpack_word(uint32_t word, uint8_t *dst, uint64_t left) {
+  if (left >= 16 && ((uintptr_t)dst & 1) == 0) {
+    uint16_t *d2 = reinterpret_cast<uint16_t *>(dst);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) d2[j] = (uint16_t)(((word >> (4 * j)) & 3u) | (((word >> (4 * j + 2)) & 3u) << 8));
+  } else {
+    for (uint32_t j = 0; j < 16 && j < left; ++j) dst[j] = (uint8_t)((word >> (2 * j)) & 3u);
+  }
+}
+
+static __global__ void __launch_bounds__(256) unpack2bit_kernel(const uint32_t *in, const uint64_t *woff, uint32_t nw,
+                                                                const uint64_t *off, uint64_t first, uint64_t count,
+                                                                uint8_t *out) {
+  const uint64_t gid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (!woff) {
+    const uint64_t s = gid / nw;
+    const uint32_t k = (uint32_t)(gid % nw);
+    if (s >= count) return;
+    const uint64_t b = off[first + s], e = off[first + s + 1];
+    if ((uint64_t)k * 16 < e - b) unpack_word(in[(first + s) * nw + k], out + b + (uint64_t)k * 16, e - b - (uint64_t)k * 16);
+  } else {
+    const uint64_t s = gid >> 5;
+    const uint32_t lane = threadIdx.x & 31;
+    if (s >= count) return;
+    const uint64_t b = off[first + s], e = off[first + s + 1], w0 = woff[first + s];
+    for (uint64_t k = lane; k * 16 < e - b; k += 32) unpack_word(in[w0 + k], out + b + k * 16, e - b - k * 16);
+  }
 }
 
 }  // namespace alnr

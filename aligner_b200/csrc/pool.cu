@@ -65,6 +65,16 @@ void pool_free(void *p, size_t granted) {
   P.free_blocks[dev].emplace(granted, p);
 }
 
+size_t pool_cached_bytes(int device) {
+  Pool &P = pool();
+  std::lock_guard<std::mutex> g(P.mu);
+  size_t total = 0;
+  auto it = P.free_blocks.find(device);
+  if (it != P.free_blocks.end())
+    for (auto &b : it->second) total += b.first;
+  return total;
+}
+
 void pool_release_all() {
   Pool &P = pool();
   std::vector<std::pair<int, void *>> blocks;

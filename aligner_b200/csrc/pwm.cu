@@ -210,6 +210,9 @@ int pwm_run(const alnr_pwm_params *p, alnr_pwm_seq *seq, const alnr_windows *w, 
   DevBuf<uint8_t> d_qry, d_Dout;
   DevBuf<int32_t> d_status;
   DevBuf<double> d_f, d_corner, d_freq, d_Hout;
+  // declared after the buffers, so destroyed first: nothing returns to the pool while kernels of an
+  // early return are still queued
+  struct SyncGuard { cudaStream_t s; ~SyncGuard() { cudaStreamSynchronize(s); (void)cudaGetLastError(); } } sync_guard{stream};
   std::vector<T> hp(4 * (size_t)L);
   for (size_t i = 0; i < hp.size(); ++i) hp[i] = (T)p->pwm[i];
   ALNR_CUDA(d_pwm.alloc(hp.size()));

@@ -1,5 +1,7 @@
 // warp_impl.cuh — launcher template shared by warp_i32.cu / warp_f64.cu.
 #pragma once
+#include <cstdlib>
+
 #include "host_util.h"
 #include "kernels_warp.cuh"
 
@@ -30,9 +32,11 @@ static int warp_launch_one(cudaStream_t stream, const WarpArgs<T> &a) {
 
 template <typename T>
 static int warp_launch_any(cudaStream_t stream, const WarpArgs<T> &a, bool local, bool mats) {
-  // MODE 1 (compile-time static penalty) only for FP64, see kernels_warp.cuh
-  constexpr bool kStaticMode = sizeof(T) == 8;
-  const int mode = !local ? 0 : ((a.stateful || !kStaticMode) ? 2 : 1);
+  // MODE 1 (compile-time static penalty): FP64 always; INT32 see kernels_warp.cuh
+  constexpr bool kStaticMode = true;
+  static const bool int_mode1 = getenv("ALNR_WARP_INT_MODE1") != nullptr;
+  const bool static_ok = sizeof(T) == 8 || int_mode1;
+  const int mode = !local ? 0 : ((a.stateful || !static_ok) ? 2 : 1);
   if (mats) {
     if (a.dl.rows_per_word != 8) return ALNR_INVALID_ARGUMENT;
     return mode == 0 ? warp_launch_one<T, 8, 0, true>(stream, a) : warp_launch_one<T, 8, 2, true>(stream, a);

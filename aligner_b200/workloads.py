@@ -137,10 +137,12 @@ def pair_frequencies(pairs, V):
 
 
 def dna_read_pairs_torch(first, count, n=150, seed=0xA11C0DE, sub_rate=0.10, device="cuda", block=1 << 20,
-                         out_q=None, out_t=None):
+                         out_q=None, out_t=None, out_q2=None, out_t2=None):
     """Same pairs as dna_read_pairs, generated on the GPU with torch (bench input setup only —
     not the product path).  int64 arithmetic wraps like uint64; logical shifts are emulated.
-    Returns (q2d, t2d) uint8 host arrays (written into out_q/out_t when given)."""
+    Returns (q2d, t2d) uint8 host arrays (written into out_q/out_t when given).  out_q2 / out_t2:
+    (count, ceil(n/16)) uint32 host arrays that receive the same pairs in the compact input format
+    (2-bit codes, include/aligner_b200.h alnr_batch.q2)."""
     import torch
 
     def i64(v):
@@ -161,6 +163,15 @@ def dna_read_pairs_torch(first, count, n=150, seed=0xA11C0DE, sub_rate=0.10, dev
     t = out_t if out_t is not None else np.empty((count, n), dtype=np.uint8)
     pos = torch.arange(n, dtype=torch.int64, device=device)[None, :] * M1
     thr = int(sub_rate * 65536.0)
+    nw = (n + 15) // 16
+    sh = (2 * torch.arange(16, dtype=torch.int64, device=device))[None, None, :]
+
+    def pack(codes):  # (B, n) uint8 -> (B, nw) uint32 bit patterns as int32
+        padded = torch.zeros((codes.shape[0], nw * 16), dtype=torch.int64, device=device)
+        padded[:, :n] = codes
+        w = (padded.view(-1, nw, 16) << sh).sum(dim=2)
+        return w.to(torch.int32).cpu().numpy().view(np.uint32)
+
     for b0 in range(0, count, block):
         b1 = min(b0 + block, count)
         idx = torch.arange(first + b0, first + b1, dtype=torch.int64, device=device)[:, None]
@@ -173,6 +184,9 @@ def dna_read_pairs_torch(first, count, n=150, seed=0xA11C0DE, sub_rate=0.10, dev
         tb = torch.where(replace, rb, qb)
         q[b0:b1] = qb.cpu().numpy()
         t[b0:b1] = tb.cpu().numpy()
+        if out_q2 is not None:
+            out_q2[b0:b1] = pack(qb)
+            out_t2[b0:b1] = pack(tb)
     return q, t
 
 

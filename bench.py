@@ -27,7 +27,6 @@ for _p in (ROOT, os.path.join(ROOT, "tests")):
 
 METRIC = "GCUPS (cell updates/s) batched SW/NW at 1/2/4/8 B200 vs reference CPU"
 OPS_PER_CELL = 10  # ALU ops per cell update of the full recurrence
-NCU_DRAM_BYTES_PER_CELL = (1.474577e9 + 7.807713e9) / (1e6 * 150 * 150)
 
 
 def parse():
@@ -44,7 +43,13 @@ def parse():
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-e2e", action="store_true", help="profiling runs: skip the host-buffer leg")
+    ap.add_argument("--no-e2e", action="store_true", help="profiling runs: skip the host-buffer legs")
+    ap.add_argument("--no-e2e-strings", action="store_true", help="skip the string-format host-buffer leg")
+    ap.add_argument("--no-configs", action="store_true", help="skip the side configs (C1, C2, C3 linear, C4, C5)")
+    ap.add_argument("--parity-pairs", type=int, default=4096, help="pairs of the timed batch checked against the oracle")
+    ap.add_argument("--c4-len", type=int, default=100000)
+    ap.add_argument("--c5-pairs", type=int, default=2000)
+    ap.add_argument("--c5-mats", type=int, default=100)
     return ap.parse_args()
 
 
@@ -187,6 +192,166 @@ def run_reference(a):
     }))
 
 
+def oracle_threads():
+    return max(1, min(os.cpu_count() or 1, 32))
+
+
+def check_against_oracle(W, O, mode_name, d, e, M, n, get_alignment, f, coords, aln_len, first, count):
+    """Bit parity of `count` pairs starting at `first` of the C3 workload against the oracle."""
+    sub = W.dna_read_batch(first, count, n)
+    ref = O.align_batch(mode_name, sub, d, e, M, threads=oracle_threads())
+    ok = bool((f[:count] == ref["f"]).all() and (coords[:count] == ref["coords"]).all()
+              and (aln_len[:count] == ref["aln_len"]).all())
+    for i in range(count):
+        qa, ta = get_alignment(i)
+        L = int(ref["aln_len"][i])
+        ok = ok and len(qa) == L and bool((qa == ref["q_aln"][i, :L]).all() and (ta == ref["t_aln"][i, :L]).all())
+    return ok
+
+
+def side_configs(a, lib, local, rank, world, int_peak, dist, torch):
+    """The BASELINE configs that are not the headline, each {gcups, ms, parity (vs the oracle on the
+    same inputs or a sample), roofline, cpu_port_gcups}.  C1 / C2 / C4 on rank 0; C5 sharded over
+    all ranks with the NCCL fitness all-reduce."""
+    import hashlib
+    import aligner_b200 as ab
+    from aligner_b200 import _native as N
+    from aligner_b200 import sharding as S
+    from aligner_b200 import workloads as W
+    import oracle_lib as O
+    out = {}
+    alu = int_peak.get("alu_tops")
+
+    def roof(cells, secs, bound="int_alu", peak=None):
+        peak = alu if peak is None else peak
+        ach = cells * OPS_PER_CELL / secs / 1e12
+        return {"bound": bound, "achieved": ach, "peak": peak, "unit": "TOP/s", "frac": ach / peak if peak else None}
+
+    def one_pair(name, mode, q, t, d, e, M, symbols, reps, lean=False):
+        cls = ab.SimpleGlobalAligner if mode == "global" else ab.SimpleLocalAligner
+        al = cls.from_seqs(q, t, symbols=symbols)
+        r = al.perform_alignment(d, e, M, want_matrices=False)
+        best = 1e9
+        for _ in range(reps):
+            t0 = time.perf_counter()
+            r = al.perform_alignment(d, e, M, want_matrices=False)
+            best = min(best, time.perf_counter() - t0)
+        t0 = time.perf_counter()
+        ref = O.align_pair(mode, q, t, float(d), float(e), M, want_matrices=False, lean=lean)
+        cpu = time.perf_counter() - t0
+        ok = bool(r.corner_score == ref["corner"] and r.alignment.f == ref["f"] and r.alignment.coords == ref["coords"]
+                  and len(r.alignment.query) == len(ref["q_aln"]) and (r.alignment.query == ref["q_aln"]).all()
+                  and (r.alignment.target == ref["t_aln"]).all())
+        cells = float(len(q)) * len(t)
+        out[name] = {"gcups": cells / best / 1e9, "ms": best * 1e3, "parity": ok, "roofline": roof(cells, best),
+                     "cpu_port_gcups": cells / cpu / 1e9, "what": "one C-ABI call (alnr_align_pair), host buffers"}
+        return r
+
+    if rank == 0:
+        ex = json.load(open(os.path.join(ROOT, "tests", "golden", "examples.json")))
+        book = [ab.Protein.str_to_vec(r["seq"]) for r in ex["book_example_1.fasta"]]
+        prot = [ab.Protein.str_to_vec(r["seq"]) for r in ex["protein.fasta"]]
+        gene = [ab.DNA.from_u8_vec(r["seq"].encode()) for r in ex["human_gene_example.fasta"]]
+        Md = ab.dna_matrix(5, -4)
+        one_pair("c1", "global", book[0], book[1], 8, 8, ab.get_blosum62(), ab.Protein, 20)
+        one_pair("c2", "local", prot[0], prot[1], 11, 2, ab.get_blosum62(), ab.Protein, 10)
+        one_pair("c4_file", "global", gene[0], gene[1], 8, 8, Md, ab.DNA, 10)
+        # C4 synthetic 10^5 x 10^5: the oracle finishes 2 x 10^4 (lean layout) in seconds; the full size
+        # is checked through properties (the path covers both sequences and re-scores to the corner)
+        q, t = W.dna_long_pair(20000, seed=4)
+        one_pair("c4_2e4", "global", q, t, 8, 8, Md, ab.DNA, 3, lean=True)
+        q, t = W.dna_long_pair(a.c4_len, seed=4)
+        pp = ab.PackedPairs.from_lists([q], [t])
+        db = ab.DeviceBatch(N.GLOBAL, pp, Md, 8, 8, device=local)
+        db.run_timed(2, profile_fill=False)
+        ms, _ = db.run_timed(3, profile_fill=False)
+        _, fill = db.run_timed(3, profile_fill=True)
+        res = db.download()
+        db.close()
+        qa, ta = res.alignment(0)
+        both = (qa[:-1] != 98) & (ta[:-1] != 98)
+        score = Md[ta[:-1][both].astype(np.intp), qa[:-1][both].astype(np.intp)].sum() - 8.0 * float((~both).sum())
+        prop = bool((qa[:-1][qa[:-1] != 98] == q).all() and (ta[:-1][ta[:-1] != 98] == t).all()
+                    and score == res.corner[0])
+        cells = float(len(q)) * len(t)
+        out["c4_1e5"] = {"gcups": cells / (ms / 3e3) / 1e9, "ms": ms / 3, "fill_ms": fill / 3,
+                         "parity": bool(prop and out["c4_2e4"]["parity"]),
+                         "parity_how": "oracle (lean layout) bit-exact at 2x10^4; full size: path covers both "
+                                       "sequences and re-scores to the corner score",
+                         "roofline": roof(cells, fill / 3e3), "cpu_port_gcups": out["c4_2e4"]["cpu_port_gcups"],
+                         "hbm_d_write_gbs": cells * 0.25 / (fill / 3e3) / 1e9,
+                         "what": "device-resident fill + traceback of one %d x %d pair" % (len(q), len(t))}
+
+    # ---- C5: heuristic matrix search, pairs sharded over the ranks, NCCL all-reduce of the block sums
+    P, K = a.c5_pairs, a.c5_mats
+    pairs = W.protein_pairs(0, P, 270, 330)
+    mats = W.candidate_matrices(K)
+    freqs = W.pair_frequencies(pairs, 24)
+    dev = torch.device("cuda", local)
+    S.matrix_search_sharded(S.slice_pairs(pairs, 0, min(P, 8)), mats[:2], 5, 5, -1.0, 576.0, freqs[:min(P, 8)],
+                            device=local, collective_device=dev)
+    best = None
+    for _ in range(3):
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        fit, (lo, hi), bk, bf, fg, sg = S.matrix_search_sharded(pairs, mats, 5, 5, -1.0, 576.0, freqs, device=local,
+                                                                collective_device=dev)
+        torch.cuda.synchronize()
+        dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        best = float(dt[0]) if best is None else min(best, float(dt[0]))
+    sub = S.slice_pairs(pairs, lo, hi)
+    res = ab.heuristic_batch(sub, mats, 5, 5, -1.0, 576.0, freqs[lo:hi], want_matrices=False, device=local)
+    n = np.diff(sub.q_off).astype(np.float64)
+    m = np.diff(sub.t_off).astype(np.float64)
+    cells_t = torch.tensor([float((res.passes.reshape(hi - lo, K) * (n * m)[:, None]).sum())], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(cells_t)
+    if rank == 0:
+        cells = float(cells_t[0])
+        f64 = measure_fp64_peak(lib, local)
+        # oracle on a sample of this rank's items (threads over items)
+        rng = np.random.default_rng(5)
+        pick = rng.choice((hi - lo) * K, size=min(48, (hi - lo) * K), replace=False)
+        t0 = time.perf_counter()
+        ok, cpu_cells = True, 0.0
+        for it in pick:
+            i, k = int(it) // K, int(it) % K
+            qv, tv = sub.pair(i)
+            r = O.heuristic(qv, tv, 5.0, 5.0, mats[k], -1.0, 576.0, freqs[lo + i])
+            ok = ok and O.STATUS_TO_ALNR[r["status"]] == int(res.status[it])
+            if r["status"] == 0:
+                ok = ok and r["f"] == res.f[it] and r["passes"] == int(res.passes[it])
+                cpu_cells += r["passes"] * float(len(qv)) * len(tv)
+        cpu = time.perf_counter() - t0
+        ach = cells * OPS_PER_CELL / best / 1e12
+        out["c5_%dx%d" % (P, K)] = {
+            "gcups": cells / best / 1e9, "ms": best * 1e3, "parity": bool(ok), "n_gpus": world,
+            "parity_how": "%d random (pair, matrix) items against the oracle's loop: f, passes, status" % len(pick),
+            "fitness_sha256_16": hashlib.sha256(fit.tobytes()).hexdigest()[:16],
+            "collective": "one NCCL all-reduce of the [blocks x K] f64 block sums" if world > 1 else "none (1 GPU)",
+            "roofline": {"bound": "fp64_add", "achieved": ach, "peak": f64.get("add_tops"), "unit": "TOP/s",
+                         "frac": ach / f64["add_tops"] if f64.get("add_tops") else None},
+            "cpu_port_gcups": cpu_cells / cpu / 1e9, "dtype": "f64",
+            "what": "sharded alnr_heuristic_batch calls (host buffers in, fitness out), max over ranks"}
+    return out
+
+
+def load_traffic(cells):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the main fill launch from the committed ncu
+    capture of THIS round's build (profiles/r02_fill_strip_traffic.json, written by
+    scripts/ncu_summary.py), scaled per cell; None when no capture is committed."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "r02_fill_strip_traffic.json")))
+        return {"bytes": cells * float(t["dram_bytes_per_cell"]), "per_cell": float(t["dram_bytes_per_cell"]),
+                "source": "profiles/r02_fill_strip_traffic.json (" + t.get("capture", "ncu --set full") + ")"}
+    except (OSError, KeyError, ValueError):
+        return None
+
+
 def main():
     a = parse()
     if a.impl == "reference":
@@ -197,6 +362,7 @@ def main():
     import aligner_b200 as ab
     from aligner_b200 import _native as N
     from aligner_b200 import workloads as W
+    import oracle_lib as O
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -211,14 +377,19 @@ def main():
     mode = N.LOCAL if a.mode == "local" else N.GLOBAL
     M = ab.dna_matrix(5, -4)
 
-    # ---- inputs: this rank's shard [rank*pairs, (rank+1)*pairs) in pinned host memory -------
+    # ---- inputs: this rank's shard [rank*pairs, (rank+1)*pairs) in pinned host memory, in both
+    # input formats (byte codes; 2-bit packed words) --------------------------------------------
     cnt, n = a.pairs, a.len
+    nw = (n + 15) // 16
     q2 = pinned_array(lib, (cnt, n), np.uint8)
     t2 = pinned_array(lib, (cnt, n), np.uint8)
-    W.dna_read_pairs_torch(rank * cnt, cnt, n, device="cuda:%d" % local, out_q=q2, out_t=t2)
+    qp = pinned_array(lib, (cnt, nw), np.uint32)
+    tp = pinned_array(lib, (cnt, nw), np.uint32)
+    W.dna_read_pairs_torch(rank * cnt, cnt, n, device="cuda:%d" % local, out_q=q2, out_t=t2, out_q2=qp, out_t2=tp)
     off = pinned_array(lib, (cnt + 1,), np.uint64)
     off[:] = np.arange(cnt + 1, dtype=np.uint64) * np.uint64(n)
     pairs = ab.PackedPairs(q2.reshape(-1), off, t2.reshape(-1), off)
+    packed = ab.Packed2Pairs(qp.reshape(-1), off, tp.reshape(-1), off)
     cells = float(cnt) * n * n
     torch.cuda.empty_cache()
 
@@ -227,76 +398,150 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---- device-resident timing (`value`) ------------------------------------------------
-    db = ab.DeviceBatch(mode, pairs, M, a.dele, a.ext, device=local)
-    l0 = lib.alnr_kernel_launch_count()
-    db.run_timed(max(a.warmup, 3), profile_fill=False)
-    launches_per_step = (lib.alnr_kernel_launch_count() - l0) // max(a.warmup, 3)
-    sampler = ClockSampler(local)
-    barrier()
-    sampler.start()
-    ms_total, _ = db.run_timed(a.steps, profile_fill=False)
-    barrier()
-    clocks = sampler.stop()
-    # roofline leg: the same steps again with every fill launch bracketed by CUDA events on its
-    # own stream.  Profiling serialises the two phases of a chunk (no overlap of the re-run
-    # passes / traceback with the next chunk's main pass), so it is kept out of `value`.
-    _, fill_total = db.run_timed(a.steps, profile_fill=True)
-    numeric = db.numeric
-    t = torch.tensor([ms_total, fill_total], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_step = float(t[0]) / a.steps
-    fill_ms_step = float(t[1]) / a.steps
-    value = cells * world / (ms_step * 1e-3) / 1e9
+    def allmax(vals):
+        t = torch.tensor(vals, dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return [float(v) for v in t]
 
-    # parity spot check of what was just timed (oracle as checker, first 512 pairs of the shard)
-    if rank == 0:
-        import oracle_lib as O
+    def device_timed(src, d, e, compact, steps, sample_clocks=False, count=None):
+        """K passes over the device-resident batch between CUDA events on the library's stream."""
+        if count is not None and count < src.count:
+            src = (ab.Packed2Pairs(src.q2[:count * nw], src.q_off[:count + 1], src.t2[:count * nw], src.t_off[:count + 1])
+                   if isinstance(src, ab.Packed2Pairs) else
+                   ab.PackedPairs(src.q[:count * n], src.q_off[:count + 1], src.t[:count * n], src.t_off[:count + 1]))
+        db = ab.DeviceBatch(mode, src, M, d, e, device=local, compact=compact)
+        l0 = lib.alnr_kernel_launch_count()
+        db.run_timed(max(a.warmup, 3), profile_fill=False)
+        lps = (lib.alnr_kernel_launch_count() - l0) // max(a.warmup, 3)
+        sampler = ClockSampler(local) if sample_clocks else None
+        barrier()
+        if sampler:
+            sampler.start()
+        ms_total, _ = db.run_timed(steps, profile_fill=False)
+        barrier()
+        clocks = sampler.stop() if sampler else None
+        # roofline leg: the same steps again with every fill launch bracketed by CUDA events on its
+        # own stream.  Profiling serialises the two phases of a chunk (no overlap of the re-run
+        # passes / traceback with the next chunk's main pass), so it is kept out of `value`.
+        _, fill_total = db.run_timed(steps, profile_fill=True)
+        ms, fill = allmax([ms_total / steps, fill_total / steps])
+        return db, ms, fill, lps, clocks
+
+    # ---- device-resident timing (`value`: the reference's result format, two byte strings) ------
+    db, ms_step, fill_ms_step, launches_per_step, clocks = device_timed(pairs, a.dele, a.ext, False, a.steps, True)
+    numeric = db.numeric
+    value = cells * world / (ms_step * 1e-3) / 1e9
+    okp, reruns = True, 0
+    if rank == 0:  # parity of what was just timed: oracle on the first pairs of the shard, every string
         res = db.download()
         reruns = int(db.rerun_count)
-        sub = W.dna_read_batch(0, 512, n)
-        ref = O.align_batch(a.mode, sub, a.dele, a.ext, M, threads=4)
-        okp = bool((res.f[:512] == ref["f"]).all() and (res.coords[:512] == ref["coords"]).all()
-                   and (res.aln_len[:512] == ref["aln_len"]).all())
-        for i in range(0, 512, 37):
-            qa, ta = res.alignment(i)
-            L = int(ref["aln_len"][i])
-            okp = okp and bool((qa == ref["q_aln"][i, :L]).all() and (ta == ref["t_aln"][i, :L]).all())
+        okp = check_against_oracle(W, O, a.mode, a.dele, a.ext, M, n, res.alignment, res.f, res.coords, res.aln_len,
+                                   0, min(a.parity_pairs, cnt))
         del res
     db.close()
+    # the same pass in the compact formats (2-bit inputs, move strings out)
+    db, ms_c, fill_c, launches_c, _ = device_timed(packed, a.dele, a.ext, True, a.steps)
+    okc = True
+    if rank == 0:
+        cr = db.download()
+        npar = min(a.parity_pairs, cnt)
+        ex = cr.expand(0, npar)
+        okc = check_against_oracle(W, O, a.mode, a.dele, a.ext, M, n, ex.alignment, cr.f, ex.coords, ex.aln_len, 0, npar)
+        del cr, ex
+    db.close()
+    value_compact = cells * world / (ms_c * 1e-3) / 1e9
 
     # ---- end to end through the public C-ABI call, host buffers in and out -------------------
-    out = ab.BatchResult.__new__(ab.BatchResult)
-    out.count = cnt
-    out.f = pinned_array(lib, (cnt,), np.float64)
-    out.corner = pinned_array(lib, (cnt,), np.float64)
-    out.coords = pinned_array(lib, (cnt, 4), np.uint64)
-    out.aln_off = pinned_array(lib, (cnt,), np.uint64)
-    out.aln_len = pinned_array(lib, (cnt,), np.uint32)
-    out.status = pinned_array(lib, (cnt,), np.int32)
-    out.q_aln = pinned_array(lib, (pairs.aln_capacity(),), np.uint8)
-    out.t_aln = pinned_array(lib, (pairs.aln_capacity(),), np.uint8)
-    # bytes that actually cross PCIe per step: the symbol codes in (equal-length batches get their
-    # offsets written on the device), and out the per-pair arrays plus the alignments back to back
-    h2d = int(pairs.q.nbytes + pairs.t.nbytes)
-    e2e_s = float("nan")
-    d2h = 0
-    if not a.no_e2e:
+    def e2e_leg(src, out, steps, count=None):
         for _ in range(3):  # warm-up
-            ab.align_batch(mode, pairs, M, a.dele, a.ext, device=local, out=out)
+            ab.align_batch(mode, src, M, a.dele, a.ext, device=local, out=out)
         barrier()
         t0 = time.perf_counter()
-        for _ in range(a.e2e_steps):
-            ab.align_batch(mode, pairs, M, a.dele, a.ext, device=local, out=out)
+        for _ in range(steps):
+            ab.align_batch(mode, src, M, a.dele, a.ext, device=local, out=out)
         torch.cuda.synchronize()
-        e2e_s = (time.perf_counter() - t0) / a.e2e_steps
-        d2h = int(2 * int(out.aln_len.astype(np.int64).sum()) + out.f.nbytes + out.corner.nbytes + out.coords.nbytes
-                  + out.aln_off.nbytes + out.aln_len.nbytes + out.status.nbytes)
-    te = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(te, op=dist.ReduceOp.MAX)
-    e2e_val = cells * world / float(te[0]) / 1e9
+        return allmax([(time.perf_counter() - t0) / steps])[0]
+
+    alloc = lambda shape, dt: pinned_array(lib, shape, dt)
+    e2e = {"value": None}
+    e2e_strings = None
+    strong = None
+    if not a.no_e2e:
+        # compact formats: 2-bit codes in; f, start cell, length, status, move-string offsets + moves out
+        cout = ab.CompactResult(packed, mode, 4, want_corner=False, want_coords=False, alloc=alloc)
+        s_c = e2e_leg(packed, cout, a.e2e_steps)
+        e2e = {"value": cells * world / s_c / 1e9, "unit": "GCUPS", "h2d_bytes_per_step": packed.bytes_in(),
+               "d2h_bytes_per_step": cout.bytes_out(), "s_per_step": s_c,
+               "format": "compact: 2-bit DNA codes in (alnr_batch.q2/.t2); f, start cell, length, status, move "
+                         "offsets and 2-bit move strings out (alnr_batch_out.moves)",
+               "timer": "host wall clock around the synchronous C-ABI call (alnr_align_batch), max over ranks"}
+        if rank == 0:
+            # what a caller does with it: expand on the host cores (lazily, or in bulk as timed here)
+            npar = min(a.parity_pairs, cnt)
+            ex = cout.expand(0, npar)
+            e2e["parity_spot_check"] = check_against_oracle(W, O, a.mode, a.dele, a.ext, M, n, ex.alignment, cout.f,
+                                                            ex.coords, ex.aln_len, 0, npar)
+            nexp = min(cnt, 1_000_000)
+            t0 = time.perf_counter()
+            cout.expand(0, nexp)
+            e2e["host_expand_pairs_per_s"] = nexp / (time.perf_counter() - t0)
+        # strong scaling (BASELINE config 3: 10M pairs sharded across N): pairs / N per GPU
+        if world > 1:
+            sc = cnt // world
+            sub_p = ab.Packed2Pairs(packed.q2[:sc * nw], off[:sc + 1], packed.t2[:sc * nw], off[:sc + 1])
+            s_s = e2e_leg(sub_p, cout, a.e2e_steps)
+            dbs, ms_s, _, _, _ = device_timed(packed, a.dele, a.ext, True, a.steps, count=sc)
+            dbs.close()
+            strong = {"pairs_total": sc * world, "pairs_per_gpu": sc, "e2e": float(sc) * world * n * n / s_s / 1e9,
+                      "e2e_s_per_step": s_s, "value_compact": float(sc) * world * n * n / (ms_s * 1e-3) / 1e9,
+                      "ms_per_step": ms_s, "unit": "GCUPS"}
+        del cout
+        if not a.no_e2e_strings:
+            out = ab.BatchResult.__new__(ab.BatchResult)
+            out.count = cnt
+            out.f = pinned_array(lib, (cnt,), np.float64)
+            out.corner = pinned_array(lib, (cnt,), np.float64)
+            out.coords = pinned_array(lib, (cnt, 4), np.uint64)
+            out.aln_off = pinned_array(lib, (cnt,), np.uint64)
+            out.aln_len = pinned_array(lib, (cnt,), np.uint32)
+            out.status = pinned_array(lib, (cnt,), np.int32)
+            out.q_aln = pinned_array(lib, (pairs.aln_capacity(),), np.uint8)
+            out.t_aln = pinned_array(lib, (pairs.aln_capacity(),), np.uint8)
+            out.end_yx = None
+            s_s = e2e_leg(pairs, out, a.e2e_steps)
+            d2h = int(2 * int(out.aln_len.astype(np.int64).sum()) + out.f.nbytes + out.corner.nbytes + out.coords.nbytes
+                      + out.aln_off.nbytes + out.aln_len.nbytes + out.status.nbytes)
+            e2e_strings = {"value": cells * world / s_s / 1e9, "unit": "GCUPS",
+                           "h2d_bytes_per_step": int(pairs.q.nbytes + pairs.t.nbytes), "d2h_bytes_per_step": d2h,
+                           "s_per_step": s_s, "format": "byte codes in, the reference's two aligned byte strings out"}
+            del out
+    if strong is None:
+        strong = {"pairs_total": cnt, "pairs_per_gpu": cnt, "e2e": e2e.get("value"), "value_compact": value_compact,
+                  "unit": "GCUPS", "note": "N = 1: identical to the weak-scaling numbers"}
+
+    int_peak = measure_int_peak(lib, local) if rank == 0 else {}
+    configs = {}
+    if not a.no_configs:
+        # C3 with the linear penalty (del == ext == 6): the other penalty setting SURVEY.md 8d names
+        dbl, ms_l, fill_l, _, _ = device_timed(pairs, 6.0, 6.0, False, max(2, a.steps // 2))
+        if rank == 0:
+            res = dbl.download()
+            npar = min(a.parity_pairs, cnt)
+            okl = check_against_oracle(W, O, a.mode, 6.0, 6.0, M, n, res.alignment, res.f, res.coords, res.aln_len, 0, npar)
+            del res
+            ach = cells * OPS_PER_CELL / (fill_l * 1e-3) / 1e12
+            tl = time.perf_counter()
+            O.align_batch(a.mode, W.dna_read_batch(0, 2048, n), 6.0, 6.0, M, threads=oracle_threads())
+            configs["c3_linear"] = {"gcups": cells * world / (ms_l * 1e-3) / 1e9, "ms": ms_l, "parity": okl,
+                                    "roofline": {"bound": "int_alu", "achieved": ach, "peak": int_peak.get("alu_tops"),
+                                                 "unit": "TOP/s", "frac": ach / int_peak["alu_tops"] if int_peak.get("alu_tops") else None},
+                                    "cpu_port_gcups": 2048.0 * n * n / (time.perf_counter() - tl) / 1e9, "n_gpus": world,
+                                    "what": "device-resident, del = ext = 6, string format"}
+        dbl.close()
+        del q2, t2, qp, tp, pairs, packed
+        lib.alnr_release_cached_memory()
+        configs.update(side_configs(a, lib, local, rank, world, int_peak, dist, torch))
 
     if rank == 0:
         peaks = {}
@@ -304,10 +549,11 @@ def main():
             peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
         except OSError:
             pass
-        int_peak = measure_int_peak(lib, local)
         achieved = cells * OPS_PER_CELL / (fill_ms_step * 1e-3) / 1e12 if fill_ms_step > 0 else None
         hbm_peak = peaks.get("hbm_gbs", 6650.0)
         d_bytes = cells * 0.25
+        traffic = load_traffic(cells)
+        peak = int_peak.get("alu_tops")
         line = {
             "metric": METRIC, "value": value, "unit": "GCUPS", "n_gpus": world, "steps": a.steps,
             "warmup": max(a.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
@@ -315,23 +561,30 @@ def main():
             "data": "synthetic",
             "config": {"workload": workload_name(a), "pairs_per_gpu": cnt, "cells_per_step_per_gpu": cells,
                        "l2": "inputs+scratch (>3 GB) exceed the 126 MB L2; no explicit flush",
-                       "parity_spot_check": okp, "host_numa": numa, "speculation_reruns_per_step": reruns},
+                       "parity_spot_check": bool(okp and okc), "parity_pairs_vs_oracle": min(a.parity_pairs, cnt),
+                       "host_numa": numa, "speculation_reruns_per_step": reruns,
+                       "value_format": "device-resident; byte codes in HBM -> the reference's two aligned byte "
+                                       "strings in HBM (value_compact: 2-bit codes -> move strings)"},
+            "value_compact": value_compact, "ms_per_step_compact": ms_c,
             "clocks": clocks, "gpu_launches": int(launches_per_step * a.steps),
-            "e2e": {"value": e2e_val, "unit": "GCUPS", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "s_per_step": float(te[0]), "timer": "host wall clock around the synchronous C-ABI call"},
-            "roofline": {"bound": "int_alu", "kernel": "fill", "achieved": achieved, "peak": int_peak.get("mixed_tops"),
-                         "unit": "TOP/s", "frac": (achieved / int_peak["mixed_tops"]) if achieved and int_peak.get("mixed_tops") else None,
+            "e2e": e2e, "e2e_strings": e2e_strings, "strong_scaling": strong,
+            "roofline": {"bound": "int_alu", "kernel": "fill_strip_kernel (+ re-run passes)", "achieved": achieved,
+                         "peak": peak, "unit": "TOP/s",
+                         "frac": (achieved / peak) if achieved and peak else None,
                          "ops_per_cell": OPS_PER_CELL, "fill_ms_per_step": fill_ms_step,
                          "fill_share_of_step": fill_ms_step / ms_step if ms_step else None,
-                         "peak_source": "measured in this run (alnr_measure_int_peak: IADD3/VIMNMX + IMAD chains, 148 SMs)",
-                         "alu_only_peak_tops": int_peak.get("alu_tops"),
-                         # dram__bytes_read.sum + dram__bytes_write.sum of the main fill launch, scaled
-                         # from the one --set full capture (profiles/r01_fill_strip_ncu.txt:
-                         # 1.47 + 7.81 GB for 10^6 pairs = 0.412 B/cell, algorithmic 0.25 B/cell)
-                         "traffic": cells * NCU_DRAM_BYTES_PER_CELL,
+                         "peak_source": "measured in this run (alnr_measure_int_peak: independent IADD3/VIMNMX/LOP3 "
+                                        "chains on the alu pipe, 148 SMs; SURVEY.md 8d); MEASURED_PEAKS.json holds no "
+                                        "integer peak",
+                         "mixed_alu_fma_peak_tops": int_peak.get("mixed_tops"),
+                         "frac_of_mixed_peak": (achieved / int_peak["mixed_tops"]) if achieved and int_peak.get("mixed_tops") else None,
+                         "traffic": traffic["bytes"] if traffic else None,
+                         "traffic_source": traffic["source"] if traffic else "no ncu capture of this build committed",
                          "hbm": {"achieved": d_bytes / (fill_ms_step * 1e-3) / 1e9 if fill_ms_step else None,
                                  "peak": hbm_peak, "unit": "GB/s", "algorithmic_bytes": d_bytes,
-                                 "note": "2-bit direction matrix writes, 0.25 B/cell; peak of measured" if peaks else "of fallback"}},
+                                 "note": "2-bit direction matrix writes, 0.25 B/cell; peak " +
+                                         ("from MEASURED_PEAKS.json" if peaks else "fallback of B200_PROFILING.md")}},
+            "configs": configs,
         }
         if not a.no_cpu_baseline:
             if _ALL_CPUS:
@@ -344,6 +597,13 @@ def main():
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def measure_fp64_peak(lib, device):
+    add, mix = C.c_double(), C.c_double()
+    if lib.alnr_measure_fp64_peak(device, C.byref(add), C.byref(mix)) != 0:
+        return {}
+    return {"add_tops": add.value / 1e12, "addmax_tops": mix.value / 1e12}
 
 
 def measure_int_peak(lib, device):

@@ -115,6 +115,15 @@ typedef struct {
   const uint8_t *t;      /* concatenated target codes */
   const uint64_t *t_off; /* count+1 offsets */
   uint64_t count;
+  /* Opt-in compact input (alnr_align_batch / alnr_batch_create* / alnr_score_batch only; V == 4):
+   * 2-bit DNA codes, 16 per 32-bit word, code k of a sequence at bits [2 * (k % 16), +2) of its word
+   * k / 16; every sequence starts on a word boundary, sequences densely one after the other (sequence
+   * i starts at word sum_{j<i} ceil(len_j / 16)); unused high bits of a last word are ignored.  Set
+   * both or neither; when set, q / t are ignored and may be NULL.  q_off / t_off keep their meaning
+   * (symbol offsets, i.e. the lengths).  A binding that walks Vec<DNA> (aligner-core/src/enums.rs:
+   * 138-147) to produce byte codes can pack 2 bits instead: 4x fewer bytes cross PCIe. */
+  const uint32_t *q2;
+  const uint32_t *t2;
 } alnr_batch;
 
 /* Caller-provided output arrays (host memory; pinned memory makes copies faster).
@@ -133,7 +142,35 @@ typedef struct {
   uint8_t *q_aln;
   uint8_t *t_aln;
   int32_t *status;     /* [count] per-pair status (EMPTY_INPUT, NO_POSITIVE_CELL, ...) */
+  /* Opt-in compact result format: set `moves` (then q_aln / t_aln / aln_off must be NULL).  The
+   * alignment of pair i is returned as the walk the reference's traceback takes
+   * (simple/mod.rs:107-127, :220-242): start cell end_yx[2i], end_yx[2i+1] = 1-based (target,
+   * query) index of the LAST aligned column (the arg-max in local mode, (m, n) in global mode) and
+   * aln_len[i] - 1 moves, move k = Direction of the k-th step away from that cell (0 Top, 1 Left,
+   * 2 Diagonal), 2 bits per move, 16 per word, move k at bits [2 * (k % 16), +2) of word
+   * moves_off[i] + k / 16.  Move strings are dense: moves_off[i] = sum_{j<i} ceil((aln_len[j] - 1)
+   * / 16) (pairs with a status own no words).  `moves` needs alnr_moves_capacity() words.
+   * Alignment.query / .target are private to aligner-core (alignment.rs:6-7): callers see coords,
+   * f, get_frequency_matrix() and get_alignment() — all of which alnr_expand_alignments() (or a
+   * lazily expanding binding) derives from this record; ~70 B instead of ~390 B per 150 bp pair. */
+  uint32_t *end_yx;    /* [count*2]; also available in the string format */
+  uint64_t *moves_off; /* [count], optional */
+  uint32_t *moves;
 } alnr_batch_out;
+
+/* Words `moves` must hold for this batch (worst case ceil((n_i + m_i) / 16) per pair). */
+uint64_t alnr_moves_capacity(const alnr_batch *b);
+
+/* Host-side expansion of the compact format (threads <= 0: all host cores).  For the pairs
+ * [first, first + count) of batch b (byte or 2-bit inputs) it writes, indexed by i - first: coords,
+ * aln_len, aln_off (alignments back to back from 0, needs sum of aln_len bytes; when the strings
+ * are NULL only coords / aln_off are produced), q_aln, t_aln exactly as the string format would
+ * (the seeded last column included, simple/mod.rs:102-105), and optionally the V x V frequency
+ * matrices of Alignment::get_frequency_matrix (alignment.rs:13-23), freq[(i - first) * V * V ...].
+ * compact->moves_off may be NULL only when first == 0 (offsets are then re-derived). */
+int alnr_expand_alignments(int mode, int volume, const alnr_batch *b, const alnr_batch_out *compact,
+                           uint64_t first, uint64_t count, alnr_batch_out *expanded, double *freq,
+                           int threads);
 
 /* Host buffers in, host buffers out (H2D + kernels + D2H, chunked and overlapped). */
 int alnr_align_batch(const alnr_params *p, const alnr_batch *b, alnr_batch_out *out);
@@ -141,6 +178,9 @@ int alnr_align_batch(const alnr_params *p, const alnr_batch *b, alnr_batch_out *
 /* Device-resident form of the same call: upload once, run many times, download. */
 typedef struct alnr_batch_handle alnr_batch_handle;
 int alnr_batch_create(const alnr_params *p, const alnr_batch *b, alnr_batch_handle **h);
+/* Same, but the traceback stops at the 2-bit move strings (compact result format, see
+ * alnr_batch_out.moves); read with alnr_batch_download and `moves` set. */
+int alnr_batch_create_compact(const alnr_params *p, const alnr_batch *b, alnr_batch_handle **h);
 int alnr_batch_run(alnr_batch_handle *h);               /* kernels only, asynchronous */
 int alnr_batch_sync(alnr_batch_handle *h);
 int alnr_batch_download(alnr_batch_handle *h, alnr_batch_out *out);
