@@ -154,6 +154,7 @@ StripPlan strip_plan(alnr_batch_impl &B, const Chunk &c, const ChunkView &cv, co
     a.wtab[qs] = w;
   }
   a.del = (int)B.del; a.ext = (int)B.ext;
+  a.k_one = 1u; a.k_mone = 0xffffffffu; a.k_bias = kBias; a.k_one2 = 0x00010001u;
   {
     double top = 0.0;
     for (double v : B.matrix) top = std::max(top, v);

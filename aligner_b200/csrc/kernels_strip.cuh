@@ -52,6 +52,8 @@ struct StripArgs {
   // (rerun_strip0_kernel): [((vduo >> 5) * n + x-1) * 32 + (vduo & 31)], pair A in the low half
   uint32_t *brow0;
   uint32_t *hglobal;           // strip boundary rows in global memory (nullptr: shared memory)
+  uint32_t k_one, k_mone;      // 1 and 0xffffffff: opaque multipliers that keep three lane-wise adds on the fma pipe
+  uint32_t k_bias, k_one2;     // 0x80008000 and 0x00010001 as values ptxas cannot re-materialise per use
   uint32_t vblocks;            // virtual blocks of kStripBlock duos (the grid may be smaller)
 };
 
@@ -100,30 +102,54 @@ __device__ __forceinline__ uint32_t first_rows_equal(const uint32_t (&h)[R], uin
   const uint32_t ea = ~eq & valid, eb = ~(eq >> 16) & valid;
   return (uint32_t)(__ffs(ea) - 1) | ((uint32_t)(__ffs(eb) - 1) << 16);
 }
+
+// Scores are kept BIASED inside the sweep: h' = h + 0x8000 in each 16-bit lane (h' = h ^ kBias), so
+// that unsigned order = signed order and every lane value is >= 0.  Then the three steps of a cell
+// that are plain differences of lane values which cannot borrow,
+//    gl = g - penalty        (gl' >= 0: |H| < 2^15 - margin is proven by the host, batch.cu::classify)
+//    mx - gl >= 0,  g - h_up >= 0   (the arguments of the flag tests "diagonal wins", "left beats top")
+// are exact as ONE 32-bit multiply-add each, which the fma pipe executes (IMAD with the opaque
+// multipliers k_one / k_mone of StripArgs, so that ptxas cannot turn them back into alu-pipe
+// IADD3 / LOP3): the alu pipe — the bound of this kernel — issues 6.5 instead of 9.5 instructions
+// per cell pair (PRMT, 2 max, 3 min-against-1, half a max3).
+constexpr uint32_t kBias = 0x80008000u;
+__device__ __forceinline__ uint32_t imad32(uint32_t a, uint32_t k, uint32_t b) {
+  uint32_t d;
+  asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(k), "r"(b));
+  return d;
+}
+
 // One strip of R rows swept over all columns.  LASTSTRIP: the strip holding row m (it may
 // have fewer than R valid rows); only there are z bits observed and the corner recorded.
 //
-// Per cell (two pairs at once): PRMT score, 2 VIADD.16x2 (top/left minus penalty),
-// VIADDMNMX.S16x2 + VIMNMX.S16x2 (max of three), 2 XOR + 3 VIMNMX.U16x2 against 1 (the flags
-// "max != top", "max != left", "max != 0" as 0/1 per lane), one VIMNMX for the column max,
-// and on the fma pipe 3 shift-accumulates of the flags into row bit-planes plus the next
-// penalty (nz * (del-ext) - del).  Direction codes are formed once per COLUMN from the three
-// planes: P0 = Z | (T & ~L), P1 = Z | (T & L)  (code = P0 + 2*P1: 0 Top, 1 Left, 2 Diagonal,
-// 3 Beginning; enums.rs:18-46), stored as one word per pair: P0 in the low, P1 in the high
-// 16 bits ("plane" D format).
+// Per cell (two pairs at once): alu pipe PRMT score, VIMNMX.U16x2 (max of H_up, H_left),
+// VIADDMNMX.U16x2 (diag + s against the gap candidate), 3 VIMNMX / VIADDMNMX.U16x2 against 1 (the
+// flags "max != gap candidate", "H_left > H_up", "max != 0" as 0/1 per lane), half a VIMNMX3 for the
+// column max; fma pipe: the penalty subtraction, the two flag differences, 3 shift-accumulates of
+// the flags into row bit-planes and the next penalty (nz * (del-ext) - del).  Direction codes are
+// formed once per COLUMN from the three planes: P0 = Z | (T & ~L), P1 = Z | (T & L)  (code =
+// P0 + 2*P1: 0 Top, 1 Left, 2 Diagonal, 3 Beginning; enums.rs:18-46), stored as one word per pair:
+// P0 in the low, P1 in the high 16 bits ("plane" D format).
+// Two columns per loop trip with the strip's scores ping-ponging between two register arrays: the
+// old H[y][x-1] (still needed as the diagonal of row y+1) and the new H[y][x] never compete for a
+// register, so no moves are left in the loop.
 // SCORE: score-only calls (alnr_score_batch) — no direction planes are formed and nothing is
-// written to the D scratch; the cell is PRMT + max + add + add-max (+ the column max).
+// written to the D scratch.
 template <int R, bool LOCAL, bool STATEFUL, bool LASTSTRIP, bool SCORE>
 __device__ __forceinline__ void strip_sweep(const StripArgs &a, StripCtx &c, const uint32_t *swt,
                                             uint32_t strip) {
   const uint32_t n = a.n, m = a.m;
   const uint32_t y0 = strip * R;
   const uint32_t rv = LASTSTRIP ? m - y0 : R;  // valid rows
-  const uint32_t ndel2 = pack2(-a.del, -a.del), next2 = pack2(-a.ext, -a.ext);
+  // penalties as 32-bit NEGATIVES of the packed positive values: x + nd32 = x - (del, del) lane-wise
+  // as long as no lane borrows (see above)
+  const uint32_t pd32 = (uint32_t)a.del * 0x00010001u, pe32 = (uint32_t)a.ext * 0x00010001u;
+  const uint32_t nd32 = 0u - pd32, ne32 = 0u - pe32;
   const uint32_t dme = (uint32_t)(a.del - a.ext);
-  const uint32_t one2 = 0x00010001u;
+  const uint32_t one2 = a.k_one2, kb = a.k_bias;  // == 0x00010001, kBias (kept in registers)
+  const uint32_t k1 = a.k_one, km1 = a.k_mone;
 
-  uint32_t sel[R], h[R];
+  uint32_t sel[R], hA[R], hB[R];
 #pragma unroll
   for (int r = 0; r < R; ++r) {
     const uint32_t y = y0 + r;  // 0-based target index
@@ -131,13 +157,14 @@ __device__ __forceinline__ void strip_sweep(const StripArgs &a, StripCtx &c, con
     sel[r] = ta | ((8u | ta) << 4) | ((4u + tb) << 8) | ((12u + tb) << 12);
     int v = 0;
     if (!LOCAL) v = (y + 1 == m) ? -(int)(m + 1) * a.del : -(int)(y + 1) * a.del;  // :64-67,:70
-    h[r] = pack2(v, v);
+    hA[r] = pack2(v, v) ^ kBias;
+    hB[r] = hA[r];
   }
   // H[y0][0]: 0 in local mode, -y0*del in global mode (the -(m+1)*del quirk sits on row m only)
-  uint32_t hdiag0 = LOCAL ? 0u : pack2(-(int)y0 * a.del, -(int)y0 * a.del);
+  uint32_t hdiag0 = (LOCAL ? 0u : pack2(-(int)y0 * a.del, -(int)y0 * a.del)) ^ kBias;
   int thrA = (c.bestA.strip == (int)strip) ? c.bestA.v : c.bestA.v + 1;
   int thrB = (c.bestB.strip == (int)strip) ? c.bestB.v : c.bestB.v + 1;
-  uint32_t nthr = pack2(-thrA, -thrB);
+  uint32_t nthr = pack2(-thrA, -thrB) ^ kBias;  // cm' + nthr = cm - thr lane-wise (the biases cancel)
   uint32_t zacc = 0, zaccB = 0;
   uint32_t qwA = 0, qwB = 0;
   uint32_t *dpA = c.dA + (size_t)strip * a.dl.ncols, *dpB = c.dB + (size_t)strip * a.dl.ncols;
@@ -146,8 +173,7 @@ __device__ __forceinline__ void strip_sweep(const StripArgs &a, StripCtx &c, con
   const uint32_t hstride = c.hstride;
   uint32_t hnext = *hp;  // one column ahead: hides the L2 latency when the row lives in global memory
 
-#pragma unroll 1
-  for (uint32_t xm1 = 0; xm1 < n; ++xm1, hp += hstride) {
+  auto column = [&](const uint32_t (&hin)[R], uint32_t (&h)[R], const uint32_t xm1) {
     const uint32_t x = xm1 + 1;
     if ((xm1 & 15) == 0) { qwA = c.qA[(size_t)(xm1 >> 4) * 32]; qwB = c.qB[(size_t)(xm1 >> 4) * 32]; }
     const uint32_t Wa = swt[qwA & 3], Wb = swt[qwB & 3];
@@ -165,45 +191,45 @@ __device__ __forceinline__ void strip_sweep(const StripArgs &a, StripCtx &c, con
           zA = (a.z_in[(size_t)c.sA * a.nzw + ((x - 2) >> 5)] >> ((x - 2) & 31)) & 1;
           zB = (a.z_in[(size_t)c.sB * a.nzw + ((x - 2) >> 5)] >> ((x - 2) & 31)) & 1;
         }
-        np = pack2(zA ? -a.del : -a.ext, zB ? -a.del : -a.ext);
+        np = 0u - ((uint32_t)(zA ? a.del : a.ext) | ((uint32_t)(zB ? a.del : a.ext) << 16));
       } else {
-        np = __vminu2(hup, one2) * dme + ndel2;  // cell above: Beginning iff == 0
+        np = __viaddmin_u16x2(hup, kb, one2) * dme + nd32;  // cell above: Beginning iff == 0
       }
     } else {
-      np = (!LOCAL && strip == 0 && x == 1) ? ndel2 : next2;  // simple/mod.rs:72: first cell pays del
+      np = (!LOCAL && strip == 0 && x == 1) ? nd32 : ne32;  // simple/mod.rs:72: first cell pays del
     }
-    uint32_t accG = 0, accU = 0, accN = 0, cm = 0x80008000u, mprev = 0x80008000u;
-    uint32_t hlast = 0;  // SCORE: H[m][x] of both pairs (its zero flag is the z bit)
+    uint32_t accG = 0, accU = 0, accN = 0, cm = 0u, mprev = 0u;
+    uint32_t hlast = kBias;  // SCORE: H[m][x] of both pairs (its zero flag is the z bit)
 #pragma unroll
     for (int r = 0; r < R; ++r) {
-      // max(top, left) = max(H_up, H_left) - penalty: one max + one add instead of two adds
+      // max(top, left) = max(H_up, H_left) - penalty: one max + one subtraction instead of two
       const uint32_t s = prmt_sx(Wa, Wb, sel[r]);
-      const uint32_t g = __vmaxs2(hup, h[r]);
-      const uint32_t gl = __vadd2(g, np);
-      const uint32_t mx = __viaddmax_s16x2(diag, s, gl);
+      const uint32_t g = __vmaxu2(hup, hin[r]);
+      const uint32_t gl = imad32(g, k1, np);               // g - penalty (fma pipe)
+      const uint32_t mx = __viaddmax_u16x2(diag, s, gl);   // max(diag + s, gl), biased
       if (!SCORE) {
-        accG += __vminu2(mx ^ gl, one2) << r;   // 1: neither gap move reaches the max -> Diagonal
-        accU += __vminu2(g ^ hup, one2) << r;   // 1: H_left > H_up -> Left beats Top (Top wins ties)
+        accG += __vminu2(imad32(gl, km1, mx), one2) << r;   // mx - gl != 0: neither gap move reaches the max
+        accU += __vminu2(imad32(hup, km1, g), one2) << r;   // g - H_up != 0: H_left > H_up (Top wins ties)
       }
       if (LOCAL && (!SCORE || STATEFUL)) {
-        const uint32_t nz = __vminu2(mx, one2);
+        const uint32_t nz = __viaddmin_u16x2(mx, kb, one2);  // min(H mod 2^16, 1)
         if (!SCORE) accN += nz << r;
-        if (STATEFUL) np = nz * dme + ndel2;  // simple/mod.rs:201-205
+        if (STATEFUL) np = nz * dme + nd32;  // simple/mod.rs:201-205
       }
       if (SCORE && STATEFUL && LASTSTRIP) { if ((uint32_t)r + 1 == rv) hlast = mx; }
-      if (!STATEFUL) np = next2;
-      diag = h[r];
+      if (!STATEFUL) np = ne32;
+      diag = hin[r];
       h[r] = mx;
       hup = mx;
       if (LOCAL) {
         // column maximum over the valid rows, two rows per 3-input max
         if (!LASTSTRIP || (uint32_t)r < rv) {
-          if (r & 1) cm = __vimax3_s16x2(cm, mprev, mx); else mprev = mx;
+          if (r & 1) cm = __vimax3_u16x2(cm, mprev, mx); else mprev = mx;
         }
       }
     }
     // an odd number of valid rows leaves the last one pending in mprev
-    if (LOCAL) { if (LASTSTRIP ? (rv & 1u) : (R & 1)) cm = __vmaxs2(cm, mprev); }
+    if (LOCAL) { if (LASTSTRIP ? (rv & 1u) : (R & 1)) cm = __vmaxu2(cm, mprev); }
     if (!LASTSTRIP) *hp = h[R - 1];
     // direction planes of this column (both pairs at once), then one word per pair:
     // Top = !G & !U, Left = !G & U, Diagonal = G, Beginning = Z  (enums.rs:18-46)
@@ -225,7 +251,8 @@ __device__ __forceinline__ void strip_sweep(const StripArgs &a, StripCtx &c, con
       // sits in an earlier strip: ties there win by smaller y)
       const uint32_t dlt = __vadd2(cm, nthr);
       if ((dlt & 0x80008000u) != 0x80008000u) {
-        const int cA = lane_lo(cm), cB = lane_hi(cm);
+        const uint32_t cmu = cm ^ kBias;
+        const int cA = lane_lo(cmu), cB = lane_hi(cmu);
         const uint32_t r0 = first_rows_equal<R>(h, cm, rv);
         if (cA >= thrA) {
           const uint32_t y = y0 + (r0 & 0xffffu) + 1;
@@ -235,12 +262,12 @@ __device__ __forceinline__ void strip_sweep(const StripArgs &a, StripCtx &c, con
           const uint32_t y = y0 + (r0 >> 16) + 1;
           if (cB > c.bestB.v || y < c.bestB.y) { c.bestB = Best{cB, y, x, (int)strip}; thrB = cB; }
         }
-        nthr = pack2(-thrA, -thrB);
+        nthr = pack2(-thrA, -thrB) ^ kBias;
       }
     }
     if (STATEFUL && LASTSTRIP) {
       // observe z[x-1] = (H[m][x] == 0); it sets the penalty of cell (1, x+1)
-      const uint32_t z = SCORE ? ~__vminu2(hlast, one2) : ~(accN >> (rv - 1));
+      const uint32_t z = SCORE ? ~__viaddmin_u16x2(hlast, kb, one2) : ~(accN >> (rv - 1));
       zacc |= (z & 1u) << (xm1 & 31);
       zaccB |= ((z >> 16) & 1u) << (xm1 & 31);
       if ((xm1 & 31) == 31 || x == n) {
@@ -266,6 +293,19 @@ __device__ __forceinline__ void strip_sweep(const StripArgs &a, StripCtx &c, con
         zacc = zaccB = 0;
       }
     }
+    hp += hstride;
+  };
+
+  uint32_t xm1 = 0;
+#pragma unroll 1
+  for (; xm1 + 1 < n; xm1 += 2) {
+    column(hA, hB, xm1);
+    column(hB, hA, xm1 + 1);
+  }
+  if (xm1 < n) {  // odd n: the last column lands in hB
+    column(hA, hB, xm1);
+#pragma unroll
+    for (int r = 0; r < R; ++r) hA[r] = hB[r];
   }
   // flush a partial group of D words (n not a multiple of 4)
   if (!SCORE && (n & 3)) {
@@ -274,14 +314,15 @@ __device__ __forceinline__ void strip_sweep(const StripArgs &a, StripCtx &c, con
     if (!c.dupB) __stcs(reinterpret_cast<uint4 *>(dpB + (n & ~3u)), make_uint4(b0, b1, b2, b3));
   }
   if (LASTSTRIP) {
-    c.corner = h[R - 1];
+    c.corner = hA[R - 1];
 #pragma unroll
-    for (int r = 0; r < R - 1; ++r) if ((uint32_t)r + 1 == rv) c.corner = h[r];
+    for (int r = 0; r < R - 1; ++r) if ((uint32_t)r + 1 == rv) c.corner = hA[r];
+    c.corner ^= kBias;
   }
 }
 
 template <int R, bool LOCAL, bool STATEFUL, bool SCORE = false>
-__global__ void __launch_bounds__(kStripBlock) fill_strip_kernel(StripArgs a) {
+__global__ void __launch_bounds__(kStripBlock, 8) fill_strip_kernel(StripArgs a) {
   extern __shared__ uint32_t smem_h[];
   __shared__ uint32_t swt[4];
   const uint32_t tid = threadIdx.x;
@@ -334,7 +375,7 @@ __global__ void __launch_bounds__(kStripBlock) fill_strip_kernel(StripArgs a) {
   for (uint32_t x = 1; x <= n; ++x) {
     int hv = 0;
     if (!LOCAL) hv = (x == n) ? -(int)(n + 1) * a.del : -(int)x * a.del;
-    c.hrow[(size_t)(x - 1) * c.hstride] = pack2(hv, hv);
+    c.hrow[(size_t)(x - 1) * c.hstride] = pack2(hv, hv) ^ kBias;
   }
 
   for (uint32_t strip = 0; strip + 1 < nstrips; ++strip) {
@@ -408,7 +449,7 @@ __global__ void __launch_bounds__(kStripBlock) rerun_strip0_kernel(StripArgs a) 
     c.bestB = Best{0, 0, 0, -1};
     c.mismatch = 0;
     c.corner = 0;
-    for (uint32_t x = 0; x < n; ++x) c.hrow[(size_t)x * 32] = 0u;  // row 0 (local)
+    for (uint32_t x = 0; x < n; ++x) c.hrow[(size_t)x * 32] = kBias;  // row 0 (local), biased
     strip_sweep<R, true, true, false, SCORE>(a, c, swt, 0);
 
     // the kept bottom row of a slot: its duo in the speculative pass, low or high half
