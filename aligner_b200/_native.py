@@ -87,6 +87,9 @@ SIGNATURES = {
                                   C.POINTER(PairResult)]),
     "alnr_free_pair_result": (None, [C.POINTER(PairResult)]),
     "alnr_align_batch": (C.c_int, [C.POINTER(Params), C.POINTER(Batch), C.POINTER(BatchOut)]),
+    "alnr_align_batch_multi": (C.c_int, [C.POINTER(Params), C.POINTER(Batch), C.POINTER(BatchOut), C.c_int]),
+    "alnr_matrix_search_multi": (C.c_int, [C.POINTER(Params), C.POINTER(Batch), f64p, C.c_uint32, C.c_double,
+                                           C.c_double, f64p, f64p, u32p, f64p, f64p, i32p, C.c_int]),
     "alnr_batch_create": (C.c_int, [C.POINTER(Params), C.POINTER(Batch), C.POINTER(C.c_void_p)]),
     "alnr_batch_create_compact": (C.c_int, [C.POINTER(Params), C.POINTER(Batch), C.POINTER(C.c_void_p)]),
     "alnr_moves_capacity": (C.c_uint64, [C.POINTER(Batch)]),

@@ -212,9 +212,10 @@ def make_params(mode, matrix, del_, ext, device=-1, numeric=N.NUM_AUTO):
 
 
 def align_batch(mode, pairs, matrix, del_, ext, device=-1, numeric=N.NUM_AUTO, want_alignments=True,
-                out=None, compact=False):
+                out=None, compact=False, n_gpus=None):
     """Host buffers in -> host buffers out (alnr_align_batch).  ``pairs``: PackedPairs (byte codes)
-    or Packed2Pairs (2-bit DNA).  ``compact``: return a CompactResult (move strings)."""
+    or Packed2Pairs (2-bit DNA).  ``compact``: return a CompactResult (move strings).  ``n_gpus``:
+    shard the batch over that many devices inside the library (alnr_align_batch_multi; 0 = all)."""
     p = make_params(mode, matrix, del_, ext, device, numeric)
     if out is not None:
         res = out
@@ -224,7 +225,10 @@ def align_batch(mode, pairs, matrix, del_, ext, device=-1, numeric=N.NUM_AUTO, w
         res = BatchResult(pairs, want_alignments)
     b = pairs.c_struct()
     o = res.c_struct()
-    N.check(N.lib().alnr_align_batch(C.byref(p), C.byref(b), C.byref(o)))
+    if n_gpus is None:
+        N.check(N.lib().alnr_align_batch(C.byref(p), C.byref(b), C.byref(o)))
+    else:
+        N.check(N.lib().alnr_align_batch_multi(C.byref(p), C.byref(b), C.byref(o), int(n_gpus)))
     return res
 
 

@@ -224,6 +224,8 @@ int alnr_batch_impl::plan_chunks(const uint64_t *q_off, const uint64_t *t_off) {
       const uint64_t pidx = uniform ? s : order[s];
       ck.wave = true; ck.wave_pair = (uint32_t)pidx; ck.q0 = q_off[pidx]; ck.t0 = t_off[pidx];
       ck.q1 = q_off[pidx + 1]; ck.t1 = t_off[pidx + 1];
+      // a direction matrix larger than the scratch budget: keep band rows, re-fill group by group
+      if (!score_only && wave_band_rows(m) == 4 && !getenv("ALNR_BAND_COLUMN")) ck.ckpt_group = wave_ckpt_group(m, n, budget);
     } else
     if (uniform) { ck.q0 = q_off[s]; ck.q1 = q_off[s + c]; ck.t0 = t_off[s]; ck.t1 = t_off[s + c]; }
     chunks.push_back(ck);
@@ -254,7 +256,10 @@ DLayout alnr_batch_impl::layout_dims(uint32_t m, uint32_t n, bool wave) const {
   return DLayout::make(d_rows_per_word(*this, m), m, n, numeric == ALNR_NUM_I16X2);
 }
 
-DLayout alnr_batch_impl::layout_for(const Chunk &c) const { return layout_dims(c.m_max, c.n_max, c.wave); }
+DLayout alnr_batch_impl::layout_for(const Chunk &c) const {
+  if (c.ckpt_group) return DLayout::make_blocked(4, std::min<uint64_t>(c.m_max, (uint64_t)c.ckpt_group * 128), c.n_max);
+  return layout_dims(c.m_max, c.n_max, c.wave);
+}
 
 // Compact alignment output: identity pair order (uniform batch, so a chunk is a contiguous
 // region of q_aln / t_aln) and move strings short enough for the two-phase traceback.
@@ -624,7 +629,9 @@ int alnr_batch_impl::moves_from_strings() {
 // the caller only ever has to synchronise `stream`.
 int alnr_batch_impl::run_chunk(size_t ci) {
   static const bool serial_env = getenv("ALNR_SERIAL_PHASES") != nullptr;
-  const bool overlap = chunks.size() > 1 && !profile && !serial_env;
+  // a checkpointed pair re-fills from the band rows in its second phase: the next long pair's first
+  // phase must not overwrite them, so that chunk stays on one stream
+  const bool overlap = chunks.size() > 1 && !profile && !serial_env && !chunks[ci].ckpt_group;
   s2 = overlap ? stream2 : stream;
   par = chunks.size() > 1 ? (int)(ci & 1) : 0;
   if (overlap && ci >= 2) ALNR_CUDA(cudaStreamWaitEvent(stream, ev_p2[ci - 2], 0));
@@ -666,7 +673,7 @@ int alnr_batch_impl::phase1(size_t ci) {
   ALNR_LAUNCHED();
   int st = fill_mark(false);
   if (st) return st;
-  if (c.wave) st = wave_run_pair(*this, c, dl, fo);
+  if (c.wave) st = wave_run_pair(*this, c, c.ckpt_group ? layout_dims(c.m_max, c.n_max, true) : dl, fo);
   else if (numeric == ALNR_NUM_F64 && dl.skewed) st = launch_warp<double>(*this, c, cv, dl, fo, hcol_d(), d_matd.p);
   else if (numeric == ALNR_NUM_I32 && dl.skewed) st = launch_warp<int>(*this, c, cv, dl, fo, hcol_i(), d_mati.p);
   else if (numeric == ALNR_NUM_F64) st = launch_exact<double>(*this, c, cv, dl, fo, hcol_d(), d_matd.p);
@@ -722,6 +729,8 @@ int alnr_batch_impl::phase2(size_t ci) {
     const uint32_t G = trace_expand_group(c.n_max, c.m_max);
     trace_expand_kernel<<<(c.count + G - 1) / G, kExpandThreads, trace_expand_smem(G, c.n_max, c.m_max), s2>>>(
         ta, d_moves.p, cxy, stride, G, c.n_max, c.m_max, nmw);
+  } else if (c.ckpt_group) {
+    return wave_ckpt_trace(*this, c, dl, ta, s2);
   } else if (dl.blocked == 4 && c.count == 1 && !getenv("ALNR_TRACE_LOCKSTEP")) {
     // long pair, 4 x 4 tiles: window walk that emits moves, then a parallel expansion
     LongTrace lt{d_moves.p, d_moves.p + nmw, d_moves.p + 3 * (size_t)nmw};

@@ -14,6 +14,7 @@ struct Chunk {
   uint64_t q0, q1, t0, t1;    // symbol ranges of the chunk (identity order only)
   bool wave = false;          // one long pair: intra-pair wavefront kernel
   uint32_t wave_pair = 0;     // its pair index; q0/t0 = its symbol offsets
+  uint32_t ckpt_group = 0;    // > 0: checkpointed traceback, the D scratch holds this many bands
 };
 
 struct alnr_batch_impl {
@@ -70,6 +71,7 @@ struct alnr_batch_impl {
   DevBuf<double> d_f, d_corner, d_matd, d_Hout, d_hcol_d;
   DevBuf<int> d_mati, d_hcol_i;
   DevBuf<int> d_band;           // band pipeline kernel: reduction cells, progress words, band rows
+  DevBuf<uint32_t> d_ckpt;      // checkpointed traceback: state of the walk between band groups
   DevBuf<uint32_t> d_pack;      // packed sequences for the strip kernel
   DevBuf<uint32_t> d_brow;      // strip kernel: kept bottom rows of strip 0 (incremental re-run), per parity
   uint64_t brow_words = 0;

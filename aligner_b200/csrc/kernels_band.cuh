@@ -43,6 +43,14 @@ struct BandArgs {
   uint32_t dcols;         // words per 4-row strip
   unsigned long long *best;  // local: packed (value | ~y | ~x) maximum
   int *corner_out;        // H[m][n]
+  // Checkpointed traceback (tile kernel only; wave.cu): a RE-FILL computes the bands
+  // [band0, band_end) again, reading every band's top boundary row from the rows the first pass
+  // kept (all final: no waiting, the bands run side by side) and writing their directions to a
+  // scratch that holds only this group's strips (strip index - strip0).  ckpt != nullptr: the launch
+  // first looks at the walk's state and returns when the path does not cross the group.
+  uint32_t band0 = 0, band_end = 0;   // band_end == 0: all bands (first pass)
+  uint32_t strip0 = 0;
+  const uint32_t *ckpt = nullptr;     // CkptState words: [0] cy, [1] cx, [4] done
 };
 
 __device__ __forceinline__ unsigned long long band_key(int v, uint32_t y, uint32_t x) {

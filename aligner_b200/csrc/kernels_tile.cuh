@@ -167,8 +167,14 @@ __global__ void __launch_bounds__(32) fill_tile_kernel(BandArgs a) {
   const int del = a.del, ext = a.ext;
   TileLane L;
   L.best_v = 0; L.best_y = 0; L.best_x = 0;
+  const bool refill = a.band_end != 0;  // checkpointed traceback: bands [band0, band_end), rows are final
+  const uint32_t band_end = refill ? a.band_end : a.nbands;
+  if (a.ckpt) {  // the path crosses this group iff its current cell lies inside the group's rows
+    const uint32_t cy = a.ckpt[0], cx = a.ckpt[1], done = a.ckpt[4];
+    if (done || cx == 0 || cy <= a.band0 * 128u || cy > band_end * 128u) return;
+  }
 
-  for (uint32_t band = blockIdx.x; band < a.nbands; band += gridDim.x) {
+  for (uint32_t band = a.band0 + blockIdx.x; band < band_end; band += gridDim.x) {
     const uint32_t yl0 = band * 128u + lane * 4u;  // this lane's rows: yl0+1 .. yl0+4 (1-based)
     uint32_t trow[4];
 #pragma unroll
@@ -193,8 +199,8 @@ __global__ void __launch_bounds__(32) fill_tile_kernel(BandArgs a) {
     const int *top_row = band ? a.rows + (size_t)(band - 1) * npad : nullptr;
     const bool store_d = yl0 < m && a.D != nullptr;  // score-only calls pass no D scratch
     const bool last_band = band + 1 == a.nbands;
-    const bool row_out = lane == 31 && !last_band;
-    L.dptr = a.D + (size_t)(yl0 / 4) * a.dcols;  // this lane's 4-row strip
+    const bool row_out = lane == 31 && !last_band && !refill;
+    L.dptr = a.D + (size_t)(yl0 / 4 - a.strip0) * a.dcols;  // this lane's 4-row strip
     L.rowp = a.rows + (size_t)band * npad;
     const uint32_t steps = ntiles + 31;
     // A band cannot start before the band above has finished its first chunk, i.e. ~39 steps per
@@ -262,10 +268,10 @@ __global__ void __launch_bounds__(32) fill_tile_kernel(BandArgs a) {
       }
     }
     TILE_STAMP(5);
-    if (last_band && L.has_corner) *a.corner_out = L.corner;
+    if (last_band && L.has_corner && !refill) *a.corner_out = L.corner;
     __syncwarp();
   }
-  if (LOCAL) {
+  if (LOCAL && !refill) {
     unsigned long long key = L.best_v > 0 ? band_key(L.best_v, L.best_y, L.best_x) : 0ull;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {

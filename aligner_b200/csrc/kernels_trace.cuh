@@ -543,9 +543,32 @@ namespace alnr {
 // per strip around the diagonal through the current cell — in one batch of independent loads,
 // and the walk then takes its words from the owning lane by shuffle.  A word that was not
 // predicted (the path drifted by indels) is loaded directly.  Output as traceback_kernel.
-static __global__ void __launch_bounds__(32) traceback_warp_kernel(TraceArgs a) {
+// Checkpointed mode (ck != nullptr; one pair): the direction scratch only holds the strips
+// [strip0, strip0 + dl.nstrips) of one GROUP of bands, re-filled from the kept band boundary rows
+// (wave.cu).  The walk resumes from *ck, stops when the path climbs above row y_stop (the rows of
+// the groups still to be re-filled) and leaves its state in *ck for the next group's launch.
+struct CkptState {
+  uint32_t cy, cx;          // current cell of the walk
+  unsigned long long pos;   // next output byte (the strings grow downwards from the slot's end)
+  uint32_t done, started;
+};
+
+static __global__ void ckpt_init_kernel(TraceArgs a, CkptState *ck) {
+  const uint32_t pair = a.cv.order ? a.cv.order[a.cv.first] : a.cv.first;
+  const uint32_t sp = a.cv.seq(pair);
+  const uint64_t qo = a.cv.q_off[sp], to = a.cv.t_off[sp];
+  ck->cy = a.fo.start[2 * (size_t)pair];
+  ck->cx = a.fo.start[2 * (size_t)pair + 1];
+  ck->pos = qo + to + pair + (a.cv.q_off[sp + 1] - qo) + (a.cv.t_off[sp + 1] - to) + 1;
+  ck->done = 0;  // a rejected pair is finished by the first walk launch
+  ck->started = 0;
+}
+
+static __global__ void __launch_bounds__(32) traceback_warp_kernel(TraceArgs a, CkptState *ck = nullptr,
+                                                                   uint32_t y_stop = 0, uint32_t strip0 = 0) {
   const uint32_t slot = blockIdx.x, lane = threadIdx.x;
   if (slot >= a.cv.count) return;
+  if (ck && ck->done) return;
   const uint32_t pair = a.cv.order ? a.cv.order[a.cv.first + slot] : a.cv.first + slot;
   const uint32_t sp = a.cv.seq(pair);
   const uint64_t qo = a.cv.q_off[sp], to = a.cv.t_off[sp];
@@ -557,6 +580,7 @@ static __global__ void __launch_bounds__(32) traceback_warp_kernel(TraceArgs a) 
       if (a.to.aln_len) a.to.aln_len[pair] = 0;
       if (a.to.aln_off) a.to.aln_off[pair] = slot_end;
       if (a.to.coords) for (int k = 0; k < 4; ++k) a.to.coords[4 * (size_t)pair + k] = 0;
+      if (ck) ck->done = 1;
     }
     return;
   }
@@ -568,14 +592,20 @@ static __global__ void __launch_bounds__(32) traceback_warp_kernel(TraceArgs a) 
   const uint32_t sy = a.fo.start[2 * (size_t)pair], sx = a.fo.start[2 * (size_t)pair + 1];
   uint32_t cy = sy, cx = sx;
   uint64_t pos = slot_end;
+  bool resumed = false;
+  if (ck) {
+    cy = ck->cy; cx = ck->cx; pos = ck->pos; resumed = ck->started != 0;
+    // the path is not inside this group's rows (local mode: the arg-max sits higher up): nothing to do
+    if (cy && cx && ((cy - 1) >> rsh) >= strip0 + a.dl.nstrips) return;
+  }
   const bool wr = lane == 0 && a.to.q_aln != nullptr && a.to.t_aln != nullptr;
   auto emit = [&](uint8_t qc, uint8_t tc) {
     --pos;
     if (wr) { a.to.q_aln[pos] = qc; a.to.t_aln[pos] = tc; }
   };
-  emit(q[cx - 1], t[cy - 1]);  // seed (simple/mod.rs:102-105, :213-216)
-  bool done = false;
-  while (!done) {
+  if (!resumed) emit(q[cx - 1], t[cy - 1]);  // seed (simple/mod.rs:102-105, :213-216)
+  bool done = false, paused = false;
+  while (!done && !paused) {
     // ---- batch of predicted words: strip base - k, k = 0..15, two words each ---------------
     uint32_t my_val = 0;
     const uint32_t base = cy ? (cy - 1) >> rsh : 0;
@@ -588,8 +618,8 @@ static __global__ void __launch_bounds__(32) traceback_warp_kernel(TraceArgs a) 
     {
       const uint32_t k = lane >> 1;
       const int64_t wc = pred_hi(k) - (lane & 1);
-      if (cy && cx && k <= base && wc >= 0)
-        my_val = __ldcs(a.D + ((uint64_t)slot * a.dl.nstrips + (base - k)) * a.dl.ncols + (uint64_t)wc);
+      if (cy && cx && k <= base && base - k >= strip0 && wc >= 0)
+        my_val = __ldcs(a.D + ((uint64_t)slot * a.dl.nstrips + (base - k - strip0)) * a.dl.ncols + (uint64_t)wc);
     }
     // ---- walk until the path leaves the 16 predicted strips ---------------------------------
     uint32_t cur_strip = 0xffffffffu, cur_wc = 0xffffffffu, cur_w = 0;
@@ -599,6 +629,7 @@ static __global__ void __launch_bounds__(32) traceback_warp_kernel(TraceArgs a) 
         if (!glob || (cy == 0 && cx == 0)) d = DIR_BEGINNING;
         else d = (cy == 0) ? DIR_LEFT : DIR_TOP;  // simple/mod.rs:59-67
       } else {
+        if (ck && cy <= y_stop) { paused = true; break; }  // the rows above belong to the next group
         const uint32_t strip = (cy - 1) >> rsh, wc = (cx - 1) >> csh;
         if (strip != cur_strip || wc != cur_wc) {
           const uint32_t k = base - strip;
@@ -607,7 +638,7 @@ static __global__ void __launch_bounds__(32) traceback_warp_kernel(TraceArgs a) 
           const uint32_t src = 2 * k + (((int64_t)wc == hi) ? 0u : 1u);
           const uint32_t v = __shfl_sync(0xffffffffu, my_val, src);
           if ((int64_t)wc == hi || (int64_t)wc == hi - 1) cur_w = v;
-          else cur_w = a.D[((uint64_t)slot * a.dl.nstrips + strip) * a.dl.ncols + wc];  // not predicted
+          else cur_w = a.D[((uint64_t)slot * a.dl.nstrips + (strip - strip0)) * a.dl.ncols + wc];  // not predicted
           cur_strip = strip; cur_wc = wc;
         }
         d = (cur_w >> (2 * (((cx - 1) & cmask) << rsh) + 2 * ((cy - 1) & rmask))) & 3u;
@@ -618,7 +649,8 @@ static __global__ void __launch_bounds__(32) traceback_warp_kernel(TraceArgs a) 
       else { emit(q[cx - 1], t[cy - 1]); --cx; --cy; }
     }
   }
-  if (lane == 0) {
+  if (lane == 0 && ck) { ck->cy = cy; ck->cx = cx; ck->pos = pos; ck->started = 1; ck->done = done ? 1u : 0u; }
+  if (lane == 0 && (done || !ck)) {
     if (a.to.aln_len) a.to.aln_len[pair] = (uint32_t)(slot_end - pos);
     if (a.to.aln_off) a.to.aln_off[pair] = pos;
     if (a.to.coords) {

@@ -6,6 +6,7 @@
 #include <vector>
 
 #include "kernels_tile.cuh"
+#include "kernels_trace.cuh"
 #include "strip_launch.h"
 #include "wave_launch.h"
 
@@ -29,6 +30,83 @@ bool wave_eligible(const alnr_batch_impl &B, uint32_t m, uint32_t n) {
   for (double v : B.matrix) mag = std::max(mag, v);
   if (B.mode == ALNR_LOCAL && mag * std::min(m, n) >= 16777216.0) return false;  // 24-bit value field
   return true;
+}
+
+// Bands per group of the checkpointed traceback for a pair of m x n cells, or 0 when the whole
+// direction matrix (m * n / 4 bytes) fits `budget` bytes.  ALNR_SCRATCH_BUDGET (bytes) overrides the
+// budget (tests).
+uint32_t wave_ckpt_group(uint32_t m, uint32_t n, uint64_t budget) {
+  if (const char *e = std::getenv("ALNR_SCRATCH_BUDGET")) {  // read per call: tests switch it on and off
+    const uint64_t forced = std::strtoull(e, nullptr, 10);
+    if (forced) budget = forced;
+  }
+  const DLayout full = DLayout::make_blocked(4, m, n);
+  if (full.words_for(1) * 4 <= budget) return 0;
+  const uint64_t per_band = 32ull * full.ncols * 4;  // 32 strips of one 128-row band
+  const uint32_t nbands = (m + 127) / 128;
+  return (uint32_t)std::min<uint64_t>(std::max<uint64_t>(budget / per_band, 1), nbands);
+}
+
+static int tile_args(alnr_batch_impl &B, const Chunk &c, BandArgs &a, size_t &smem, unsigned &resident);
+
+// Checkpointed traceback (BASELINE north_star (2): "checkpointed Hirschberg-style for very long
+// pairs"; the loop it reproduces: simple/mod.rs:99-130, :213-245).  The first pass ran score-only
+// and kept the bottom row of every 128-row band (m * n / 32 bytes instead of m * n / 4).  The path
+// is then walked group by group from the bottom: the group's bands are filled again WITH directions
+// into a scratch of `group` bands — every band starts from the kept row above it, so the bands of a
+// group run side by side — and the walk crosses the group and parks at its top row.  Everything is
+// enqueued without host synchronisation: a re-fill whose group the path does not cross (local
+// mode: the alignment starts and ends anywhere) returns at once.
+int wave_ckpt_trace(alnr_batch_impl &B, const Chunk &c, const DLayout &dl, const TraceArgs &ta_in, cudaStream_t s) {
+  BandArgs a;
+  size_t smem = 0;
+  unsigned resident = 1;
+  int st = tile_args(B, c, a, smem, resident);
+  if (st) return st;
+  const uint32_t G = c.ckpt_group, nbands = a.nbands;
+  if (!B.d_ckpt.p) ALNR_CUDA(B.d_ckpt.alloc(8));
+  CkptState *ck = reinterpret_cast<CkptState *>(B.d_ckpt.p);
+  TraceArgs ta = ta_in;
+  ta.dl = dl;
+  ckpt_init_kernel<<<1, 1, 0, s>>>(ta, ck);
+  ALNR_LAUNCHED();
+  const bool local = B.mode == ALNR_LOCAL;
+  a.best = nullptr; a.corner_out = nullptr; a.ckpt = B.d_ckpt.p;
+  a.D = B.Dp();
+  for (uint32_t b1 = nbands; b1 > 0;) {
+    const uint32_t b0 = b1 > G ? b1 - G : 0;
+    a.band0 = b0; a.band_end = b1; a.strip0 = b0 * 32;
+    const unsigned grid = std::min<unsigned>(b1 - b0, resident);
+    if (local) fill_tile_kernel<true><<<grid, 32, smem, s>>>(a);
+    else fill_tile_kernel<false><<<grid, 32, smem, s>>>(a);
+    ALNR_LAUNCHED();
+    traceback_warp_kernel<<<1, 32, 0, s>>>(ta, ck, b0 * 128u, b0 * 32u);
+    ALNR_LAUNCHED();
+    b1 = b0;
+  }
+  // the border run of a global path (column 0 / row 0 need no directions) and the result record
+  traceback_warp_kernel<<<1, 32, 0, s>>>(ta, ck, 0u, 0u);
+  ALNR_LAUNCHED();
+  return ALNR_OK;
+}
+
+// BandArgs, shared-memory size and resident grid of the tile kernel for the pair of chunk c
+static int tile_args(alnr_batch_impl &B, const Chunk &c, BandArgs &a, size_t &smem, unsigned &resident) {
+  a.q = B.d_q.p + c.q0; a.t = B.d_t.p + c.t0;
+  a.n = c.n_max; a.m = c.m_max; a.V = B.V; a.matrix = B.d_mati.p;
+  a.del = (int)B.del; a.ext = (int)B.ext;
+  a.nbands = (a.m + 127) / 128;
+  a.prog = nullptr;
+  a.rows = B.d_band.p + 4;
+  a.dcols = DLayout::make_blocked(4, a.m, a.n).ncols;
+  smem = (size_t)B.V * 32 * sizeof(int4) + 32 * sizeof(int);
+  int occ0 = 0, occ1 = 0, sms = 0, dev = 0;
+  ALNR_CUDA(cudaGetDevice(&dev));
+  ALNR_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  ALNR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ0, fill_tile_kernel<false>, 32, smem));
+  ALNR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ1, fill_tile_kernel<true>, 32, smem));
+  resident = (unsigned)std::max(1, std::min(occ0, occ1)) * (unsigned)std::max(1, sms);
+  return ALNR_OK;
 }
 
 // Tile pipeline (kernels_tile.cuh): 4 x 4 cells per lane and step, sentinel hand-off of the band rows.
@@ -61,7 +139,7 @@ static int tile_run_pair(alnr_batch_impl &B, const Chunk &c, const DLayout &dl, 
 #ifdef ALNR_TILE_DEBUG
   a.prog = reinterpret_cast<uint32_t *>(base + 4 + (row_words + 3) / 4 * 4);
 #endif
-  a.D = B.Dp();
+  a.D = c.ckpt_group ? nullptr : B.Dp();  // checkpointed: score-only first pass, directions group by group later
   a.dcols = dl.ncols;
   const size_t smem = (size_t)B.V * 32 * sizeof(int4) + 32 * sizeof(int);
   int occ0 = 0, occ1 = 0, sms = 0, dev = 0;

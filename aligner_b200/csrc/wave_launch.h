@@ -11,4 +11,9 @@ uint32_t wave_band_rows(uint32_t m);
 // enqueue init + the persistent band pipeline launch + finish for the single pair of chunk c.
 int wave_run_pair(alnr_batch_impl &B, const Chunk &c, const DLayout &dl, const FillOut &fo);
 
+// checkpointed traceback (pairs whose direction matrix exceeds the scratch budget)
+uint32_t wave_ckpt_group(uint32_t m, uint32_t n, uint64_t budget);
+struct TraceArgs;
+int wave_ckpt_trace(alnr_batch_impl &B, const Chunk &c, const DLayout &dl, const TraceArgs &ta, cudaStream_t s);
+
 }  // namespace alnr

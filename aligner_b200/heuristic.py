@@ -68,8 +68,9 @@ def heuristic_batch(pairs, matrices, del_, ext, kd, r_squared, frequencies, pair
     return res
 
 
-def matrix_search(pairs, matrices, del_, ext, kd, r_squared, frequencies, device=-1, want_grid=True):
-    """All pairs x all candidate matrices -> (fitness[K], best_k[P], best_f[P], f_grid[P,K], status[P,K])."""
+def matrix_search(pairs, matrices, del_, ext, kd, r_squared, frequencies, device=-1, want_grid=True, n_gpus=None):
+    """All pairs x all candidate matrices -> (fitness[K], best_k[P], best_f[P], f_grid[P,K], status[P,K]).
+    ``n_gpus``: shard the pairs over that many devices inside the library (alnr_matrix_search_multi)."""
     mats = np.ascontiguousarray(matrices, dtype=np.float64)
     K, V = mats.shape[0], mats.shape[1]
     fr = np.ascontiguousarray(frequencies, dtype=np.float64)
@@ -82,12 +83,14 @@ def matrix_search(pairs, matrices, del_, ext, kd, r_squared, frequencies, device
     dummy = np.zeros((V, V))
     p = N.Params(N.LOCAL, V, float(del_), float(ext), dummy.ctypes.data_as(N.f64p), device, N.NUM_AUTO)
     b = pairs.c_struct()
-    N.check(N.lib().alnr_matrix_search(C.byref(p), C.byref(b), mats.ctypes.data_as(N.f64p), K, float(kd),
-                                       float(r_squared), fr.ctypes.data_as(N.f64p),
-                                       fitness.ctypes.data_as(N.f64p), best_k.ctypes.data_as(N.u32p),
-                                       best_f.ctypes.data_as(N.f64p),
-                                       grid.ctypes.data_as(N.f64p) if want_grid else N.f64p(),
-                                       sgrid.ctypes.data_as(N.i32p) if want_grid else N.i32p()))
+    args = (C.byref(p), C.byref(b), mats.ctypes.data_as(N.f64p), K, float(kd), float(r_squared),
+            fr.ctypes.data_as(N.f64p), fitness.ctypes.data_as(N.f64p), best_k.ctypes.data_as(N.u32p),
+            best_f.ctypes.data_as(N.f64p), grid.ctypes.data_as(N.f64p) if want_grid else N.f64p(),
+            sgrid.ctypes.data_as(N.i32p) if want_grid else N.i32p())
+    if n_gpus is None:
+        N.check(N.lib().alnr_matrix_search(*args))
+    else:
+        N.check(N.lib().alnr_matrix_search_multi(*args, int(n_gpus)))
     return fitness, best_k, best_f, grid, sgrid
 
 

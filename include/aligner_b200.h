@@ -175,6 +175,16 @@ int alnr_expand_alignments(int mode, int volume, const alnr_batch *b, const alnr
 /* Host buffers in, host buffers out (H2D + kernels + D2H, chunked and overlapped). */
 int alnr_align_batch(const alnr_params *p, const alnr_batch *b, alnr_batch_out *out);
 
+/* The same call over the GPUs of one box (BASELINE north_star (3); replaces the Kafka fan-out of
+ * aligner-web/src/bin/dispatcher/handlers.rs:193-251 + node/main.rs:61-74 for independent pairs):
+ * the batch is cut into n_gpus contiguous shards of pairs balanced by the sum of n * m, every shard
+ * runs on its own device (shard k on device k % alnr_device_count(), p->device is ignored) from its
+ * own host thread, and writes straight into the caller's arrays at its offset.  No collective.
+ * n_gpus <= 0: one shard per device.  Results are those of alnr_align_batch for every n_gpus, except
+ * that in the compact format the move strings are dense per SHARD (moves_off is mandatory and
+ * authoritative; shard k's words start at the worst-case capacity of the shards before it). */
+int alnr_align_batch_multi(const alnr_params *p, const alnr_batch *b, alnr_batch_out *out, int n_gpus);
+
 /* Device-resident form of the same call: upload once, run many times, download. */
 typedef struct alnr_batch_handle alnr_batch_handle;
 int alnr_batch_create(const alnr_params *p, const alnr_batch *b, alnr_batch_handle **h);
@@ -307,6 +317,15 @@ int alnr_matrix_search(const alnr_params *p, const alnr_batch *b, const double *
                        uint32_t n_matrices, double kd, double r_squared, const double *frequencies,
                        double *fitness, uint32_t *best_k, double *best_f, double *f_grid,
                        int32_t *status_grid);
+
+/* alnr_matrix_search over n_gpus devices of one box: pairs sharded on ALNR_FITNESS_BLOCK boundaries
+ * (balanced by the sum of n * m), one host thread and stream set per device, the f grid written in
+ * place, fitness reduced in the fixed blocked order below — bit-identical for every n_gpus.  (One
+ * process per GPU exchanges the block sums with one NCCL all-reduce instead: aligner_b200/sharding.py.) */
+int alnr_matrix_search_multi(const alnr_params *p, const alnr_batch *b, const double *matrices,
+                             uint32_t n_matrices, double kd, double r_squared, const double *frequencies,
+                             double *fitness, uint32_t *best_k, double *best_f, double *f_grid,
+                             int32_t *status_grid, int n_gpus);
 
 /* Fixed-order fitness reduction, the one step of the search that crosses GPUs.
  * block_sums[b * n_matrices + k] = sum of f_grid[i * n_matrices + k] over the pairs i of block b

@@ -157,3 +157,74 @@ def test_several_long_pairs_of_growing_size_in_one_batch():
             assert res.status[i] == 0 and res.f[i] == ref["f"] and res.corner[i] == ref["corner"]
             qa, ta = res.alignment(i)
             assert (qa == ref["q_aln"]).all() and (ta == ref["t_aln"]).all()
+
+
+# ---- checkpointed traceback (aligner_b200/csrc/wave.cu::wave_ckpt_trace) ------------------------
+# ALNR_SCRATCH_BUDGET (bytes) forces pairs whose direction matrix is larger onto the checkpointed
+# path: score-only first pass that keeps the band rows, then re-fill + walk group by group.
+
+@pytest.mark.parametrize("budget", [40_000, 300_000, 3_000_000])
+@pytest.mark.parametrize("n,mode,d", [(5000, "global", 8), (5000, "local", 6), (9000, "global", 8)])
+def test_checkpointed_traceback_vs_lean_oracle(monkeypatch, n, mode, d, budget):
+    q, t = _long_pair(n, seed=40 + n)
+    M = ab.dna_matrix(5, -4)
+    ref = O.align_pair(mode, q, t, float(d), float(d), M, lean=True)
+    monkeypatch.setenv("ALNR_SCRATCH_BUDGET", str(budget))  # 1 .. many bands per group
+    cls = ab.SimpleGlobalAligner if mode == "global" else ab.SimpleLocalAligner
+    r = cls.from_seqs(q, t, symbols=ab.DNA).perform_alignment(d, d, M, want_matrices=False)
+    assert r.alignment.f == ref["f"] and r.corner_score == ref["corner"] and r.alignment.coords == ref["coords"]
+    assert (r.alignment.query == ref["q_aln"]).all() and (r.alignment.target == ref["t_aln"]).all()
+
+
+@pytest.mark.parametrize("m,n", [(300, 5000), (5000, 300), (40000, 33), (33, 40000), (4097, 1023)])
+@pytest.mark.parametrize("mode,d", [("global", 8), ("local", 6)])
+def test_checkpointed_traceback_extreme_shapes(monkeypatch, m, n, mode, d):
+    """Unrelated sequences: global paths run along the border rows, local alignments are short and
+    sit anywhere (most groups are skipped)."""
+    rng = np.random.default_rng(m * 7 + n)
+    q = rng.integers(0, 4, n).astype(np.uint8)
+    t = rng.integers(0, 4, m).astype(np.uint8)
+    M = ab.dna_matrix(5, -4)
+    ref = O.align_pair(mode, q, t, float(d), float(d), M, lean=True)
+    monkeypatch.setenv("ALNR_SCRATCH_BUDGET", "20000")
+    cls = ab.SimpleGlobalAligner if mode == "global" else ab.SimpleLocalAligner
+    r = cls.from_seqs(q, t, symbols=ab.DNA).perform_alignment(d, d, M, want_matrices=False)
+    assert r.alignment.f == ref["f"] and r.corner_score == ref["corner"] and r.alignment.coords == ref["coords"]
+    assert (r.alignment.query == ref["q_aln"]).all() and (r.alignment.target == ref["t_aln"]).all()
+
+
+def test_checkpointed_traceback_equals_full_matrix_path_1e5(monkeypatch):
+    """10^5 x 10^5 global: the checkpointed path (64 MB of direction scratch instead of 2.5 GB) returns
+    the strings and the score of the full-matrix path."""
+    q, t = W.dna_long_pair(100000, seed=4)
+    M = ab.dna_matrix(5, -4)
+    al = ab.SimpleGlobalAligner.from_seqs(q, t, symbols=ab.DNA)
+    l0 = N.lib().alnr_kernel_launch_count()
+    full = al.perform_alignment(8, 8, M, want_matrices=False)
+    l1 = N.lib().alnr_kernel_launch_count()
+    monkeypatch.setenv("ALNR_SCRATCH_BUDGET", str(64 << 20))
+    ck = al.perform_alignment(8, 8, M, want_matrices=False)
+    # 2.5 GB of directions in 64 MB groups: one re-fill + one walk launch per group
+    assert N.lib().alnr_kernel_launch_count() - l1 > (l1 - l0) + 40
+    assert ck.corner_score == full.corner_score and ck.alignment.coords == full.alignment.coords
+    assert (ck.alignment.query == full.alignment.query).all() and (ck.alignment.target == full.alignment.target).all()
+
+
+def test_checkpointed_pair_inside_a_batch(monkeypatch):
+    rng = np.random.default_rng(5)
+    q1, t1 = _long_pair(6000, seed=77)
+    q2, t2 = _long_pair(5000, seed=78)
+    qs = [rng.integers(0, 4, 60).astype(np.uint8), q1, q2]
+    ts = [rng.integers(0, 4, 70).astype(np.uint8), t1, t2]
+    pairs = ab.PackedPairs.from_lists(qs, ts)
+    M = ab.dna_matrix(5, -4)
+    ref = ab.align_batch(N.GLOBAL, pairs, M, 8, 8)
+    monkeypatch.setenv("ALNR_SCRATCH_BUDGET", "500000")
+    res = ab.align_batch(N.GLOBAL, pairs, M, 8, 8)
+    cr = ab.align_batch(N.GLOBAL, pairs, M, 8, 8, compact=True).expand()
+    for i in range(3):
+        assert res.corner[i] == ref.corner[i]
+        for got in (res, cr):
+            qa, ta = got.alignment(i)
+            qb, tb = ref.alignment(i)
+            assert (qa == qb).all() and (ta == tb).all()
