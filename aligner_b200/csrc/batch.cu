@@ -486,6 +486,7 @@ int alnr_batch_impl::plan_and_alloc(const alnr_batch *b) {
     hcol = std::max<uint64_t>(hcol, (uint64_t)((c.count + 31) / 32) * 32 * ((uint64_t)std::max(c.m_max, c.n_max) + 1));
   }
   const size_t copies = chunks.size() > 1 ? 2 : 1;
+  if (numeric == ALNR_NUM_I16X2) hcol = std::max<uint64_t>(hcol, 2 * strip_row_words(*this));
   d_words = (dwords + 3) / 4 * 4; hcol_elems = (hcol + 3) / 4 * 4;
   ALNR_CUDA(d_D.alloc(d_words * copies));
   if (numeric == ALNR_NUM_F64) ALNR_CUDA(d_hcol_d.alloc(hcol_elems * copies));

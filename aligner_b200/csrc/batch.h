@@ -73,8 +73,6 @@ struct alnr_batch_impl {
   DevBuf<int> d_band;           // band pipeline kernel: reduction cells, progress words, band rows
   DevBuf<uint32_t> d_ckpt;      // checkpointed traceback: state of the walk between band groups
   DevBuf<uint32_t> d_pack;      // packed sequences for the strip kernel
-  DevBuf<uint32_t> d_brow;      // strip kernel: kept bottom rows of strip 0 (incremental re-run), per parity
-  uint64_t brow_words = 0;
   DevBuf<uint32_t> d_wz;        // warp kernel: [8 counters][fail list][z bits 2*nzw per slot]
   DevBuf<uint32_t> d_q2raw, d_t2raw;  // packed input as it crossed the ABI (pair-major words)
   DevBuf<uint64_t> d_qwoff, d_twoff;  // ragged packed input: word offsets (count + 1)

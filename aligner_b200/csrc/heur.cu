@@ -34,7 +34,13 @@ struct HeurState {
   int32_t *status, *passes;
   uint64_t *coords_cur, *coords_out;
   const int32_t *pair_status;
+  // Items are grouped by the rows-per-lane instantiation their target needs (pair_gid[pair]); every
+  // group keeps its own active list (list base + gid * list_stride, counter base + gid).
+  const uint8_t *pair_gid;
+  uint32_t list_stride;
 };
+
+constexpr int kHeurGroups = 4;
 
 // Both kernels below give every item a group of 8 lanes (transform_matrix_g8): grid = items * 8 threads.
 static __global__ void heur_init_kernel(HeurState h, uint32_t items, uint32_t *list, uint32_t *count) {
@@ -52,7 +58,8 @@ static __global__ void heur_init_kernel(HeurState h, uint32_t items, uint32_t *l
   h.maxf[i] = 0.0;  // heuristic/mod.rs:55
   h.passes[i] = 0;
   h.fout[i] = 0.0;
-  if (!st) list[atomicAdd(count, 1u)] = i;
+  const uint32_t g = h.pair_gid[h.pair_idx[i]];
+  if (!st) list[(size_t)g * h.list_stride + atomicAdd(count + g, 1u)] = i;
 }
 
 // after fill + traceback of one round
@@ -77,7 +84,8 @@ static __global__ void heur_update_kernel(HeurState h, const uint32_t *list, uin
     h.passes[i] += 1;
     h.maxf[i] = f;
     if (st) { h.status[i] = st; return; }  // .unwrap() panic in the reference
-    next[atomicAdd(next_count, 1u)] = i;
+    const uint32_t g = h.pair_gid[h.pair_idx[i]];
+    next[(size_t)g * h.list_stride + atomicAdd(next_count + g, 1u)] = i;
   } else {  // :73-76 — the LAST (non-improving) result and the matrix that produced it
     for (int j = gl; j < VV; j += 8) L[j] = T[j];
     if (gl != 0) return;
@@ -141,6 +149,44 @@ extern "C" int alnr_heuristic_batch(const alnr_params *p, const alnr_batch *b,
     n_max = std::max<uint32_t>(n_max, (uint32_t)(b->q_off[i + 1] - b->q_off[i]));
     m_max = std::max<uint32_t>(m_max, (uint32_t)(b->t_off[i + 1] - b->t_off[i]));
   }
+  // Groups by rows per lane: a 300-row target in the 352-row band of the longest target (R = 11)
+  // drags 15 % idle rows through every step; with its own R = 10 instantiation it drags 6 %.  At most
+  // kHeurGroups groups (the rarest R values are merged upwards); all groups share the rounds — one
+  // launch sequence per group and round, one host synchronisation per round.  ALNR_HEUR_ONE_GROUP=1:
+  // one group with the R of the longest target (the round-1 behaviour, A/B runs).
+  std::vector<uint8_t> pair_gid(P, 0);
+  uint32_t group_R[kHeurGroups] = {0, 0, 0, 0}, group_m[kHeurGroups] = {0, 0, 0, 0};
+  int n_groups = 1;
+  {
+    uint64_t hist[17] = {0};
+    for (uint64_t i = 0; i < P; ++i) hist[warp_pick_rows(std::max<uint32_t>((uint32_t)(b->t_off[i + 1] - b->t_off[i]), 1u))]++;
+    int up[17];  // R -> the R of the group it is merged into
+    for (int r = 0; r <= 16; ++r) up[r] = r;
+    auto distinct = [&] { int c = 0; for (int r = 2; r <= 16; ++r) c += hist[r] != 0; return c; };
+    const bool one_group = getenv("ALNR_HEUR_ONE_GROUP") != nullptr;
+    while (distinct() > (one_group ? 1 : kHeurGroups)) {
+      int best = -1;  // the rarest R that has a larger neighbour
+      for (int r = 2; r < 16; ++r) {
+        if (!hist[r]) continue;
+        bool has_up = false;
+        for (int q = r + 1; q <= 16; ++q) has_up = has_up || hist[q];
+        if (has_up && (best < 0 || hist[r] < hist[best])) best = r;
+      }
+      int nxt = best + 1;
+      while (!hist[nxt]) ++nxt;
+      hist[nxt] += hist[best]; hist[best] = 0;
+      for (int r = 2; r <= 16; ++r) if (up[r] == best) up[r] = nxt;
+    }
+    int gid_of[17];
+    n_groups = 0;
+    for (int r = 2; r <= 16; ++r) if (hist[r]) { gid_of[r] = n_groups; group_R[n_groups++] = (uint32_t)r; }
+    for (uint64_t i = 0; i < P; ++i) {
+      const uint32_t m = std::max<uint32_t>((uint32_t)(b->t_off[i + 1] - b->t_off[i]), 1u);
+      const int g = gid_of[up[warp_pick_rows(m)]];
+      pair_gid[i] = (uint8_t)g;
+      group_m[g] = std::max(group_m[g], m);
+    }
+  }
   const uint64_t q_total = b->q_off[P], t_total = b->t_off[P];
   // one warp per item (kernels_warp.cuh): the item's own matrix sits in shared memory
   const DLayout dl0 = DLayout::make_skewed(warp_pick_rows(std::max(m_max, 1u)), std::max(m_max, 1u), std::max(n_max, 1u));
@@ -158,7 +204,7 @@ extern "C" int alnr_heuristic_batch(const alnr_params *p, const alnr_batch *b,
   ALNR_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
   struct StreamGuard { cudaStream_t s; ~StreamGuard() { cudaStreamSynchronize(s); cudaStreamDestroy(s); } } guard{stream};
 
-  DevBuf<uint8_t> d_q, d_t;
+  DevBuf<uint8_t> d_q, d_t, d_gid;
   DevBuf<uint64_t> d_qoff, d_toff, d_cc, d_co;
   DevBuf<uint32_t> d_pi, d_mi, d_lists, d_cnt, d_start, d_D, d_wz;
   DevBuf<int32_t> d_pst, d_st, d_passes;
@@ -172,7 +218,8 @@ extern "C" int alnr_heuristic_batch(const alnr_params *p, const alnr_batch *b,
   ALNR_CUDA(d_mats.alloc(K * VV)); ALNR_CUDA(d_freqs.alloc(P * V));
   ALNR_CUDA(d_pst.alloc(P)); ALNR_CUDA(d_flag.alloc(4));
   ALNR_CUDA(d_pi.alloc(chunk)); ALNR_CUDA(d_mi.alloc(chunk));
-  ALNR_CUDA(d_lists.alloc(2 * chunk)); ALNR_CUDA(d_cnt.alloc(64));
+  ALNR_CUDA(d_lists.alloc(2 * chunk * kHeurGroups)); ALNR_CUDA(d_cnt.alloc(64 * kHeurGroups));
+  ALNR_CUDA(d_gid.alloc(P));
   ALNR_CUDA(d_start.alloc(2 * chunk)); ALNR_CUDA(d_D.alloc(dl0.words_for(chunk)));
   ALNR_CUDA(d_st.alloc(chunk)); ALNR_CUDA(d_passes.alloc(chunk));
   ALNR_CUDA(d_T.alloc(chunk * VV)); ALNR_CUDA(d_L.alloc(chunk * VV)); ALNR_CUDA(d_F.alloc(chunk * VV));
@@ -188,6 +235,7 @@ extern "C" int alnr_heuristic_batch(const alnr_params *p, const alnr_batch *b,
   ALNR_CUDA(h2d(d_q.p, b->q, q_total)); ALNR_CUDA(h2d(d_t.p, b->t, t_total));
   ALNR_CUDA(h2d(d_qoff.p, b->q_off, (P + 1) * 8)); ALNR_CUDA(h2d(d_toff.p, b->t_off, (P + 1) * 8));
   ALNR_CUDA(h2d(d_mats.p, it->matrices, K * VV * 8)); ALNR_CUDA(h2d(d_freqs.p, it->frequencies, P * V * 8));
+  ALNR_CUDA(h2d(d_gid.p, pair_gid.data(), P));
   // per-pair validation (empty sequences, symbols outside the alphabet)
   ALNR_CUDA(cudaMemsetAsync(d_flag.p, 0, 4 * sizeof(int), stream));
   any_symbol_out_of_range_kernel<<<148 * 4, 256, 0, stream>>>(d_q.p, q_total, V, d_flag.p); ALNR_LAUNCHED();
@@ -209,14 +257,16 @@ extern "C" int alnr_heuristic_batch(const alnr_params *p, const alnr_batch *b,
     ALNR_CUDA(h2d(d_pi.p, hpi.data(), cnt * 4)); ALNR_CUDA(h2d(d_mi.p, hmi.data(), cnt * 4));
     ALNR_CUDA(cudaStreamSynchronize(stream));  // hpi/hmi are reused by the next chunk
     HeurState hs{d_pi.p, d_mi.p, d_mats.p, d_freqs.p, it->kd, r2, V, d_T.p, d_L.p, d_F.p, d_maxf.p,
-                 d_fcur.p, d_fout.p, d_st.p, d_passes.p, d_cc.p, d_co.p, d_pst.p};
-    uint32_t *lists[2] = {d_lists.p, d_lists.p + chunk};
-    ALNR_CUDA(cudaMemsetAsync(d_cnt.p, 0, 64 * sizeof(uint32_t), stream));
+                 d_fcur.p, d_fout.p, d_st.p, d_passes.p, d_cc.p, d_co.p, d_pst.p, d_gid.p, (uint32_t)chunk};
+    uint32_t *lists[2] = {d_lists.p, d_lists.p + chunk * kHeurGroups};
+    ALNR_CUDA(cudaMemsetAsync(d_cnt.p, 0, 64 * kHeurGroups * sizeof(uint32_t), stream));
     ALNR_CUDA(cudaMemsetAsync(d_co.p, 0, (size_t)cnt * 32, stream));
     heur_init_kernel<<<(cnt + 15) / 16, 128, 0, stream>>>(hs, cnt, lists[0], d_cnt.p); ALNR_LAUNCHED();
-    uint32_t n_active = 0;
-    ALNR_CUDA(cudaMemcpyAsync(&n_active, d_cnt.p, 4, cudaMemcpyDeviceToHost, stream));
+    uint32_t act[kHeurGroups] = {0, 0, 0, 0};  // active items per group
+    ALNR_CUDA(cudaMemcpyAsync(act, d_cnt.p, sizeof(act), cudaMemcpyDeviceToHost, stream));
     ALNR_CUDA(cudaStreamSynchronize(stream));
+    auto total_active = [&] { uint32_t t = 0; for (int g = 0; g < n_groups; ++g) t += act[g]; return t; };
+    uint32_t n_active = total_active();
     // The reference loops until f stops improving with no cap (heuristic/mod.rs:58-77); f is bounded
     // above, so it ends, but a cap keeps a pathological item from holding the batch: items still
     // active after max_rounds passes get the per-item status ALNR_CALCULATION_ERROR, every other
@@ -229,48 +279,58 @@ extern "C" int alnr_heuristic_batch(const alnr_params *p, const alnr_batch *b,
     }();
     for (int round = 0; n_active > 0; ++round) {
       if (round >= max_rounds) {
-        heur_mark_unconverged_kernel<<<(n_active + 127) / 128, 128, 0, stream>>>(hs, lists[round & 1], n_active);
-        ALNR_LAUNCHED();
+        for (int g = 0; g < n_groups; ++g) {
+          if (!act[g]) continue;
+          heur_mark_unconverged_kernel<<<(act[g] + 127) / 128, 128, 0, stream>>>(hs, lists[round & 1] + (size_t)g * chunk, act[g]);
+          ALNR_LAUNCHED();
+        }
         break;
       }
-      const uint32_t *cur = lists[round & 1];
-      uint32_t *nxt = lists[(round + 1) & 1];
-      uint32_t *cnt_next = d_cnt.p + 1 + round;
-      ChunkView cv{d_q.p, d_t.p, d_qoff.p, d_toff.p, cur, 0, n_active};
-      cv.seqmap = d_pi.p;
-      FillOut fo{d_fcur.p, d_corner.p, d_start.p, d_st.p};
-      WarpArgs<double> w;
-      w.cv = cv; w.V = V; w.del = p->del; w.ext = p->ext; w.stateful = stateful;
-      w.matrix = nullptr; w.item_matrices = d_T.p; w.D = d_D.p; w.dl = dl0; w.fo = fo;
-      w.rowbuf = d_hcol.p; w.rowbuf_stride = n_max + 1;
-      w.nzw = nzw;
-      warp_scratch_bind(w, d_wz.p, chunk, true);
-      w.H_out = nullptr; w.D_out = nullptr;
-      ALNR_CUDA(cudaMemsetAsync(d_wz.p, 0, 8 * sizeof(uint32_t), stream));
-      { int wst = warp_launch_f64(stream, w, true, false); if (wst) return wst; }
-      {  // items the warp kernel handed over (fail list): exact column-major kernel
-        ExactArgs<double> e;
-        e.cv = cv; e.mode = ALNR_LOCAL; e.V = V; e.del = p->del; e.ext = p->ext;
-        e.matrix = nullptr; e.hcol = d_hcol.p; e.hrows = m_max + 1; e.D = d_D.p; e.dl = dl0; e.fo = fo;
-        e.H_out = nullptr; e.D_out = nullptr; e.item_matrices = d_T.p;
-        e.list = w.fail_list; e.list_count = w.fail_count;
-        fill_exact_kernel<double><<<(n_active + 127) / 128, 128, (size_t)VV * 8, stream>>>(e); ALNR_LAUNCHED();
+      uint32_t *cnt_next = d_cnt.p + (size_t)(1 + round) * kHeurGroups;
+      for (int g = 0; g < n_groups; ++g) {
+        const uint32_t n_g = act[g];
+        if (n_g == 0) continue;
+        const uint32_t *cur = lists[round & 1] + (size_t)g * chunk;
+        uint32_t *nxt = lists[(round + 1) & 1];
+        const uint32_t m_g = std::max(group_m[g], 1u);
+        const DLayout dl_g = DLayout::make_skewed(group_R[g], m_g, std::max(n_max, 1u));
+        ChunkView cv{d_q.p, d_t.p, d_qoff.p, d_toff.p, cur, 0, n_g};
+        cv.seqmap = d_pi.p;
+        FillOut fo{d_fcur.p, d_corner.p, d_start.p, d_st.p};
+        WarpArgs<double> w;
+        w.cv = cv; w.V = V; w.del = p->del; w.ext = p->ext; w.stateful = stateful;
+        w.matrix = nullptr; w.item_matrices = d_T.p; w.D = d_D.p; w.dl = dl_g; w.fo = fo;
+        w.rowbuf = d_hcol.p; w.rowbuf_stride = n_max + 1;
+        w.nzw = nzw;
+        warp_scratch_bind(w, d_wz.p, chunk, true);
+        w.H_out = nullptr; w.D_out = nullptr;
+        ALNR_CUDA(cudaMemsetAsync(d_wz.p, 0, 8 * sizeof(uint32_t), stream));
+        { int wst = warp_launch_f64(stream, w, true, false); if (wst) return wst; }
+        {  // items the warp kernel handed over (fail list): exact column-major kernel
+          ExactArgs<double> e;
+          e.cv = cv; e.mode = ALNR_LOCAL; e.V = V; e.del = p->del; e.ext = p->ext;
+          e.matrix = nullptr; e.hcol = d_hcol.p; e.hrows = m_max + 1; e.D = d_D.p; e.dl = dl_g; e.fo = fo;
+          e.H_out = nullptr; e.D_out = nullptr; e.item_matrices = d_T.p;
+          e.list = w.fail_list; e.list_count = w.fail_count;
+          fill_exact_kernel<double><<<(n_g + 127) / 128, 128, (size_t)VV * 8, stream>>>(e); ALNR_LAUNCHED();
+        }
+        TraceOut to{d_cc.p, nullptr, nullptr, nullptr, nullptr, d_F.p};
+        TraceArgs ta{cv, ALNR_LOCAL, V, d_D.p, dl_g, fo, to};
+        // one warp per item, counts in shared memory (kernels_trace.cuh); very long pairs whose staged
+        // sequences do not fit shared memory take the one-thread-per-item kernel
+        const size_t tsm = 4 * ((size_t)VV + ((n_max + 7) / 8 * 8 + (m_g + 7) / 8 * 8) / 8) * sizeof(double);
+        if (tsm <= 200 * 1024) {
+          if (tsm > 48 * 1024)
+            ALNR_CUDA(cudaFuncSetAttribute(traceback_freq_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsm));
+          traceback_freq_warp_kernel<<<(n_g + 3) / 4, 128, tsm, stream>>>(ta, n_max, m_g); ALNR_LAUNCHED();
+        } else {
+          traceback_kernel<<<(n_g + 127) / 128, 128, 0, stream>>>(ta); ALNR_LAUNCHED();
+        }
+        heur_update_kernel<<<(n_g + 15) / 16, 128, 0, stream>>>(hs, cur, n_g, nxt, cnt_next); ALNR_LAUNCHED();
       }
-      TraceOut to{d_cc.p, nullptr, nullptr, nullptr, nullptr, d_F.p};
-      TraceArgs ta{cv, ALNR_LOCAL, V, d_D.p, dl0, fo, to};
-      // one warp per item, counts in shared memory (kernels_trace.cuh); very long pairs whose staged
-      // sequences do not fit shared memory take the one-thread-per-item kernel
-      const size_t tsm = 4 * ((size_t)VV + ((n_max + 7) / 8 * 8 + (m_max + 7) / 8 * 8) / 8) * sizeof(double);
-      if (tsm <= 200 * 1024) {
-        if (tsm > 48 * 1024)
-          ALNR_CUDA(cudaFuncSetAttribute(traceback_freq_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsm));
-        traceback_freq_warp_kernel<<<(n_active + 3) / 4, 128, tsm, stream>>>(ta, n_max, m_max); ALNR_LAUNCHED();
-      } else {
-        traceback_kernel<<<(n_active + 127) / 128, 128, 0, stream>>>(ta); ALNR_LAUNCHED();
-      }
-      heur_update_kernel<<<(n_active + 15) / 16, 128, 0, stream>>>(hs, cur, n_active, nxt, cnt_next); ALNR_LAUNCHED();
-      ALNR_CUDA(cudaMemcpyAsync(&n_active, cnt_next, 4, cudaMemcpyDeviceToHost, stream));
+      ALNR_CUDA(cudaMemcpyAsync(act, cnt_next, sizeof(act), cudaMemcpyDeviceToHost, stream));
       ALNR_CUDA(cudaStreamSynchronize(stream));
+      n_active = total_active();
     }
     auto d2h = [&](void *dst, const void *src, size_t bytes) -> cudaError_t {
       if (!dst) return cudaSuccess;

@@ -54,10 +54,6 @@ int strip_prepare(alnr_batch_impl &B) {
   // [list0 cmax][list1 cmax][z0 cmax*nzw][z1 cmax*nzw]
   B.rerun_words = 2ull * cmax + 2ull * cmax * nzw;
   ALNR_CUDA(B.d_rerun.alloc(8 * B.chunks.size() + (B.chunks.size() > 1 ? 2 : 1) * B.rerun_words));
-  if (strip_incremental(B)) {
-    B.brow_words = ((uint64_t)(cmax + 63) / 64 + 1) * 32 * B.n_max;  // one word per duo and column
-    ALNR_CUDA(B.d_brow.alloc((B.chunks.size() > 1 ? 2 : 1) * B.brow_words));
-  }
   return ALNR_OK;
 }
 
@@ -117,6 +113,15 @@ uint32_t strip_wave_pairs() {
   return cached;
 }
 
+// Words of ONE boundary-row buffer of the strip kernels: a row of n words per physical thread of the
+// largest launch (a resident wave, or fewer for small chunks).  The incremental re-run keeps two.
+uint64_t strip_row_words(const alnr_batch_impl &B) {
+  uint32_t cmax = 0;
+  for (const Chunk &k : B.chunks) cmax = std::max(cmax, k.count);
+  const uint64_t threads = std::min<uint64_t>(((uint64_t)cmax + 127) / 128 * 64, strip_wave_pairs() / 2) + kStripBlock;
+  return (threads + 31) / 32 * 32 * (uint64_t)std::max(B.n_max, 1u);
+}
+
 namespace {
 struct StripPlan {
   StripArgs a;
@@ -169,7 +174,9 @@ StripPlan strip_plan(alnr_batch_impl &B, const Chunk &c, const ChunkView &cv, co
   a.fail_list = P.lists[0]; a.fail_count = P.counters + 0;
   static const bool hrow_global = getenv("ALNR_STRIP_HROW_SMEM") == nullptr;
   a.hglobal = hrow_global ? (uint32_t *)B.hcol_i() : nullptr;
-  a.brow0 = (B.d_brow.p && a.hglobal) ? B.d_brow.p + (size_t)B.par * B.brow_words : nullptr;
+  // the incremental re-run keeps a second row per resident thread, half a row buffer further on
+  a.incremental = (strip_incremental(B) && a.hglobal) ? 1u : 0u;
+  a.hglobal2 = strip_row_words(B);
   P.R = dl.rows_per_word;
   return P;
 }
@@ -213,7 +220,7 @@ int strip_rerun_passes(alnr_batch_impl &B, const Chunk &c, const ChunkView &cv, 
   cudaStream_t stream = B.s2;
   // Incremental pass first (rerun_strip0_kernel): strip 0 only, with the observed bits; what it
   // cannot settle goes on list 1.  The full passes then read list `off + pass`.
-  const int off = (P.a.brow0 && c.m_max > P.R) ? 1 : 0;
+  const int off = (P.a.incremental && c.m_max > P.R) ? 1 : 0;
   if (off) {
     StripArgs r = P.a;
     r.list = P.lists[0]; r.list_count = P.counters + 0;

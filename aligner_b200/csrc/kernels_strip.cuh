@@ -48,9 +48,10 @@ struct StripArgs {
   // (1, x+1) is Diagonal with the same value under either penalty (row 0 is zero, H[1][x] cannot
   // exceed the largest score), so a wrongly assumed z bit in front of it changes nothing.
   uint32_t safe_mask;
-  // bottom row of strip 0 of every duo of the chunk, kept for the incremental re-run
-  // (rerun_strip0_kernel): [((vduo >> 5) * n + x-1) * 32 + (vduo & 31)], pair A in the low half
-  uint32_t *brow0;
+  // incremental re-run (rerun_strip0_kernel): non-zero enables it; the kernel's second row buffer
+  // starts hglobal2 words after hglobal
+  uint32_t incremental;
+  uint64_t hglobal2;
   uint32_t *hglobal;           // strip boundary rows in global memory (nullptr: shared memory)
   uint32_t k_one, k_mone;      // 1 and 0xffffffff: opaque multipliers that keep three lane-wise adds on the fma pipe
   uint32_t k_bias, k_one2;     // 0x80008000 and 0x00010001 as values ptxas cannot re-materialise per use
@@ -113,6 +114,26 @@ __device__ __forceinline__ uint32_t first_rows_equal(const uint32_t (&h)[R], uin
 // IADD3 / LOP3): the alu pipe — the bound of this kernel — issues 6.5 instead of 9.5 instructions
 // per cell pair (PRMT, 2 max, 3 min-against-1, half a max3).
 constexpr uint32_t kBias = 0x80008000u;
+
+// The strip boundary rows (one word per column and resident thread, 57 MB for 150 bp reads on 148
+// SMs) are written by strip k and read by strip k + 1 of the same pair a few microseconds later:
+// they belong in the 126 MB L2.  With default priority the 9 GB of direction words a chunk streams
+// through the same L2 kept evicting them — every row store ended up as a DRAM write-back and every
+// second load as a DRAM read (ncu r02: 13.3 GB written for 9.0 GB of directions).  evict_last keeps
+// the rows resident; the direction words go out evict-first (st.global.cs).
+__device__ __forceinline__ uint64_t row_policy() {
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ uint32_t ld_row(const uint32_t *p, uint64_t pol) {
+  uint32_t v;
+  asm volatile("ld.global.L2::cache_hint.u32 %0, [%1], %2;" : "=r"(v) : "l"(p), "l"(pol) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_row(uint32_t *p, uint32_t v, uint64_t pol) {
+  asm volatile("st.global.L2::cache_hint.u32 [%0], %1, %2;" ::"l"(p), "r"(v), "l"(pol) : "memory");
+}
 __device__ __forceinline__ uint32_t imad32(uint32_t a, uint32_t k, uint32_t b) {
   uint32_t d;
   asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(k), "r"(b));
@@ -171,7 +192,9 @@ __device__ __forceinline__ void strip_sweep(const StripArgs &a, StripCtx &c, con
   uint32_t a0 = 0, a1 = 0, a2 = 0, a3 = 0, b0 = 0, b1 = 0, b2 = 0, b3 = 0;  // 4 pending D words per pair
   uint32_t *hp = c.hrow;
   const uint32_t hstride = c.hstride;
-  uint32_t hnext = *hp;  // one column ahead: hides the L2 latency when the row lives in global memory
+  const bool grow = a.hglobal != nullptr;  // rows in global memory (L2-resident) or in shared memory
+  const uint64_t pol = row_policy();
+  uint32_t hnext = grow ? ld_row(hp, pol) : *hp;  // one column ahead: hides the L2 latency
 
   auto column = [&](const uint32_t (&hin)[R], uint32_t (&h)[R], const uint32_t xm1) {
     const uint32_t x = xm1 + 1;
@@ -179,7 +202,7 @@ __device__ __forceinline__ void strip_sweep(const StripArgs &a, StripCtx &c, con
     const uint32_t Wa = swt[qwA & 3], Wb = swt[qwB & 3];
     qwA >>= 2; qwB >>= 2;
     uint32_t hup = hnext;
-    if (xm1 + 1 < n) hnext = hp[hstride];
+    if (xm1 + 1 < n) hnext = grow ? ld_row(hp + hstride, pol) : hp[hstride];
     uint32_t diag = hdiag0;
     hdiag0 = hup;
     // penalty of the strip's first row
@@ -230,7 +253,7 @@ __device__ __forceinline__ void strip_sweep(const StripArgs &a, StripCtx &c, con
     }
     // an odd number of valid rows leaves the last one pending in mprev
     if (LOCAL) { if (LASTSTRIP ? (rv & 1u) : (R & 1)) cm = __vmaxu2(cm, mprev); }
-    if (!LASTSTRIP) *hp = h[R - 1];
+    if (!LASTSTRIP) { if (grow) st_row(hp, h[R - 1], pol); else *hp = h[R - 1]; }
     // direction planes of this column (both pairs at once), then one word per pair:
     // Top = !G & !U, Left = !G & U, Diagonal = G, Beginning = Z  (enums.rs:18-46)
     if (!SCORE) {
@@ -380,11 +403,6 @@ __global__ void __launch_bounds__(kStripBlock, 8) fill_strip_kernel(StripArgs a)
 
   for (uint32_t strip = 0; strip + 1 < nstrips; ++strip) {
     strip_sweep<R, LOCAL, STATEFUL, false, SCORE>(a, c, swt, strip);
-    if (STATEFUL && strip == 0 && a.brow0 && !a.list) {
-      // speculative pass: keep the bottom row of strip 0 (the next strip overwrites hrow)
-      uint32_t *bp = a.brow0 + ((size_t)(duo >> 5) * n) * 32 + (duo & 31);
-      for (uint32_t x = 0; x < n; ++x) __stcs(bp + (size_t)x * 32, c.hrow[(size_t)x * c.hstride]);
-    }
   }
   strip_sweep<R, LOCAL, STATEFUL, true, SCORE>(a, c, swt, nstrips - 1);
 
@@ -413,13 +431,17 @@ __global__ void __launch_bounds__(kStripBlock, 8) fill_strip_kernel(StripArgs a)
 // Incremental re-run (local mode, del != ext, more than one strip).  A wrongly assumed z bit changes
 // the penalty of ONE cell, (1, x+1); the disturbance dies out within a few rows (measured on the C3
 // reads: at most 9 rows deep in 99 % of the failing pairs, never below strip 0).  So the pairs on the
-// fail list first get only strip 0 recomputed with the observed bits: if its bottom row equals the
-// one the speculative pass kept (brow0), every lower strip, row m and with it the observed bits are
-// unchanged — the pair is settled after 1/nstrips of a full re-run.  The arg-max is re-derived from
-// the new best of strip 0 (P) and the pair's previous arg-max (G): G outside strip 0 is still the first
-// maximum of the unchanged strips, so the answer is P if P.v >= G.v (strip 0 wins ties by smaller y),
-// else G; G inside strip 0 stands only if P.v >= G.v.  Pairs whose bottom row changed, or whose
-// arg-max cannot be decided this way, go on to the full re-run passes.
+// fail list first get only strip 0 recomputed: once score-only with the bits the speculative pass
+// ASSUMED (all zero) — that reproduces the bottom row the speculative pass handed to strip 1 — and
+// once with the OBSERVED bits (directions rewritten).  Equal bottom rows prove that every lower
+// strip, row m and with it the observed bits are unchanged: the pair is settled after 2/nstrips of a
+// full re-run, and the speculative pass does not have to keep anything (it used to write the bottom
+// row of strip 0 of EVERY pair back to HBM: 300 B per pair and a 150-iteration copy loop).  The
+// arg-max is re-derived from the new best of strip 0 (P) and the pair's previous arg-max (G): G
+// outside strip 0 is still the first maximum of the unchanged strips, so the answer is P if
+// P.v >= G.v (strip 0 wins ties by smaller y), else G; G inside strip 0 stands only if P.v >= G.v.
+// Pairs whose bottom row changed, or whose arg-max cannot be decided this way, go on to the full
+// re-run passes.
 template <int R, bool SCORE>
 __global__ void __launch_bounds__(kStripBlock) rerun_strip0_kernel(StripArgs a) {
   __shared__ uint32_t swt[4];
@@ -443,27 +465,31 @@ __global__ void __launch_bounds__(kStripBlock) rerun_strip0_kernel(StripArgs a) 
     const uint32_t n = a.n;
     c.dA = SCORE ? nullptr : a.D + a.dl.word(c.sA, 0, 0);
     c.dB = SCORE ? nullptr : a.D + a.dl.word(c.sB, 0, 0);
-    c.hrow = a.hglobal + ((size_t)(pduo >> 5) * n) * 32 + (pduo & 31);
+    uint32_t *row_spec = a.hglobal + a.hglobal2 + ((size_t)(pduo >> 5) * n) * 32 + (pduo & 31);
+    uint32_t *row_obs = a.hglobal + ((size_t)(pduo >> 5) * n) * 32 + (pduo & 31);
     c.hstride = 32;
-    c.bestA = Best{0, 0, 0, -1};
-    c.bestB = Best{0, 0, 0, -1};
     c.mismatch = 0;
     c.corner = 0;
-    for (uint32_t x = 0; x < n; ++x) c.hrow[(size_t)x * 32] = kBias;  // row 0 (local), biased
+    // (1) what the speculative pass computed: assumed bits all zero, scores only
+    {
+      StripArgs spec = a;
+      spec.z_in = nullptr;
+      c.hrow = row_spec;
+      c.bestA = Best{0, 0, 0, -1};
+      c.bestB = Best{0, 0, 0, -1};
+      for (uint32_t x = 0; x < n; ++x) row_spec[(size_t)x * 32] = kBias;  // row 0 (local), biased
+      strip_sweep<R, true, true, false, true>(spec, c, swt, 0);
+    }
+    // (2) the observed bits, directions rewritten
+    c.hrow = row_obs;
+    c.bestA = Best{0, 0, 0, -1};
+    c.bestB = Best{0, 0, 0, -1};
+    for (uint32_t x = 0; x < n; ++x) row_obs[(size_t)x * 32] = kBias;
     strip_sweep<R, true, true, false, SCORE>(a, c, swt, 0);
 
-    // the kept bottom row of a slot: its duo in the speculative pass, low or high half
-    auto kept = [&](uint32_t slot) {
-      const uint32_t vduo = (slot >> 6) * 32 + (slot & 31), half = (slot >> 5) & 1u;
-      return reinterpret_cast<const uint16_t *>(a.brow0 + ((size_t)(vduo >> 5) * n) * 32 + (vduo & 31)) + half;
-    };
-    const uint16_t *kA = kept(c.sA), *kB = kept(c.sB);
-    bool chA = false, chB = false;
-    for (uint32_t x = 0; x < n; ++x) {
-      const uint32_t v = c.hrow[(size_t)x * 32];
-      chA |= (uint16_t)(v & 0xffffu) != kA[(size_t)x * 64];
-      chB |= (uint16_t)(v >> 16) != kB[(size_t)x * 64];
-    }
+    uint32_t diff = 0;  // per lane: some column of the bottom row changed
+    for (uint32_t x = 0; x < n; ++x) diff |= row_obs[(size_t)x * 32] ^ row_spec[(size_t)x * 32];
+    const bool chA = (diff & 0xffffu) != 0, chB = (diff >> 16) != 0;
     auto settle = [&](uint32_t bslot, uint32_t slot, const Best &p, bool changed) {
       const uint32_t pair = a.order ? a.order[bslot] : bslot;
       const int32_t st = a.fo.status[pair];

@@ -55,6 +55,15 @@ __device__ __forceinline__ double wmax3(double a, double b, double c) {
 }
 constexpr double kWarpFiniteBound = 1e290;
 
+// |max - cand| < f64::EPSILON (enums.rs:21,23,39,41) when max >= cand is known — here max was picked
+// from the candidates by compare-select over finite values, so max - cand >= +0.0 exactly and the
+// fabs is dropped.  (Measured alternatives, profiles/r02_fill_warp_f64_ncu.txt: the alu pipe, with
+// the selects, is this kernel's busiest at 68 %, the FP64 pipe has room — so the test stays a DSETP;
+// as an integer compare of the difference's high word against 0x3CB00000 it cost two alu
+// instructions per cell and gained nothing.  Predicated IMAD moves instead of FSEL for the max are
+// if-converted back into selects by ptxas.)  The exact kernel keeps the literal fabs / fmax form.
+__device__ __forceinline__ bool same_ge(int mx, int c) { return mx == c; }
+__device__ __forceinline__ bool same_ge(double mx, double c) { return __dsub_rn(mx, c) < DBL_EPSILON; }
 // "this cell may reach the running maximum": a conservative test that only triggers the ordered
 // rescan (which compares exactly).  FP64: the running maximum is never negative, so mx >= best
 // implies hi32(mx) >= hi32(best) as signed integers (a negative mx has a negative high word) — one
@@ -65,10 +74,15 @@ __device__ __forceinline__ bool may_hit(double mx, double best) {
   return __double2hiint(mx) >= __double2hiint(best);
 }
 
-// MODE: 0 global; 1 local with del == ext (static penalty, FP64 only: saves two selects per cell in
-// the matrix search); 2 local, any del / ext (a.stateful says whether the speculation is needed).
-// The INT32 instantiation of MODE 1 gave wrong scores on B200 (nvcc 12.9, cause not found; caught by
-// tests/test_warp.py::test_every_rows_per_lane_int), so INT32 static-penalty problems run MODE 2.
+// MODE: 0 global; 1 local with del == ext (static penalty: saves two selects per cell); 2 local, any
+// del / ext (a.stateful says whether the speculation is needed).
+// History: an intermediate round-1 build (1db19ef) saw wrong scores from the INT32 instantiation of
+// MODE 1 and routed INT32 around it.  The two places where MODE 1 and MODE 2 differed in generated
+// code then — the inline per-cell arg-max update and the rows below row m — were rewritten soon
+// after (a5e2e93: deferred rescan, idle lanes), and since then the failure does not reproduce: every
+// R = 2..16, INT32 and FP64, and the whole parity suite are bit-exact in BOTH modes on the B200
+// (compute-sanitizer is closed on this pool).  MODE 1 serves INT32 again;
+// ALNR_WARP_INT_MODE2=1 restores the old routing.
 template <typename T, int R, int MODE, bool MATS>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32) fill_warp_kernel(WarpArgs<T> a) {
   constexpr bool LOCAL = MODE != 0;
@@ -169,8 +183,12 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) fill_warp_kernel(WarpArgs
     for (uint32_t band = 0; band < nbands; ++band) {
       const uint32_t yb = band * BH + lane * R;  // this lane's rows: yb+1 .. yb+R (1-based)
       const bool last_band = band + 1 == nbands;
+      // The lane's R scores ping-pong between two register arrays (two steps per loop trip): the old
+      // H[y][x-1] — still needed as the diagonal of row y+1 — and the new H[y][x] never compete for a
+      // register, so the step loop carries no register moves (they were ~5 of 30 instructions per
+      // FP64 cell).  Both arrays start as column 0: a lane idles until step `lane`.
       uint32_t toff[R];
-      T h[R];
+      T hA[R], hB[R];
 #pragma unroll
       for (int r = 0; r < R; ++r) {
         const uint32_t y = yb + r + 1;
@@ -178,7 +196,8 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) fill_warp_kernel(WarpArgs
         toff[r] = smat_addr + (valid ? (uint32_t)t[y - 1] * V : 0u) * (uint32_t)sizeof(T);  // row of the matrix
         T v = T(0);
         if (!LOCAL && valid) v = (y == m) ? -(T(m) + T(1)) * del : -T(y) * del;  // :64-67, :70
-        h[r] = v;
+        hA[r] = v;
+        hB[r] = v;
       }
       T dprev = (LOCAL || yb == 0) ? T(0) : -T(yb) * del;  // H[yb][0]
       T bottom = T(0);
@@ -189,7 +208,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) fill_warp_kernel(WarpArgs
       const bool obs_lane = last_band && lane == m_lane;
       const bool top_lane = band == 0 && lane == 0;
       const uint32_t steps = n + 31;
-      for (uint32_t s = 0; s < steps; ++s, dp += 32) {
+      auto step = [&](const T (&hin)[R], T (&h)[R], const uint32_t s) {
         T up = shfl_up_t(bottom);
         const uint32_t c = s - lane;  // 0-based column; wraps for s < lane
         if (c < n && yb < m) {  // lanes whose rows all lie below row m idle (last band)
@@ -227,16 +246,16 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) fill_warp_kernel(WarpArgs
             if (MODE == 2 && r > 0) {
               // penalty = del iff the cell above is Beginning, i.e. hup == 0: both candidates are
               // formed off the dependent chain, the zero test of the cell above only selects
-              const T le = nsub(h[r], ext), ld = nsub(h[r], del);
+              const T le = nsub(hin[r], ext), ld = nsub(hin[r], del);
               top = zp ? ndel0 : nsub(hup, ext);
               lft = zp ? ld : le;
             } else {
-              top = nsub(hup, pen); lft = nsub(h[r], pen);
+              top = nsub(hup, pen); lft = nsub(hin[r], pen);
             }
             const T dg = nadd(diag, sc);
             const T mx = wmax3(top, lft, dg);
-            uint32_t d = Num<T>::same(mx, lft) ? DIR_LEFT : DIR_DIAGONAL;  // enums.rs:23/:41
-            d = Num<T>::same(mx, top) ? DIR_TOP : d;                       // enums.rs:21/:39
+            uint32_t d = same_ge(mx, lft) ? DIR_LEFT : DIR_DIAGONAL;  // enums.rs:23/:41
+            d = same_ge(mx, top) ? DIR_TOP : d;                       // enums.rs:21/:39
             if (LOCAL) {
               const bool zero = Num<T>::is_zero(mx);                       // enums.rs:37
               d = zero ? DIR_BEGINNING : d;
@@ -244,7 +263,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) fill_warp_kernel(WarpArgs
             }
             if (MODE != 2) pen = ext;
             bits |= d << (2 * r);
-            diag = h[r];
+            diag = hin[r];
             h[r] = mx;
             hup = mx;
             if (LOCAL) hit |= may_hit(mx, best);
@@ -288,7 +307,15 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) fill_warp_kernel(WarpArgs
             }
           }
         }
+        dp += 32;
+      };
+      uint32_t s = 0;
+#pragma unroll 1
+      for (; s + 1 < steps; s += 2) {
+        step(hA, hB, s);
+        step(hB, hA, s + 1);
       }
+      if (s < steps) step(hA, hB, s);
       __syncwarp();  // rowbuf / z words written by one lane are read by another
     }
     if (!stateful) break;

@@ -10,6 +10,8 @@ bool strip_eligible(const alnr_batch_impl &B, double value_bound);
 uint32_t d_rows_per_word(const alnr_batch_impl &B, uint32_t m);
 // pairs per resident wave of the strip kernel (chunk sizes are multiples of it).
 uint32_t strip_wave_pairs();
+// words of one boundary-row buffer (per chunk parity the batch keeps two of them, see kernels_strip.cu)
+uint64_t strip_row_words(const alnr_batch_impl &B);
 // one-time per-batch preparation (packed sequences, profile table).
 int strip_prepare(alnr_batch_impl &B);
 // phase 1 (B.stream): pack the chunk's sequences and run the speculative main pass.

@@ -32,10 +32,11 @@ static int warp_launch_one(cudaStream_t stream, const WarpArgs<T> &a) {
 
 template <typename T>
 static int warp_launch_any(cudaStream_t stream, const WarpArgs<T> &a, bool local, bool mats) {
-  // MODE 1 (compile-time static penalty): FP64 always; INT32 see kernels_warp.cuh
+  // MODE 1 (compile-time static penalty) for del == ext.  ALNR_WARP_INT_MODE2=1 sends INT32
+  // static-penalty problems through the MODE 2 code instead (the round-1 routing, kept for A/B runs
+  // and tests/test_warp.py::test_int32_static_penalty_both_modes; read per launch).
   constexpr bool kStaticMode = true;
-  static const bool int_mode1 = getenv("ALNR_WARP_INT_MODE1") != nullptr;
-  const bool static_ok = sizeof(T) == 8 || int_mode1;
+  const bool static_ok = sizeof(T) == 8 || getenv("ALNR_WARP_INT_MODE2") == nullptr;
   const int mode = !local ? 0 : ((a.stateful || !static_ok) ? 2 : 1);
   if (mats) {
     if (a.dl.rows_per_word != 8) return ALNR_INVALID_ARGUMENT;

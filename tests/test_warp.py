@@ -42,6 +42,25 @@ def test_every_rows_per_lane_int(hi):
         assert (res.status == 0).all()
 
 
+@pytest.mark.parametrize("force_mode2", [False, True])
+@pytest.mark.parametrize("hi", [40, 100, 180, 250, 310, 380, 440, 512])
+def test_int32_static_penalty_both_modes(hi, force_mode2, monkeypatch):
+    """INT32 local alignment with del == ext through the compile-time static-penalty instantiation
+    (MODE 1, the default again) and through the MODE 2 code (ALNR_WARP_INT_MODE2=1): round 1 saw
+    wrong MODE 1 scores on an intermediate build and routed around it; both must be bit-exact."""
+    if force_mode2:
+        monkeypatch.setenv("ALNR_WARP_INT_MODE2", "1")
+    else:
+        monkeypatch.delenv("ALNR_WARP_INT_MODE2", raising=False)
+    rng = np.random.default_rng(7000 + hi)
+    pairs = _ragged(rng, 64, max(24, hi - 60), hi, 24)
+    for d in (5, 11):
+        res = _check_batch("local", pairs, d, d, ab.get_blosum62(), numeric=N.NUM_I32)
+        assert (res.status == 0).all()
+    dna = _ragged(rng, 64, max(24, hi - 60), hi, 4, related=False)
+    _check_batch("local", dna, 1, 1, ab.dna_matrix(1, -1), numeric=N.NUM_I32)  # many ties and zeros
+
+
 @pytest.mark.parametrize("hi", [60, 90, 150, 200, 220, 280, 330, 410, 470, 520])
 def test_every_rows_per_lane_f64(hi):
     rng = np.random.default_rng(1000 + hi)
