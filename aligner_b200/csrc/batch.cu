@@ -253,7 +253,8 @@ bool alnr_batch_impl::use_warp(uint32_t m) const {
 DLayout alnr_batch_impl::layout_dims(uint32_t m, uint32_t n, bool wave) const {
   if (wave) return DLayout::make_blocked(wave_band_rows(m), m, n);
   if (use_warp(m)) return DLayout::make_skewed(want_matrices ? 8 : warp_pick_rows(m), m, n);
-  return DLayout::make(d_rows_per_word(*this, m), m, n, numeric == ALNR_NUM_I16X2);
+  // strip kernel: interleaved map (a warp's column store is one 128-byte line), bit-plane words
+  return DLayout::make(d_rows_per_word(*this, m), m, n, false, numeric == ALNR_NUM_I16X2 ? 1 : 0);
 }
 
 DLayout alnr_batch_impl::layout_for(const Chunk &c) const {

@@ -188,8 +188,9 @@ __device__ __forceinline__ void strip_sweep(const StripArgs &a, StripCtx &c, con
   uint32_t nthr = pack2(-thrA, -thrB) ^ kBias;  // cm' + nthr = cm - thr lane-wise (the biases cancel)
   uint32_t zacc = 0, zaccB = 0;
   uint32_t qwA = 0, qwB = 0;
-  uint32_t *dpA = c.dA + (size_t)strip * a.dl.ncols, *dpB = c.dB + (size_t)strip * a.dl.ncols;
-  uint32_t a0 = 0, a1 = 0, a2 = 0, a3 = 0, b0 = 0, b1 = 0, b2 = 0, b3 = 0;  // 4 pending D words per pair
+  // interleaved D layout (common.cuh): word (strip, x) of the 32 slots of a group are consecutive, so
+  // the warp's store of one column is one complete 128-byte line per pair
+  uint32_t *dpA = c.dA + (size_t)strip * a.dl.ncols * 32, *dpB = c.dB + (size_t)strip * a.dl.ncols * 32;
   uint32_t *hp = c.hrow;
   const uint32_t hstride = c.hstride;
   const bool grow = a.hglobal != nullptr;  // rows in global memory (L2-resident) or in shared memory
@@ -260,13 +261,12 @@ __device__ __forceinline__ void strip_sweep(const StripArgs &a, StripCtx &c, con
       uint32_t P0, P1;
       if (LOCAL) { P0 = ~accN | (~accG & accU); P1 = ~accN | accG; }
       else { P0 = ~accG & accU; P1 = accG; }
-      a0 = a1; a1 = a2; a2 = a3; a3 = __byte_perm(P0, P1, 0x5410);
-      b0 = b1; b1 = b2; b2 = b3; b3 = __byte_perm(P0, P1, 0x7632);
-      if ((xm1 & 3) == 3) {
-        // streaming stores: D is written once and read only by the traceback; keep L2 for the rows
-        __stcs(reinterpret_cast<uint4 *>(dpA + (xm1 - 3)), make_uint4(a0, a1, a2, a3));
-        if (!c.dupB) __stcs(reinterpret_cast<uint4 *>(dpB + (xm1 - 3)), make_uint4(b0, b1, b2, b3));
-      }
+      // streaming stores of whole lines: D is written once and read only by the traceback; L2 is for
+      // the boundary rows.  (16-byte stores of 4 columns into a contiguous per-pair layout left every
+      // 32-byte sector half written for ~3 us; half of them reached DRAM as two partial writes and the
+      // open lines crowded the rows out of L2: 13.5 GB written for 9.0 GB of directions.)
+      __stcs(dpA + (size_t)xm1 * 32, __byte_perm(P0, P1, 0x5410));
+      if (!c.dupB) __stcs(dpB + (size_t)xm1 * 32, __byte_perm(P0, P1, 0x7632));
     }
 
     if (LOCAL) {
@@ -329,12 +329,6 @@ __device__ __forceinline__ void strip_sweep(const StripArgs &a, StripCtx &c, con
     column(hA, hB, xm1);
 #pragma unroll
     for (int r = 0; r < R; ++r) hA[r] = hB[r];
-  }
-  // flush a partial group of D words (n not a multiple of 4)
-  if (!SCORE && (n & 3)) {
-    for (uint32_t k = n & 3; k < 4; ++k) { a0 = a1; a1 = a2; a2 = a3; a3 = 0; b0 = b1; b1 = b2; b2 = b3; b3 = 0; }
-    __stcs(reinterpret_cast<uint4 *>(dpA + (n & ~3u)), make_uint4(a0, a1, a2, a3));
-    if (!c.dupB) __stcs(reinterpret_cast<uint4 *>(dpB + (n & ~3u)), make_uint4(b0, b1, b2, b3));
   }
   if (LASTSTRIP) {
     c.corner = hA[R - 1];

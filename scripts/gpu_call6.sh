@@ -1,7 +1,7 @@
 #!/bin/bash
 cd "$GRAFT_REPO_ROOT" 2>/dev/null || cd /root/repo
 O=gpurun_out
-timeout 900 python -m pytest tests/test_gpu_parity.py tests/test_compact.py tests/test_full_size.py -m gpu -x -q > $O/pytest6.log 2>&1; echo "pytest rc=$?" >> $O/pytest6.log; tail -3 $O/pytest6.log
+timeout 900 python -m pytest tests/test_gpu_parity.py tests/test_compact.py tests/test_full_size.py tests/test_scores.py tests/test_multi.py -m gpu -x -q > $O/pytest6.log 2>&1; echo "pytest rc=$?" >> $O/pytest6.log; tail -3 $O/pytest6.log
 timeout 600 python bench.py --steps 5 --warmup 3 --no-configs --no-e2e-strings --no-cpu-baseline > $O/bench_v4.json 2> $O/bench_v4.err; echo "bench rc=$?"
 python - <<'PY'
 import json
