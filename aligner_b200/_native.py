@@ -106,6 +106,10 @@ SIGNATURES = {
     "alnr_score_batch": (C.c_int, [C.POINTER(Params), C.POINTER(Batch), f64p, f64p, u32p, i32p]),
     "alnr_batch_create_scores": (C.c_int, [C.POINTER(Params), C.POINTER(Batch), C.POINTER(C.c_void_p)]),
     "alnr_batch_download_scores": (C.c_int, [C.c_void_p, f64p, f64p, u32p, i32p]),
+    "alnr_score_batch_noalloc": (C.c_int, [C.POINTER(Params), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                           C.c_uint64, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p,
+                                           C.c_void_p, C.c_void_p]),
+    "alnr_noalloc_scratch_bytes": (C.c_uint64, []),
     "alnr_pwm_seq_create": (C.c_int, [u8p, C.c_uint64, C.c_int, C.POINTER(C.c_void_p)]),
     "alnr_pwm_seq_len": (C.c_uint64, [C.c_void_p]),
     "alnr_pwm_seq_destroy": (None, [C.c_void_p]),

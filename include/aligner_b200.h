@@ -221,6 +221,31 @@ int alnr_batch_create_scores(const alnr_params *p, const alnr_batch *b, alnr_bat
 int alnr_batch_download_scores(alnr_batch_handle *h, double *f, double *corner, uint32_t *end_yx,
                                int32_t *status);
 
+/* ---- score-only batch that allocates nothing ----------------------------------------------------
+ * No counterpart in the reference: added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  Same results as alnr_score_batch (f, corner, end_yx, status — see above) from ONE kernel
+ * launch on `stream` (a cudaStream_t, NULL = the default stream): no cudaMalloc / cudaFree, no
+ * copies, no pool.  The call returns after enqueueing; synchronise the stream before reading.
+ *  - d_q, d_q_off, d_t, d_t_off, d_f, d_corner, d_end_yx, d_status are DEVICE pointers on device
+ *    p->device (-1 = device 0); output pointers may be NULL.  p->matrix (host, V*V) goes by value.
+ *  - max_query_len / max_target_len: the caller's promise about the longest sequences.  A longer
+ *    pair gets status ALNR_INVALID_ARGUMENT (it is not computed).
+ *  - The scratch (one score column per pair) is a static device array of
+ *    ALNR_NOALLOC_SCRATCH_BYTES that every GPU loading the library holds until exit.  Limit:
+ *      ceil(count / 32) * 32 * (max_target_len + 1) * (4 integer problems | 8 FP64) <= that size
+ *    (e.g. 8192 pairs x 500 rows integer, 4096 pairs x 500 rows FP64); beyond it the call returns
+ *    ALNR_INVALID_ARGUMENT with the arithmetic in alnr_last_error_detail().  Split the batch.
+ *  - Every call on a device shares the array and it keeps the last call's contents (nothing in it
+ *    needs clearing: each pair writes its column 0 first).  Calls that overlap on the same GPU —
+ *    different streams or host threads — RACE on it: serialise them. */
+#define ALNR_NOALLOC_SCRATCH_BYTES (16u << 20)
+int alnr_score_batch_noalloc(const alnr_params *p, const uint8_t *d_q, const uint64_t *d_q_off,
+                             const uint8_t *d_t, const uint64_t *d_t_off, uint64_t count,
+                             uint32_t max_query_len, uint32_t max_target_len, double *d_f,
+                             double *d_corner, uint32_t *d_end_yx, int32_t *d_status, void *stream);
+uint64_t alnr_noalloc_scratch_bytes(void);
+
 /* ---- PWM aligner --------------------------------------------------------
  * PWMAligner::perform_alignment (aligner-core/src/pwm/mod.rs:29-126): Smith-Waterman-like local
  * alignment of a DNA window (the DP rows) against the L columns of a 4 x L position-weight matrix,
