@@ -225,7 +225,7 @@ int alnr_batch_impl::plan_chunks(const uint64_t *q_off, const uint64_t *t_off) {
       ck.wave = true; ck.wave_pair = (uint32_t)pidx; ck.q0 = q_off[pidx]; ck.t0 = t_off[pidx];
       ck.q1 = q_off[pidx + 1]; ck.t1 = t_off[pidx + 1];
       // a direction matrix larger than the scratch budget: keep band rows, re-fill group by group
-      if (!score_only && wave_band_rows(m) == 4 && !getenv("ALNR_BAND_COLUMN")) ck.ckpt_group = wave_ckpt_group(m, n, budget);
+      if (!score_only) ck.ckpt_group = wave_ckpt_group(m, n, budget);
     } else
     if (uniform) { ck.q0 = q_off[s]; ck.q1 = q_off[s + c]; ck.t0 = t_off[s]; ck.t1 = t_off[s + c]; }
     chunks.push_back(ck);
@@ -733,18 +733,12 @@ int alnr_batch_impl::phase2(size_t ci) {
         ta, d_moves.p, cxy, stride, G, c.n_max, c.m_max, nmw);
   } else if (c.ckpt_group) {
     return wave_ckpt_trace(*this, c, dl, ta, s2);
-  } else if (dl.blocked == 4 && c.count == 1 && !getenv("ALNR_TRACE_LOCKSTEP")) {
-    // long pair, 4 x 4 tiles: window walk that emits moves, then a parallel expansion
+  } else if (dl.blocked == 4 && c.count == 1) {
+    // long pair, 4 x 4 tiles: cooperative window walk that emits moves, then a parallel expansion
     LongTrace lt{d_moves.p, d_moves.p + nmw, d_moves.p + 3 * (size_t)nmw};
-    // ALNR_TRACE_SEQ=1: the one-lane window walk (it records the cells itself; A/B runs)
-    static const bool seq_walk = getenv("ALNR_TRACE_SEQ") != nullptr;
-    if (seq_walk) {
-      trace_walk_window_kernel<<<1, 32, 0, s2>>>(ta, lt);
-    } else {
-      trace_walk_coop_kernel<<<1, 32, 0, s2>>>(ta, lt);
-      ALNR_LAUNCHED();
-      trace_cells_kernel<<<1, 1024, 0, s2>>>(ta, lt);
-    }
+    trace_walk_coop_kernel<<<1, 32, 0, s2>>>(ta, lt);
+    ALNR_LAUNCHED();
+    trace_cells_kernel<<<1, 1024, 0, s2>>>(ta, lt);
     ALNR_LAUNCHED();
     trace_expand_long_kernel<<<(nmw + 255) / 256, 256, 0, s2>>>(ta, lt);
   } else if (dl.blocked) {

@@ -155,7 +155,9 @@ __device__ __forceinline__ void tile_step(TileLane &L, const int4 *sm_sc, const 
 
 // BandArgs as in kernels_band.cuh, except: rows = [nbands][npad] indexed by the 0-based column
 // (npad = n rounded up to 4, preset to kTileSentinel), prog unused.
-template <bool LOCAL>
+// REFILL (checkpointed traceback, wave.cu): a compile-time variant, so that the ordinary sweep keeps
+// the instruction schedule it was tuned with (as run-time conditions the same lines cost it 12 %).
+template <bool LOCAL, bool REFILL = false>
 __global__ void __launch_bounds__(32) fill_tile_kernel(BandArgs a) {
   extern __shared__ int4 tsm[];  // [V][32] score quadruples, then 32 ints of boundary values
   const uint32_t lane = threadIdx.x;
@@ -167,14 +169,14 @@ __global__ void __launch_bounds__(32) fill_tile_kernel(BandArgs a) {
   const int del = a.del, ext = a.ext;
   TileLane L;
   L.best_v = 0; L.best_y = 0; L.best_x = 0;
-  const bool refill = a.band_end != 0;  // checkpointed traceback: bands [band0, band_end), rows are final
-  const uint32_t band_end = refill ? a.band_end : a.nbands;
-  if (a.ckpt) {  // the path crosses this group iff its current cell lies inside the group's rows
+  constexpr bool refill = REFILL;  // checkpointed traceback: bands [band0, band_end), rows are final
+  const uint32_t band_end = REFILL ? a.band_end : a.nbands;
+  if (REFILL && a.ckpt) {  // the path crosses this group iff its current cell lies inside the group's rows
     const uint32_t cy = a.ckpt[0], cx = a.ckpt[1], done = a.ckpt[4];
     if (done || cx == 0 || cy <= a.band0 * 128u || cy > band_end * 128u) return;
   }
 
-  for (uint32_t band = a.band0 + blockIdx.x; band < band_end; band += gridDim.x) {
+  for (uint32_t band = (REFILL ? a.band0 : 0u) + blockIdx.x; band < band_end; band += gridDim.x) {
     const uint32_t yl0 = band * 128u + lane * 4u;  // this lane's rows: yl0+1 .. yl0+4 (1-based)
     uint32_t trow[4];
 #pragma unroll
@@ -200,7 +202,7 @@ __global__ void __launch_bounds__(32) fill_tile_kernel(BandArgs a) {
     const bool store_d = yl0 < m && a.D != nullptr;  // score-only calls pass no D scratch
     const bool last_band = band + 1 == a.nbands;
     const bool row_out = lane == 31 && !last_band && !refill;
-    L.dptr = a.D + (size_t)(yl0 / 4 - a.strip0) * a.dcols;  // this lane's 4-row strip
+    L.dptr = a.D + (size_t)(yl0 / 4 - (REFILL ? a.strip0 : 0u)) * a.dcols;  // this lane's 4-row strip
     L.rowp = a.rows + (size_t)band * npad;
     const uint32_t steps = ntiles + 31;
     // A band cannot start before the band above has finished its first chunk, i.e. ~39 steps per

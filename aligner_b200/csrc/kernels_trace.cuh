@@ -665,13 +665,14 @@ static __global__ void __launch_bounds__(32) traceback_warp_kernel(TraceArgs a, 
 // Two-phase traceback of ONE long pair through the "blocked" D layout with 4 x 4 tiles per word
 // (tile pipeline kernel).  The walk is one dependent chain of n + m steps; everything that is not
 // on that chain is moved off it:
-//   phase W (trace_walk_window_kernel, one warp): lane 0 walks inside a WINDOW of 32 strips x 64
+//   phase W (trace_walk_coop_kernel, one warp): the walk happens inside a WINDOW of 32 strips x 64
 //     words (128 rows x 256 columns, 8 KB) held in shared memory and emits only 2-bit moves (16 per
-//     word) plus the cell at which every move word starts; no sequence loads, no alignment
-//     stores.  All 32 lanes fetch a window with 16-byte cp.async; while lane 0 walks, the window
-//     the path is predicted to enter next (straight up the diagonal, 16 words of slack to the
-//     right, 47 to the left) is already in flight into the second buffer.  A path that leaves a
-//     window elsewhere (long gap runs) gets a window loaded at its cell.
+//     word); no sequence loads, no alignment stores.  All 32 lanes fetch a window with 16-byte
+//     cp.async; while the window is walked, the one the path is predicted to enter next (straight
+//     up the diagonal, 16 words of slack to the right, 47 to the left) is already in flight into the
+//     second buffer.  A path that leaves a window elsewhere (long gap runs) gets a window loaded at
+//     its cell.  (The first version walked the window with lane 0 alone: 8.9 ms per 10^5 x 10^5
+//     against 1.7 ms for the cooperative walk below; removed in round 2.)
 //   phase E (trace_expand_long_kernel, one thread per move word): re-walks its 16 moves from the
 //     recorded cell and writes the two aligned strings, right-aligned in the pair's slot exactly
 //     as traceback_kernel does (seed pair first: simple/mod.rs:102-105, :213-216).
@@ -709,124 +710,8 @@ __device__ __forceinline__ void win_fetch(uint32_t *buf, const uint32_t *D, cons
   asm volatile("cp.async.commit_group;" ::: "memory");
 }
 
-static __global__ void __launch_bounds__(32) trace_walk_window_kernel(TraceArgs a, LongTrace lt) {
-  __shared__ __align__(16) uint32_t win[2][kWinStrips * kWinWords];
-  const uint32_t lane = threadIdx.x;
-  const uint32_t pair = a.cv.order ? a.cv.order[a.cv.first] : a.cv.first;
-  if (a.fo.status[pair] != 0) {
-    if (lane == 0) { lt.tail[0] = 0; lt.tail[1] = 0; lt.tail[2] = 0; }
-    return;
-  }
-  const bool glob = a.mode == 0;
-  uint32_t cy = a.fo.start[2 * (size_t)pair], cx = a.fo.start[2 * (size_t)pair + 1];
-  uint32_t cnt = 0, acc = 0;
-  int cur = 0;
-  if (lane == 0) { lt.cell[0] = cy; lt.cell[1] = cx; }
-  // current window: (s_bot, w_lo) in buffer `cur`; valid strips max(0, s_bot - 31) .. s_bot
-  uint32_t s_bot = 0, w_lo = 0;
-  bool have = false, done = false;
-  while (!done) {
-    const bool inside = cy && cx;
-    const uint32_t strip = inside ? (cy - 1) >> 2 : 0, wc = inside ? (cx - 1) >> 2 : 0;
-    if (inside && !have) {  // no usable window: fetch one at the current cell
-      s_bot = strip; w_lo = win_lo(wc);
-      win_fetch(win[cur], a.D, a.dl, s_bot, w_lo, lane);
-      asm volatile("cp.async.wait_group 0;" ::: "memory");
-      __syncwarp();
-      have = true;
-    }
-    // predicted next window: the path climbs the rest of this window along the diagonal
-    const uint32_t s_top = s_bot >= kWinStrips - 1 ? s_bot - (kWinStrips - 1) : 0;
-    bool pre = false;
-    uint32_t ns_bot = 0, nw_lo = 0, nw_hi = 0;
-    if (inside && s_top > 0) {
-      const uint32_t climb = strip - s_top + 1;
-      if (wc > climb) {
-        ns_bot = s_top - 1;
-        nw_hi = min(wc - climb + 16, a.dl.ncols - 1);
-        nw_lo = win_lo(nw_hi);
-        win_fetch(win[cur ^ 1], a.D, a.dl, ns_bot, nw_lo, lane);
-        pre = true;
-      }
-    }
-    if (lane == 0) {
-      const uint32_t *wb = win[cur];
-      // one move: append its 2 bits; a full word goes out together with the cell the next word starts at
-      auto put = [&](uint32_t d, uint32_t ny, uint32_t nx) {
-        acc |= d << (2 * (cnt & 15));
-        ++cnt;
-        if ((cnt & 15) == 0) {
-          lt.moves[(cnt >> 4) - 1] = acc; acc = 0;
-          lt.cell[2 * (cnt >> 4)] = ny; lt.cell[2 * (cnt >> 4) + 1] = nx;
-        }
-      };
-      for (;;) {
-        if (cy == 0 || cx == 0) {  // border: Beginning in local mode, a run to (0, 0) in global mode
-          if (glob) {              // simple/mod.rs:59-67
-            while (cx) { --cx; put(DIR_LEFT, cy, cx); }
-            while (cy) { --cy; put(DIR_TOP, cy, cx); }
-          }
-          done = true;
-          break;
-        }
-        const uint32_t st = (cy - 1) >> 2, ww = (cx - 1) >> 2;
-        if (st < s_top || ww < w_lo) break;  // left the window
-        const uint32_t w = wb[(s_bot - st) * kWinWords + (ww - w_lo)];
-        // walk inside the 4 x 4 tile on local coordinates: only (w >> sh) -> d -> (ly, lx) -> sh is a
-        // chain; the tile's <= 7 moves are collected in `tm` and appended to the move string once
-        const int ly0 = (int)((cy - 1) & 3), lx0 = (int)((cx - 1) & 3);
-        int ly = ly0, lx = lx0;
-        const uint32_t y0 = st * 4 + 1, x0 = ww * 4 + 1;
-        bool begin = false;
-        uint32_t tm = 0, tc = 0;
-        do {
-          const uint32_t d = (w >> (8 * lx + 2 * ly)) & 3u;
-          if (d == DIR_BEGINNING) { begin = true; break; }  // local mode only (enums.rs:37)
-          ly -= (d != DIR_LEFT);
-          lx -= (d != DIR_TOP);
-          tm |= d << (2 * tc);
-          ++tc;
-        } while (ly >= 0 && lx >= 0);
-        const uint32_t fill = cnt & 15;
-        const unsigned long long wide = (unsigned long long)acc | ((unsigned long long)tm << (2 * fill));
-        cnt += tc;
-        acc = (uint32_t)wide;
-        if (fill + tc >= 16) {  // a move word is complete: it goes out with the cell the next word starts at
-          int py = ly0, px = lx0;
-          for (uint32_t k = 0, mm = tm; k < 16 - fill; ++k, mm >>= 2) {
-            py -= ((mm & 3u) != DIR_LEFT);
-            px -= ((mm & 3u) != DIR_TOP);
-          }
-          lt.moves[(cnt >> 4) - 1] = acc;
-          lt.cell[2 * (cnt >> 4)] = y0 + py; lt.cell[2 * (cnt >> 4) + 1] = x0 + px;
-          acc = (uint32_t)(wide >> 32);
-        }
-        cy = y0 + ly; cx = x0 + lx;
-        if (begin) { done = true; break; }
-      }
-    }
-    cy = __shfl_sync(0xffffffffu, cy, 0);
-    cx = __shfl_sync(0xffffffffu, cx, 0);
-    done = __shfl_sync(0xffffffffu, (int)done, 0) != 0;
-    asm volatile("cp.async.wait_group 0;" ::: "memory");
-    __syncwarp();
-    have = false;
-    if (!done && pre && cy && cx) {
-      const uint32_t st = (cy - 1) >> 2, ww = (cx - 1) >> 2;
-      const uint32_t ns_top = ns_bot >= kWinStrips - 1 ? ns_bot - (kWinStrips - 1) : 0;
-      if (st <= ns_bot && st >= ns_top && ww >= nw_lo && ww <= nw_hi) {
-        cur ^= 1; s_bot = ns_bot; w_lo = nw_lo; have = true;
-      }
-    }
-  }
-  if (lane == 0) {
-    if (cnt & 15) lt.moves[cnt >> 4] = acc;
-    lt.tail[0] = cnt; lt.tail[1] = cy; lt.tail[2] = cx;
-  }
-}
 
-// Cooperative window walk: the same windows and the same move string as trace_walk_window_kernel,
-// but the 32 strips of a window are walked by the 32 lanes AT ONCE.  Lane l takes strip s_bot - l
+// Cooperative window walk: the 32 strips of a window are walked by the 32 lanes AT ONCE.  Lane l takes strip s_bot - l
 // and starts on the bottom row of its strip at a GUESSED column — where the path would arrive if
 // it kept climbing the diagonal from the last known cell.  The guesses are then stitched: lane l's
 // walk is the real path iff lane l-1's walk is and leaves its strip at the column lane l started

@@ -1,5 +1,5 @@
-// wave.cu — host side of the intra-pair wavefront path for one long pair: the band pipeline
-// kernel (kernels_band.cuh).
+// wave.cu — host side of the intra-pair wavefront path for one long pair: the tile pipeline
+// (kernels_tile.cuh) and the checkpointed traceback.
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
@@ -77,8 +77,8 @@ int wave_ckpt_trace(alnr_batch_impl &B, const Chunk &c, const DLayout &dl, const
     const uint32_t b0 = b1 > G ? b1 - G : 0;
     a.band0 = b0; a.band_end = b1; a.strip0 = b0 * 32;
     const unsigned grid = std::min<unsigned>(b1 - b0, resident);
-    if (local) fill_tile_kernel<true><<<grid, 32, smem, s>>>(a);
-    else fill_tile_kernel<false><<<grid, 32, smem, s>>>(a);
+    if (local) fill_tile_kernel<true, true><<<grid, 32, smem, s>>>(a);
+    else fill_tile_kernel<false, true><<<grid, 32, smem, s>>>(a);
     ALNR_LAUNCHED();
     traceback_warp_kernel<<<1, 32, 0, s>>>(ta, ck, b0 * 128u, b0 * 32u);
     ALNR_LAUNCHED();
@@ -174,68 +174,13 @@ static int tile_run_pair(alnr_batch_impl &B, const Chunk &c, const DLayout &dl, 
   return ALNR_OK;
 }
 
-// Band pipeline (kernels_band.cuh): one persistent launch for the whole pair.
-static int band_run_pair(alnr_batch_impl &B, const Chunk &c, const DLayout &dl, const FillOut &fo) {
-  BandArgs a;
-  a.q = B.d_q.p + c.q0; a.t = B.d_t.p + c.t0;
-  a.n = c.n_max; a.m = c.m_max; a.V = B.V; a.matrix = B.d_mati.p;
-  a.del = (int)B.del; a.ext = (int)B.ext;
-  const uint32_t R = dl.rows_per_word, band_rows = 32 * R;
-  a.nbands = (a.m + band_rows - 1) / band_rows;
-  const bool local = B.mode == ALNR_LOCAL;
-  // scratch: [best (8 B)][corner][pad][prog nbands][rows nbands * (n + 1)]
-  const size_t words = 4 + (size_t)a.nbands + (size_t)a.nbands * (a.n + 1);
-  if (B.d_band.n < words) {
-    // a longer pair than the previous one of this batch: its fill may still be running on the old rows
-    if (B.d_band.p) ALNR_CUDA(cudaStreamSynchronize(B.stream));
-    ALNR_CUDA(B.d_band.alloc(words));
-  }
-  int *base = B.d_band.p;
-  a.best = reinterpret_cast<unsigned long long *>(base);
-  a.corner_out = base + 2;
-  a.prog = reinterpret_cast<uint32_t *>(base + 4);
-  a.rows = base + 4 + a.nbands;
-  a.D = B.Dp();
-  a.dcols = dl.ncols;
-  static unsigned resident = 0;
-  if (!resident) {
-    int occ0 = 0, occ1 = 0, sms = 0, dev = 0;
-    ALNR_CUDA(cudaGetDevice(&dev));
-    ALNR_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    const size_t smem0 = 32 * 32 * 4;
-    ALNR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ0, fill_band_kernel<4, false>, 32, smem0));
-    ALNR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ1, fill_band_kernel<4, true>, 32, smem0));
-    resident = (unsigned)std::max(1, std::min(occ0, occ1)) * (unsigned)std::max(1, sms);
-  }
-  band_init_kernel<<<(a.nbands + 255) / 256, 256, 0, B.stream>>>(a);
-  ALNR_LAUNCHED();
-  const unsigned grid = std::min<unsigned>(a.nbands, resident);  // every block must be resident
-  const size_t smem = (size_t)B.V * B.V * 4;
-  if (R == 2) {
-    if (local) fill_band_kernel<2, true><<<grid, 32, smem, B.stream>>>(a);
-    else fill_band_kernel<2, false><<<grid, 32, smem, B.stream>>>(a);
-  } else {
-    if (local) fill_band_kernel<4, true><<<grid, 32, smem, B.stream>>>(a);
-    else fill_band_kernel<4, false><<<grid, 32, smem, B.stream>>>(a);
-  }
-  ALNR_LAUNCHED();
-  band_finish_kernel<<<1, 1, 0, B.stream>>>(a, local ? 1 : 0, fo, c.wave_pair);
-  ALNR_LAUNCHED();
-  return ALNR_OK;
-}
-
-// rows per lane of the band pipeline: thinner bands = more warps in flight (ALNR_BAND_R overrides)
+// rows per lane of the tile pipeline (its D layout is DLayout::make_blocked(4, ...))
 uint32_t wave_band_rows(uint32_t m) {
-  static const int env = std::getenv("ALNR_BAND_R") ? std::atoi(std::getenv("ALNR_BAND_R")) : 0;
-  if (env == 2) return 2u;  // first-generation column kernel with 64-row bands
   (void)m;
   return 4u;  // measured: 128-row bands beat 64-row bands at 3 x 10^4 and at 10^5 (pipeline fill dominates)
 }
 
 int wave_run_pair(alnr_batch_impl &B, const Chunk &c, const DLayout &dl, const FillOut &fo) {
-  // ALNR_BAND_COLUMN=1 / ALNR_BAND_R=2: the first-generation column-per-step kernel (A/B runs)
-  static const bool column = std::getenv("ALNR_BAND_COLUMN") != nullptr;
-  if (column || dl.rows_per_word != 4) return band_run_pair(B, c, dl, fo);
   return tile_run_pair(B, c, dl, fo);
 }
 

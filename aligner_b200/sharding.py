@@ -12,7 +12,7 @@ import ctypes as C
 import numpy as np
 
 from . import _native as N
-from .batch import PackedPairs, align_batch
+from .batch import BatchResult, PackedPairs, align_batch
 from .heuristic import heuristic_batch
 
 BLOCK = N.FITNESS_BLOCK
@@ -127,21 +127,85 @@ def matrix_search_sharded(pairs, matrices, del_, ext, kd, r_squared, frequencies
     return fitness, (lo, hi), best_k, best_f, f, st
 
 
-def align_batch_sharded(mode, pairs, matrix, del_, ext, device=-1, gather=True):
+def _gather_arrays(arrs, dst=0):
+    """Rank ``dst`` receives every rank's list of numpy arrays, the others get None.  No pickling of
+    the payload: the byte sizes travel in one all_gather of an int64 tensor, the arrays as ONE uint8
+    tensor per rank (padded to the longest) through ``gather`` — on the GPU for NCCL, on the CPU for
+    gloo."""
+    import torch
+    d = _dist()
+    rank, world = _rank_world()
+    dev = torch.device("cuda", torch.cuda.current_device()) if d.get_backend() == "nccl" else torch.device("cpu")
+    arrs = [np.ascontiguousarray(a) for a in arrs]
+    sizes = torch.tensor([a.nbytes for a in arrs], dtype=torch.int64, device=dev)
+    all_sizes = [torch.zeros_like(sizes) for _ in range(world)]
+    d.all_gather(all_sizes, sizes)
+    totals = [int(t.sum()) for t in all_sizes]
+    cap = max(max(totals), 1)
+    buf = torch.zeros(cap, dtype=torch.uint8, device=dev)
+    pos = 0
+    for a in arrs:
+        if a.nbytes:
+            buf[pos:pos + a.nbytes] = torch.from_numpy(a.reshape(-1).view(np.uint8)).to(dev)
+        pos += a.nbytes
+    bins = [torch.zeros(cap, dtype=torch.uint8, device=dev) for _ in range(world)] if rank == dst else None
+    d.gather(buf, bins, dst=dst)
+    if rank != dst:
+        return None
+    out = []
+    for r in range(world):
+        host = bins[r].cpu().numpy()
+        pos, got = 0, []
+        for k, a in enumerate(arrs):  # same dtypes and trailing shapes on every rank
+            nb = int(all_sizes[r][k])
+            got.append(host[pos:pos + nb].view(a.dtype).reshape((-1,) + a.shape[1:]).copy())
+            pos += nb
+        out.append(got)
+    return out
+
+
+def align_batch_sharded(mode, pairs, matrix, del_, ext, device=-1, gather=True, compact=False):
     """C3 on N ranks: this rank aligns its contiguous range of pairs (balanced by sum of n*m) on its
     own GPU; no collective on the data path.  With ``gather`` rank 0 receives every rank's
-    (lo, hi, BatchResult) in rank order (``gather_object``), the other ranks get their own only."""
+    (lo, hi, result) in rank order, the other ranks get their own only; the arrays travel as raw
+    tensors (``_gather_arrays``), nothing is pickled.  ``compact``: results in the compact format
+    (CompactResult: start cell + 2-bit moves, ~5x fewer bytes to gather).  Inside one process
+    ``align_batch(..., n_gpus=N)`` (alnr_align_batch_multi) does the same without any gather."""
+    from .batch import CompactResult
     rank, world = _rank_world()
     cells = np.diff(pairs.q_off).astype(np.float64) * np.diff(pairs.t_off).astype(np.float64)
     lo, hi = shard_range(pairs.count, rank, world, cells)
-    res = align_batch(mode, slice_pairs(pairs, lo, hi), matrix, del_, ext, device=device)
+    sub = slice_pairs(pairs, lo, hi)
+    res = align_batch(mode, sub, matrix, del_, ext, device=device, compact=compact)
     mine = (lo, hi, res)
     d = _dist()
     if not gather or d is None or world == 1:
         return [mine]
-    out = [None] * world if rank == 0 else None
-    d.gather_object(mine, out, dst=0)
-    return out if rank == 0 else [mine]
+    if compact:
+        used = res.move_words()
+        fields = ["f", "corner", "coords", "end_yx", "aln_len", "status", "moves_off", "moves"]
+        arrs = [getattr(res, k) if k != "moves" else res.moves[:used] for k in fields]
+    else:
+        fields = ["f", "corner", "coords", "aln_off", "aln_len", "status", "q_aln", "t_aln"]
+        arrs = [getattr(res, k) for k in fields]
+    bounds = np.array([lo, hi], dtype=np.int64)
+    got = _gather_arrays([bounds] + arrs, dst=0)
+    if rank != 0:
+        return [mine]
+    out = []
+    for r in range(world):
+        rlo, rhi = (int(v) for v in got[r][0])
+        if compact:
+            rr = CompactResult.__new__(CompactResult)
+            rr.pairs, rr.mode, rr.volume = slice_pairs(pairs, rlo, rhi), mode, np.asarray(matrix).shape[0]
+        else:
+            rr = BatchResult.__new__(BatchResult)
+            rr.end_yx = None
+        rr.count = rhi - rlo
+        for k, arr in zip(fields, got[r][1:]):
+            setattr(rr, k, arr)
+        out.append((rlo, rhi, rr))
+    return out
 
 
 def score_batch_sharded(mode, pairs, matrix, del_, ext, device=-1, gather=True):

@@ -327,13 +327,13 @@ def side_configs(a, lib, local, rank, world, int_peak, dist, torch):
                 ok = ok and r["f"] == res.f[it] and r["passes"] == int(res.passes[it])
                 cpu_cells += r["passes"] * float(len(qv)) * len(tv)
         cpu = time.perf_counter() - t0
-        ach = cells * OPS_PER_CELL / best / 1e12
+        ach = cells * OPS_PER_CELL / best / 1e12 / world  # per GPU, like the peak
         out["c5_%dx%d" % (P, K)] = {
             "gcups": cells / best / 1e9, "ms": best * 1e3, "parity": bool(ok), "n_gpus": world,
             "parity_how": "%d random (pair, matrix) items against the oracle's loop: f, passes, status" % len(pick),
             "fitness_sha256_16": hashlib.sha256(fit.tobytes()).hexdigest()[:16],
             "collective": "one NCCL all-reduce of the [blocks x K] f64 block sums" if world > 1 else "none (1 GPU)",
-            "roofline": {"bound": "fp64_add", "achieved": ach, "peak": f64.get("add_tops"), "unit": "TOP/s",
+            "roofline": {"bound": "fp64_add", "per": "GPU", "achieved": ach, "peak": f64.get("add_tops"), "unit": "TOP/s",
                          "frac": ach / f64["add_tops"] if f64.get("add_tops") else None},
             "cpu_port_gcups": cpu_cells / cpu / 1e9, "dtype": "f64",
             "what": "sharded alnr_heuristic_batch calls (host buffers in, fitness out), max over ranks"}

@@ -50,8 +50,22 @@ def main():
         P = int(sys.argv[3])
         pairs = W.dna_read_batch(0, P, n=150)
         got = S.align_batch_sharded(ab.LOCAL, pairs, ab.dna_matrix(5, -4), 10, 2, device=0)
+        cgot = S.align_batch_sharded(ab.LOCAL, pairs, ab.dna_matrix(5, -4), 10, 2, device=0, compact=True)
         if rank == 0:
-            result = [(lo, hi, r.f, r.coords, r.aln_len) for lo, hi, r in got]
+            result = []
+            for (lo, hi, r), (clo, chi, c) in zip(got, cgot):
+                assert (lo, hi) == (clo, chi)
+                ex = c.expand()
+                strings = [r.alignment(i) for i in (0, r.count // 2, r.count - 1)]
+                cstrings = [ex.alignment(i) for i in (0, r.count // 2, r.count - 1)]
+                same = all((a[0] == b[0]).all() and (a[1] == b[1]).all() for a, b in zip(strings, cstrings))
+                result.append((lo, hi, r.f, r.coords, r.aln_len, bool(same and (ex.coords == r.coords).all()), strings))
+    elif mode == "gather":  # host logic only (CPU test): raw-tensor gather of ragged arrays
+        rng = np.random.default_rng(100 + rank)
+        arrs = [rng.normal(size=5 + 3 * rank), rng.integers(0, 200, (rank * 4, 4)).astype(np.uint64),
+                rng.integers(0, 255, 1000 * (world - rank)).astype(np.uint8), np.zeros(0, dtype=np.uint32)]
+        got = S._gather_arrays(arrs, dst=0)
+        result = {"sent": arrs, "got": got}
     elif mode == "windows":  # host logic only (CPU test): the ranges tile the windows
         count = int(sys.argv[3])
         result = S.window_range(count, rank, world)

@@ -70,9 +70,10 @@ def test_heuristic_single_pair_matches_oracle(examples):
 
 @pytest.mark.gpu
 def test_heuristic_grid_matches_oracle_config5_subgrid():
-    """BASELINE config 5 on a sub-grid: 10 protein pairs x 12 candidate matrices."""
-    pairs = W.protein_pairs(0, 10, 60, 90)
-    mats = W.candidate_matrices(12)
+    """BASELINE config 5 on the sub-grid SURVEY.md 8d names: 10 protein pairs of ~300 aa x 50
+    candidate matrices (500 items, each the oracle's full heuristic loop)."""
+    pairs = W.protein_pairs(0, 10, 270, 330)
+    mats = W.candidate_matrices(50)
     freqs = W.pair_frequencies(pairs, 24)
     fitness, best_k, best_f, grid, sgrid = ab.matrix_search(pairs, mats, 5, 5, -1.0, 576.0, freqs)
     P, K = pairs.count, len(mats)

@@ -119,9 +119,24 @@ def test_align_batch_sharded_two_ranks(tmp_path):
     ref = ab.align_batch(ab.LOCAL, pairs, ab.dna_matrix(5, -4), 10, 2)
     got = _launch(2, "batch", tmp_path, P)[0]
     assert len(got) == 2 and got[0][0] == 0 and got[0][1] == got[1][0] and got[1][1] == P
-    for lo, hi, f, coords, aln_len in got:
+    for lo, hi, f, coords, aln_len, compact_same, strings in got:
         assert (f == ref.f[lo:hi]).all() and (coords == ref.coords[lo:hi]).all()
         assert (aln_len == ref.aln_len[lo:hi]).all()
+        assert compact_same  # the compact gather expands to the gathered strings
+        for i, (qa, ta) in zip((0, (hi - lo) // 2, hi - lo - 1), strings):
+            qr, tr = ref.alignment(lo + i)
+            assert (qa == qr).all() and (ta == tr).all()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_gather_arrays_without_pickling_gloo(world, tmp_path):
+    """sharding._gather_arrays: ragged per-rank arrays (different lengths, an empty one, 2-D) arrive
+    on rank 0 bit for bit; the other ranks receive nothing."""
+    got = _launch(world, "gather", tmp_path)
+    assert all(g["got"] is None for g in got[1:])
+    for r in range(world):
+        for sent, recv in zip(got[r]["sent"], got[0]["got"][r]):
+            assert recv.dtype == sent.dtype and recv.shape == sent.shape and (recv == sent).all()
 
 
 @pytest.mark.parametrize("world", [2, 3])

@@ -86,19 +86,16 @@ def test_tile_pipeline_extreme_shapes(m, n, mode, d):
     assert (r.alignment.query == ref["q_aln"]).all() and (r.alignment.target == ref["t_aln"]).all()
 
 
-def test_tile_pipeline_equals_column_kernel_and_lockstep_traceback(monkeypatch):
-    """The first-generation kernels and the one-lane window walk stay selectable; all paths give the same alignment."""
-    import subprocess, sys, os, json
-    code = ("import sys, json, hashlib; sys.path.insert(0, %r); import aligner_b200 as ab; "
-            "from aligner_b200 import workloads as W; q, t = W.dna_long_pair(6000, seed=11); "
-            "r = ab.SimpleGlobalAligner.from_seqs(q, t, symbols=ab.DNA).perform_alignment(8, 8, ab.dna_matrix(5, -4), want_matrices=False); "
-            "print(json.dumps([r.corner_score, hashlib.sha256(r.alignment.query.tobytes() + r.alignment.target.tobytes()).hexdigest()]))"
-            % os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-    outs = []
-    for extra in ({}, {"ALNR_BAND_COLUMN": "1"}, {"ALNR_TRACE_LOCKSTEP": "1"}, {"ALNR_TRACE_SEQ": "1"}):
-        env = dict(os.environ, **extra)
-        outs.append(json.loads(subprocess.check_output([sys.executable, "-c", code], env=env).decode().strip().splitlines()[-1]))
-    assert outs[0] == outs[1] == outs[2] == outs[3]
+def test_cooperative_walk_equals_lockstep_walk(monkeypatch):
+    """The two long-pair tracebacks — the cooperative window walk (full direction matrix) and the
+    lockstep walk (used group by group by the checkpointed traceback) — give the same alignment."""
+    q, t = W.dna_long_pair(6000, seed=11)
+    al = ab.SimpleGlobalAligner.from_seqs(q, t, symbols=ab.DNA)
+    a = al.perform_alignment(8, 8, ab.dna_matrix(5, -4), want_matrices=False)
+    monkeypatch.setenv("ALNR_SCRATCH_BUDGET", "100000000")  # one group holding every band
+    b = al.perform_alignment(8, 8, ab.dna_matrix(5, -4), want_matrices=False)
+    assert a.corner_score == b.corner_score
+    assert (a.alignment.query == b.alignment.query).all() and (a.alignment.target == b.alignment.target).all()
 
 
 @pytest.mark.parametrize("seed", range(24))
