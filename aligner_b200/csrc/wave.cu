@@ -5,6 +5,7 @@
 #include <cstdlib>
 #include <vector>
 
+#include "kernels_diff.cuh"
 #include "kernels_tile.cuh"
 #include "kernels_trace.cuh"
 #include "strip_launch.h"
@@ -174,6 +175,92 @@ static int tile_run_pair(alnr_batch_impl &B, const Chunk &c, const DLayout &dl, 
   return ALNR_OK;
 }
 
+// Difference-recurrence kernel (kernels_diff.cuh): global mode, DNA-sized alphabet, small integer
+// scores — the BASELINE config-4 shape.  Everything else stays on the tile pipeline.
+// ALNR_NO_DIFF=1 switches it off (A/B runs, tests).
+static bool diff_eligible(const alnr_batch_impl &B, const Chunk &c) {
+  if (std::getenv("ALNR_NO_DIFF")) return false;
+  if (B.mode != ALNR_GLOBAL || B.V > 4 || c.ckpt_group) return false;
+  if (c.m_max < 128 || c.n_max < 128) return false;
+  const int del = (int)B.del, ext = (int)B.ext;
+  if (!(ext >= 1 && del >= ext && del <= 24)) return false;
+  for (double v : B.matrix)
+    if (v + 2 * del + ext > 127.0 || v < -1024.0) return false;  // S = s + B + p is a byte
+  return true;
+}
+
+static int diff_run_pair(alnr_batch_impl &B, const Chunk &c, const DLayout &dl, const FillOut &fo) {
+  DiffArgs a;
+  a.q = B.d_q.p + c.q0; a.t = B.d_t.p + c.t0;
+  a.n = c.n_max; a.m = c.m_max;
+  a.del = (int)B.del; a.ext = (int)B.ext;
+  const int bias = 2 * a.del + a.ext;
+  for (int ts = 0; ts < 4; ++ts) {  // one word per TARGET symbol, one byte per query symbol
+    uint32_t w = 0;
+    for (int qs = 0; qs < 4; ++qs) {
+      int v = (qs < B.V && ts < B.V) ? (int)B.matrix[(size_t)ts * B.V + qs] + bias : 0;
+      v = std::min(std::max(v, 0), 127);  // a negative S never wins the max against DH, DV >= 0
+      w |= (uint32_t)v << (8 * qs);
+    }
+    a.wtab[ts] = w;
+  }
+  a.nbands = (a.m + kDiffBandRows - 1) / kDiffBandRows;
+  a.npad = (a.n + 63) / 64 * 64;
+  // scratch: [pad 2][corner acc][pad][rows: nbands * npad 16-bit values][256 words of slack for the
+  // kernel's reads past the end of a row]
+  const size_t words = 4 + ((size_t)a.nbands * a.npad + 1) / 2 + 256;
+  if (B.d_band.n < words) {
+    if (B.d_band.p) ALNR_CUDA(cudaStreamSynchronize(B.stream));  // an earlier pair may still use the old rows
+    ALNR_CUDA(B.d_band.alloc(words));
+  }
+  a.corner_acc = B.d_band.p + 2;
+  a.rows = reinterpret_cast<uint16_t *>(B.d_band.p + 4);
+  a.stamps = nullptr;
+#ifdef ALNR_DIFF_DEBUG
+  static unsigned long long *d_stamps = nullptr;
+  if (!d_stamps) cudaMalloc(&d_stamps, (size_t)65536 * 64);
+  a.stamps = d_stamps;
+#endif
+  a.D = B.Dp();
+  a.dcols = dl.ncols;
+  static unsigned resident = 0;
+  if (!resident) {
+    int occ = 0, sms = 0, dev = 0;
+    ALNR_CUDA(cudaGetDevice(&dev));
+    ALNR_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    ALNR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fill_diff_kernel, 32, 0));
+    resident = (unsigned)std::max(1, occ) * (unsigned)std::max(1, sms);
+  }
+  ALNR_CUDA(cudaMemsetAsync(B.d_band.p, 0, 16, B.stream));
+  if (a.nbands > 1)  // every boundary value below row 0 starts as "not produced yet"
+    ALNR_CUDA(cudaMemsetAsync(a.rows + a.npad, 0xff, (size_t)(a.nbands - 1) * a.npad * sizeof(uint16_t), B.stream));
+  const unsigned grid = std::min<unsigned>(a.nbands, resident);  // a waiter depends on lower bands only
+  fill_diff_kernel<<<grid, 32, 0, B.stream>>>(a);
+  ALNR_LAUNCHED();
+  diff_finish_kernel<<<1, 1, 0, B.stream>>>(a, fo, c.wave_pair);
+  ALNR_LAUNCHED();
+#ifdef ALNR_DIFF_DEBUG
+  {  // per-band time stamps, us since the first band's entry: entry, woken, block 1, t0 = 64, 72, 8192, end
+    std::vector<unsigned long long> ts((size_t)a.nbands * 8);
+    cudaStreamSynchronize(B.stream);
+    cudaMemcpy(ts.data(), a.stamps, ts.size() * 8, cudaMemcpyDeviceToHost);
+    const unsigned long long t0 = ts[0];
+    for (uint32_t b = 0; b < a.nbands; b += (a.nbands > 40 ? a.nbands / 24 : 1)) {
+      fprintf(stderr, "band %4u:", b);
+      for (int k = 0; k < 7; ++k) fprintf(stderr, " %9.1f", (double)(ts[(size_t)b * 8 + k] - t0) / 1000.0);
+      if (b) fprintf(stderr, " | behind the band above at block 1 / 72 / 8192: %.2f %.2f %.2f us; own block 1 -> 72: %.2f us; above's 72 -> own block 1: %.2f us",
+                     (double)(ts[(size_t)b * 8 + 2] - ts[(size_t)(b - 1) * 8 + 2]) / 1000.0,
+                     (double)(ts[(size_t)b * 8 + 4] - ts[(size_t)(b - 1) * 8 + 4]) / 1000.0,
+                     (double)(ts[(size_t)b * 8 + 5] - ts[(size_t)(b - 1) * 8 + 5]) / 1000.0,
+                     (double)(ts[(size_t)b * 8 + 4] - ts[(size_t)b * 8 + 2]) / 1000.0,
+                     (double)((long long)ts[(size_t)b * 8 + 2] - (long long)ts[(size_t)(b - 1) * 8 + 4]) / 1000.0);
+      fprintf(stderr, "\n");
+    }
+  }
+#endif
+  return ALNR_OK;
+}
+
 // rows per lane of the tile pipeline (its D layout is DLayout::make_blocked(4, ...))
 uint32_t wave_band_rows(uint32_t m) {
   (void)m;
@@ -181,6 +268,7 @@ uint32_t wave_band_rows(uint32_t m) {
 }
 
 int wave_run_pair(alnr_batch_impl &B, const Chunk &c, const DLayout &dl, const FillOut &fo) {
+  if (diff_eligible(B, c)) return diff_run_pair(B, c, dl, fo);
   return tile_run_pair(B, c, dl, fo);
 }
 

@@ -225,3 +225,30 @@ def test_checkpointed_pair_inside_a_batch(monkeypatch):
             qa, ta = got.alignment(i)
             qb, tb = ref.alignment(i)
             assert (qa == qb).all() and (ta == tb).all()
+
+
+# ---- difference-recurrence kernel (kernels_diff.cuh): global mode, DNA, small integer scores ------
+
+@pytest.mark.parametrize("m,n", [(128, 128), (129, 4001), (4000, 131), (2500, 2500), (3333, 5100), (6007, 2049)])
+@pytest.mark.parametrize("d,e,mat", [(8, 8, (5, -4)), (10, 2, (5, -4)), (3, 1, (1, -1)), (24, 24, (10, -9))])
+def test_diff_kernel_vs_lean_oracle_and_tile_kernel(monkeypatch, m, n, d, e, mat):
+    """Every band / lane / tile boundary case of the skewed sweep (rows and columns not multiples of
+    4, 8, 64 or 128, one band, many bands), penalties with del > ext (cell (1,1) pays del) and the
+    +1/-1 scheme full of ties — against the lean oracle and against the tile pipeline."""
+    rng = np.random.default_rng(m * 31 + n + d)
+    q = rng.integers(0, 4, n).astype(np.uint8)
+    t = rng.integers(0, 4, m).astype(np.uint8)
+    k = min(m, n)
+    keep = rng.random(k) < 0.85
+    t[:k] = np.where(keep, q[:k], t[:k])  # related prefix, unrelated tail: diagonal runs and long gaps
+    M = ab.dna_matrix(*mat)
+    ref = O.align_pair("global", q, t, float(d), float(e), M, lean=True)
+    al = ab.SimpleGlobalAligner.from_seqs(q, t, symbols=ab.DNA)
+    monkeypatch.delenv("ALNR_NO_DIFF", raising=False)
+    r = al.perform_alignment(d, e, M, want_matrices=False)
+    assert r.corner_score == ref["corner"] and r.alignment.f == 0.0 and r.alignment.coords == ref["coords"]
+    assert (r.alignment.query == ref["q_aln"]).all() and (r.alignment.target == ref["t_aln"]).all()
+    monkeypatch.setenv("ALNR_NO_DIFF", "1")
+    r2 = al.perform_alignment(d, e, M, want_matrices=False)
+    assert r2.corner_score == r.corner_score
+    assert (r2.alignment.query == r.alignment.query).all() and (r2.alignment.target == r.alignment.target).all()
