@@ -18,8 +18,4 @@ print('strong',d['strong_scaling'])
 for k,v in d['configs'].items(): print(k, round(v['gcups'],2), v['parity'], v.get('fitness_sha256_16'), v.get('roofline',{}).get('frac'))
 print('cpu', d.get('cpu_baseline'))
 PY
-python bench.py --impl reference --steps 3 --warmup 1 > $O/bench_ref.json 2> $O/bench_ref.err; cut -c1-300 $O/bench_ref.json
-python scripts/prof_c5.py 2000 100 > $O/prof_c5_plain.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:fill_warp_kernel -s 0 -c 1 -f -o $O/c5_r02 python scripts/prof_c5.py 2000 100 > $O/ncu_c5.log 2>&1
-echo "ncu rc=$?"
-python scripts/prof_c5.py 2000 100 > /dev/null 2>&1 && ncu --metrics gpu__time_duration.sum --clock-control none -c 300 --csv --log-file $O/c5_launches_r02.csv python scripts/prof_c5.py 2000 100 > /dev/null 2>&1
+timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > $O/bench_ref.json 2> $O/bench_ref.err; cut -c1-300 $O/bench_ref.json
