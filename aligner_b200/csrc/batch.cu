@@ -217,7 +217,9 @@ int alnr_batch_impl::plan_chunks(const uint64_t *q_off, const uint64_t *t_off) {
     }
     uint32_t m1, n1;
     dims(s, m1, n1);
-    const bool wave = wave_eligible(*this, m1, n1);
+    bool wave = wave_eligible(*this, m1, n1);
+    // the checkpointed re-fill has no stateful instantiation: such a pair stays on the warp kernel
+    if (wave && mode == ALNR_LOCAL && del != ext && !score_only && wave_ckpt_group(m1, n1, budget)) wave = false;
     if (wave) { c = 1; m = m1; n = n1; }
     Chunk ck{(uint32_t)s, (uint32_t)c, m, n, 0, 0, 0, 0};
     if (wave) {

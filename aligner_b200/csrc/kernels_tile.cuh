@@ -54,6 +54,14 @@ struct TileLane {
   bool has_corner;
 };
 
+// STATEFUL instantiation only (kept out of TileLane: the other instantiations keep their tuned schedule)
+struct TileStateful {
+  uint32_t dmw, dmw_next;     // first lane of the first band: delmap words of this and the next 32 columns
+  const uint32_t *delmap;
+  uint32_t *zeromap;
+  bool last_band;
+};
+
 // 4 symbols starting at any byte address (two aligned words + funnel shift; the buffers carry 16
 // bytes of padding, batch.cu)
 __device__ __forceinline__ uint32_t tile_load_q4(const uint8_t *p) {
@@ -153,12 +161,109 @@ __device__ __forceinline__ void tile_step(TileLane &L, const int4 *sm_sc, const 
   L.rowp += 4;
 }
 
+// tile_step for local mode with del != ext (simple/mod.rs:201-205): a cell pays del iff the cell above it
+// holds 0 (it was a Beginning, and it is the cell before this one in the reference's column-major
+// order); row 1 pays del where the speculated map says so (kernels_band.cuh); the last band records
+// the zeros of row m.  Otherwise the code of tile_step<true, EDGE>:
+// one step: lane l computes tile ti = s - l (columns 4 ti + 1 .. 4 ti + 4) of its 4 rows.
+// EDGE = 1 (ramp-up: the first 32 steps of a band, which every band below waits for) adds the
+// ti < ntiles test and the one cell that pays `del` in global mode; EDGE = 2 (last columns and
+// drain) also masks the query symbols past column n (those cells are computed and never read)
+// and captures H[m][n].
+template <int EDGE>
+__device__ __forceinline__ void tile_step_stateful(TileLane &L, TileStateful &Z, const int4 *sm_sc, const int *sm_top, uint32_t s, uint32_t lane,
+                                          uint32_t yl0, uint32_t n, uint32_t m, uint32_t ntiles, int del, int ext,
+                                          bool store_d, bool row_out) {
+  int up[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) up[j] = __shfl_up_sync(0xffffffffu, L.bot[j], 1);
+  const int4 tp = *reinterpret_cast<const int4 *>(sm_top + 4 * (s & (kTileChunk - 1)));
+  if (lane == 0) { up[0] = tp.x; up[1] = tp.y; up[2] = tp.z; up[3] = tp.w; }
+  const uint32_t ti = s - lane;  // wraps for s < lane
+  if (EDGE && ti >= ntiles) return;
+  const uint32_t c0 = ti * 4;
+  const uint32_t qw = L.qw;
+  L.qp += 4;
+  L.qw = tile_load_q4(L.qp);
+  const int corner_in = L.diag0;
+  L.diag0 = up[3];
+  uint32_t word = 0;
+  bool hit = false;
+  int v[4][4];
+  constexpr bool LOCAL = true;
+  uint32_t dm4 = 0;  // row 1: which of the tile's 4 columns pay del
+  if (yl0 == 0) {
+    dm4 = Z.dmw >> (c0 & 31u);
+    if ((c0 & 31u) == 28u) { Z.dmw = Z.dmw_next; Z.dmw_next = __ldg(Z.delmap + (c0 >> 5) + 2); }
+  }
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    uint32_t sym = (qw >> (8 * j)) & 0xffu;
+    if (EDGE == 2 && c0 + j >= n) sym = 0;
+    const int4 s4 = sm_sc[sym * 32 + lane];
+    const int sc[4] = {s4.x, s4.y, s4.z, s4.w};
+    int diag = j == 0 ? corner_in : up[j - 1];
+    int hup = up[j];
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      int pen = (hup == 0) ? del : ext;
+      if (r == 0 && yl0 == 0) pen = ((dm4 >> j) & 1u) ? del : ext;  // H[0][x] is 0 by definition, not a Beginning
+      const int top = hup - pen, left = L.h[r] - pen, dg = diag + sc[r];
+      const int mx = max(max(top, left), dg);
+      uint32_t code = (mx == left) ? DIR_LEFT : DIR_DIAGONAL;  // enums.rs:23/:41
+      code = (mx == top) ? DIR_TOP : code;                     // enums.rs:21/:39
+      if (LOCAL) code = (mx == 0) ? DIR_BEGINNING : code;      // enums.rs:37
+      word |= code << (8 * j + 2 * r);
+      diag = L.h[r];
+      L.h[r] = mx;
+      hup = mx;
+      if (LOCAL) { hit |= mx >= L.best_v; v[r][j] = mx; }
+    }
+    L.bot[j] = hup;
+    if (EDGE == 2 && c0 + j + 1 == n) {
+#pragma unroll
+      for (int r = 0; r < 4; ++r)
+        if (yl0 + r + 1 == m) { L.corner = L.h[r]; L.has_corner = true; }
+    }
+  }
+  if (LOCAL && hit) {  // rare: first maximum in row-major order (simple/mod.rs:212)
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      const uint32_t y = yl0 + r + 1;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const uint32_t x = c0 + j + 1;
+        const int w = v[r][j];
+        if (y <= m && x <= n && (w > L.best_v || (w == L.best_v && y < L.best_y))) {
+          L.best_v = w; L.best_y = y; L.best_x = x;
+        }
+      }
+    }
+  }
+  if (Z.last_band) {  // zeros of row m: the next pass's row 1 pays del one column later
+    const uint32_t zr = m - 1u - yl0;  // the lane's row that is row m (>= 4: another lane's)
+    uint32_t zm = 0;
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if ((uint32_t)r == zr && v[r][j] == 0 && c0 + j < n) zm |= 1u << j;
+    if (zm) atomicOr(Z.zeromap + (c0 >> 5), zm << (c0 & 31u));
+  }
+  if (store_d) __stcs(L.dptr, word);
+  ++L.dptr;
+  if (row_out) __stcg(reinterpret_cast<int4 *>(L.rowp), make_int4(L.bot[0], L.bot[1], L.bot[2], L.bot[3]));
+  L.rowp += 4;
+}
+
 // BandArgs as in kernels_band.cuh, except: rows = [nbands][npad] indexed by the 0-based column
 // (npad = n rounded up to 4, preset to kTileSentinel), prog unused.
 // REFILL (checkpointed traceback, wave.cu): a compile-time variant, so that the ordinary sweep keeps
 // the instruction schedule it was tuned with (as run-time conditions the same lines cost it 12 %).
-template <bool LOCAL, bool REFILL = false>
+template <bool LOCAL, bool REFILL = false, bool STATEFUL = false>
 __global__ void __launch_bounds__(32) fill_tile_kernel(BandArgs a) {
+  static_assert(!STATEFUL || (LOCAL && !REFILL), "the stateful penalty only exists in local mode");
+  if (STATEFUL && a.prog[0]) return;  // an earlier pass reproduced its penalty map: the results stand
   extern __shared__ int4 tsm[];  // [V][32] score quadruples, then 32 ints of boundary values
   const uint32_t lane = threadIdx.x;
   const uint32_t V = (uint32_t)a.V;
@@ -202,6 +307,12 @@ __global__ void __launch_bounds__(32) fill_tile_kernel(BandArgs a) {
     const bool store_d = yl0 < m && a.D != nullptr;  // score-only calls pass no D scratch
     const bool last_band = band + 1 == a.nbands;
     const bool row_out = lane == 31 && !last_band && !refill;
+    TileStateful Z;
+    if (STATEFUL) {
+      Z.delmap = stateful_delmap(a); Z.zeromap = stateful_zeromap(a); Z.last_band = last_band;
+      Z.dmw = Z.dmw_next = 0;
+      if (yl0 == 0) { Z.dmw = __ldg(Z.delmap); Z.dmw_next = __ldg(Z.delmap + 1); }
+    }
     L.dptr = a.D + (size_t)(yl0 / 4 - (REFILL ? a.strip0 : 0u)) * a.dcols;  // this lane's 4-row strip
     L.rowp = a.rows + (size_t)band * npad;
     const uint32_t steps = ntiles + 31;
@@ -254,19 +365,28 @@ __global__ void __launch_bounds__(32) fill_tile_kernel(BandArgs a) {
 #pragma unroll
         for (uint32_t j = 0; j < kTileChunk; ++j) {
           if (j == kTilePrefetchAt && pf) pre = tile_ld_row(pf);
-          tile_step<LOCAL, 0>(L, sm_sc, sm_top, s0 + j, lane, yl0, n, m, ntiles, del, ext, store_d, row_out);
+          if constexpr (STATEFUL)
+            tile_step_stateful<0>(L, Z, sm_sc, sm_top, s0 + j, lane, yl0, n, m, ntiles, del, ext, store_d, row_out);
+          else
+            tile_step<LOCAL, 0>(L, sm_sc, sm_top, s0 + j, lane, yl0, n, m, ntiles, del, ext, store_d, row_out);
         }
       } else if (inner) {
 #pragma unroll
         for (uint32_t j = 0; j < kTileChunk; ++j) {
           if (j == kTilePrefetchAt && pf) pre = tile_ld_row(pf);
-          tile_step<LOCAL, 1>(L, sm_sc, sm_top, s0 + j, lane, yl0, n, m, ntiles, del, ext, store_d, row_out);
+          if constexpr (STATEFUL)
+            tile_step_stateful<1>(L, Z, sm_sc, sm_top, s0 + j, lane, yl0, n, m, ntiles, del, ext, store_d, row_out);
+          else
+            tile_step<LOCAL, 1>(L, sm_sc, sm_top, s0 + j, lane, yl0, n, m, ntiles, del, ext, store_d, row_out);
         }
       } else {
         const uint32_t jend = min(kTileChunk, steps - s0);
         if (pf) pre = tile_ld_row(pf);
         for (uint32_t j = 0; j < jend; ++j)
-          tile_step<LOCAL, 2>(L, sm_sc, sm_top, s0 + j, lane, yl0, n, m, ntiles, del, ext, store_d, row_out);
+          if constexpr (STATEFUL)
+            tile_step_stateful<2>(L, Z, sm_sc, sm_top, s0 + j, lane, yl0, n, m, ntiles, del, ext, store_d, row_out);
+          else
+            tile_step<LOCAL, 2>(L, sm_sc, sm_top, s0 + j, lane, yl0, n, m, ntiles, del, ext, store_d, row_out);
       }
     }
     TILE_STAMP(5);

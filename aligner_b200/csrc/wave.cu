@@ -26,7 +26,10 @@ bool wave_eligible(const alnr_batch_impl &B, uint32_t m, uint32_t n) {
   if (B.numeric != ALNR_NUM_I32 || B.want_matrices) return false;
   if ((uint64_t)m * n < (B.count <= 4 ? kWaveMinCellsSingle : kWaveMinCellsBatch)) return false;
   if (m >= 0xFFFFFu || n >= 0xFFFFFu) return false;       // arg-max key packs 20-bit coordinates
-  if (B.mode == ALNR_LOCAL && B.del != B.ext) return false;  // stateful penalty: columns serialise
+  // stateful penalty (local, del != ext): the tile pipeline speculates row 1's penalties and repeats
+  // the pass until they reproduce themselves (tile_run_pair); worth it from ~2000 x 2000 cells on
+  if (B.mode == ALNR_LOCAL && B.del != B.ext && ((uint64_t)m * n < (1ull << 22) || std::getenv("ALNR_NO_WAVE_STATEFUL")))
+    return false;
   double mag = 0;
   for (double v : B.matrix) mag = std::max(mag, v);
   if (B.mode == ALNR_LOCAL && mag * std::min(m, n) >= 16777216.0) return false;  // 24-bit value field
@@ -110,6 +113,42 @@ static int tile_args(alnr_batch_impl &B, const Chunk &c, BandArgs &a, size_t &sm
   return ALNR_OK;
 }
 
+// Stateful local pairs: what a pass of the tile pipeline needs reset, unless an earlier pass converged.
+static __global__ void stateful_reset_kernel(BandArgs a, size_t row_words, uint32_t map_words) {
+  if (a.prog[0]) return;
+  const size_t stride = (size_t)gridDim.x * blockDim.x, tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  uint32_t *zeromap = stateful_zeromap(a);
+  for (size_t i = tid; i < row_words; i += stride) a.rows[i] = kTileSentinel;
+  for (size_t i = tid; i < map_words; i += stride) zeromap[i] = 0;
+  if (tid == 0) { *a.best = 0; *a.corner_out = 0; }
+}
+
+// After a pass: cell (1, x) must pay del iff H[m][x-1] == 0 (simple/mod.rs:201-205), cell (1,1) pays
+// del.  In map bits (bit c = column c + 1): wanted = (zeromap << 1) | 1.  Equal to the map the pass
+// ran with: converged.  Otherwise the pass is repeated with the wanted map.  One block.
+static __global__ void stateful_check_kernel(BandArgs a, uint32_t map_words) {
+  if (a.prog[0]) return;
+  uint32_t *delmap = stateful_delmap(a);
+  const uint32_t *zeromap = stateful_zeromap(a);
+  __shared__ int differs;
+  if (threadIdx.x == 0) differs = 0;
+  __syncthreads();
+  const uint32_t nwords = (a.n + 31) / 32;
+  for (uint32_t w = threadIdx.x; w < map_words; w += blockDim.x) {
+    uint32_t want = 0;
+    if (w < nwords) {
+      want = (zeromap[w] << 1) | (w ? zeromap[w - 1] >> 31 : 1u);
+      if (w + 1 == nwords && (a.n & 31u)) want &= (1u << (a.n & 31u)) - 1u;  // columns 1 .. n only
+    }
+    if (want != delmap[w]) { differs = 1; delmap[w] = want; }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    a.prog[1] += 1;
+    if (!differs) a.prog[0] = 1;
+  }
+}
+
 // Tile pipeline (kernels_tile.cuh): 4 x 4 cells per lane and step, sentinel hand-off of the band rows.
 static int tile_run_pair(alnr_batch_impl &B, const Chunk &c, const DLayout &dl, const FillOut &fo) {
   BandArgs a;
@@ -126,7 +165,10 @@ static int tile_run_pair(alnr_batch_impl &B, const Chunk &c, const DLayout &dl, 
 #else
   const size_t dbg_words = 0;
 #endif
-  const size_t words = 4 + row_words + dbg_words;
+  // stateful local pair: [state 4 words][delmap][zeromap], each map (n + 31) / 32 words + 4 of slack
+  const bool stateful = local && B.del != B.ext;
+  const uint32_t map_words = stateful ? stateful_map_words(a.n) : 0;
+  const size_t words = 4 + row_words + dbg_words + (stateful ? 4 + 2 * (size_t)map_words : 0);
   if (B.d_band.n < words) {
     // a longer pair than the previous one of this batch: its fill may still be running on the old rows
     if (B.d_band.p) ALNR_CUDA(cudaStreamSynchronize(B.stream));
@@ -153,10 +195,40 @@ static int tile_run_pair(alnr_batch_impl &B, const Chunk &c, const DLayout &dl, 
   if (a.nbands > 1)  // every word of the boundary rows starts as "not produced yet" (0x80808080)
     ALNR_CUDA(cudaMemsetAsync(a.rows, 0x80, (size_t)(a.nbands - 1) * npad * sizeof(int), B.stream));
   const unsigned grid = std::min<unsigned>(a.nbands, resident);  // every block must be resident
-  if (local) fill_tile_kernel<true><<<grid, 32, smem, B.stream>>>(a);
+  if (stateful) {
+    // Speculate-and-repeat (kernels_band.cuh): kStatefulPasses passes are enqueued; a pass whose
+    // penalty map reproduced itself sets state[0] and the later ones return at once, so nothing
+    // synchronises with the host.  A map still moving after the last pass ends as
+    // ALNR_CALCULATION_ERROR for the pair (band_finish_kernel) — every pass pins at least the first
+    // column that differed, and zeros in row m are rare away from the matrix's left edge.
+    constexpr int kStatefulPasses = 8;
+    uint32_t *sbase = reinterpret_cast<uint32_t *>(base + 4 + row_words + dbg_words);
+    uint32_t *delmap = sbase + 4;
+    a.prog = sbase;  // the state block (kernels_band.cuh)
+    ALNR_CUDA(cudaMemsetAsync(sbase, 0, (4 + 2 * (size_t)map_words) * sizeof(uint32_t), B.stream));
+    const uint32_t one = 1;  // cell (1,1) pays del (simple/mod.rs:185)
+    ALNR_CUDA(cudaMemcpyAsync(delmap, &one, sizeof(one), cudaMemcpyHostToDevice, B.stream));
+    const size_t reset_words = (size_t)(a.nbands - 1) * npad;
+    for (int pass = 0; pass < kStatefulPasses; ++pass) {
+      if (pass) {  // the first pass starts from the memsets above
+        stateful_reset_kernel<<<148 * 4, 256, 0, B.stream>>>(a, reset_words, map_words);
+        ALNR_LAUNCHED();
+      }
+      fill_tile_kernel<true, false, true><<<grid, 32, smem, B.stream>>>(a);
+      ALNR_LAUNCHED();
+      stateful_check_kernel<<<1, 256, 0, B.stream>>>(a, map_words);
+      ALNR_LAUNCHED();
+    }
+    if (std::getenv("ALNR_WAVE_STATS")) {  // tests: passes run, through alnr_batch_rerun_count (synchronises)
+      uint32_t st[2] = {0, 0};
+      ALNR_CUDA(cudaMemcpyAsync(st, sbase, sizeof(st), cudaMemcpyDeviceToHost, B.stream));
+      ALNR_CUDA(cudaStreamSynchronize(B.stream));
+      B.rerun_total += st[1];
+    }
+  } else if (local) fill_tile_kernel<true><<<grid, 32, smem, B.stream>>>(a);
   else fill_tile_kernel<false><<<grid, 32, smem, B.stream>>>(a);
   ALNR_LAUNCHED();
-  band_finish_kernel<<<1, 1, 0, B.stream>>>(a, local ? 1 : 0, fo, c.wave_pair);
+  band_finish_kernel<<<1, 1, 0, B.stream>>>(a, stateful ? 2 : (local ? 1 : 0), fo, c.wave_pair);
   ALNR_LAUNCHED();
 #ifdef ALNR_TILE_DEBUG
   {  // per-band time stamps (ns since the first band's entry): entry, woken, first chunk, step 32, step 64, end

@@ -252,3 +252,67 @@ def test_diff_kernel_vs_lean_oracle_and_tile_kernel(monkeypatch, m, n, d, e, mat
     r2 = al.perform_alignment(d, e, M, want_matrices=False)
     assert r2.corner_score == r.corner_score
     assert (r2.alignment.query == r.alignment.query).all() and (r2.alignment.target == r.alignment.target).all()
+
+
+# ---- stateful local pairs on the tile pipeline (del != ext; simple/mod.rs:201-205) --------------------
+
+def _stateful_case(kind, n, seed):
+    rng = np.random.default_rng(seed)
+    if kind == "similar":
+        return _long_pair(n, seed)
+    if kind == "unrelated":
+        return rng.integers(0, 4, n).astype(np.uint8), rng.integers(0, 4, n - 37).astype(np.uint8)
+    # "island": unrelated flanks around a shared core — the best cell lies far from every border
+    core = rng.integers(0, 4, n // 3).astype(np.uint8)
+    q = np.concatenate([rng.integers(0, 4, n // 3).astype(np.uint8), core, rng.integers(0, 4, n // 4).astype(np.uint8)])
+    t = np.concatenate([rng.integers(0, 4, n // 5).astype(np.uint8), core, rng.integers(0, 4, n // 3).astype(np.uint8)])
+    return q, t
+
+
+@pytest.mark.parametrize("kind,n,match,mis,d,e", [
+    ("similar", 4200, 5, -4, 10, 2), ("similar", 9000, 5, -4, 11, 2), ("island", 6000, 5, -4, 10, 2),
+    ("unrelated", 3000, 5, -4, 10, 2),
+    # small scores: row m holds many zeros, the penalty map of row 1 needs several passes to settle
+    ("unrelated", 3000, 2, -2, 4, 2), ("island", 5000, 1, -1, 3, 1), ("unrelated", 2600, 1, -1, 2, 1)])
+def test_stateful_local_long_pair_vs_lean_oracle(kind, n, match, mis, d, e, monkeypatch):
+    q, t = _stateful_case(kind, n, seed=11 + n + d)
+    M = ab.dna_matrix(match, mis)
+    ref = O.align_pair("local", q, t, float(d), float(e), M, lean=True)
+    monkeypatch.setenv("ALNR_WAVE_STATS", "1")
+    pairs = ab.PackedPairs.from_lists([q], [t])
+    db = ab.DeviceBatch(N.LOCAL, pairs, M, d, e)
+    db.run()
+    passes = db.rerun_count
+    res = db.download()
+    db.close()
+    assert 1 <= passes <= 8, passes            # it ran on the tile pipeline
+    assert res.status[0] == ref["status"]
+    if ref["status"] == 0:
+        assert res.f[0] == ref["f"] and res.corner[0] == ref["corner"]
+        qa, ta = res.alignment(0)
+        assert (qa == ref["q_aln"]).all() and (ta == ref["t_aln"]).all()
+        assert tuple(int(v) for v in res.coords[0]) == ref["coords"][0] + ref["coords"][1]
+    # the warp kernel (the path such pairs took before) gives the same bytes
+    monkeypatch.setenv("ALNR_NO_WAVE_STATEFUL", "1")
+    old = ab.align_batch(N.LOCAL, pairs, M, d, e)
+    assert old.status[0] == res.status[0] and old.f[0] == res.f[0] and old.corner[0] == res.corner[0]
+    qo, to = old.alignment(0)
+    qn, tn = res.alignment(0)
+    assert (qo == qn).all() and (to == tn).all() and (old.coords == res.coords).all()
+
+
+def test_stateful_local_score_only_and_in_batch():
+    rng = np.random.default_rng(8)
+    big_q, big_t = _stateful_case("island", 7000, 5)
+    qs = [rng.integers(0, 4, 60).astype(np.uint8), big_q, rng.integers(0, 4, 45).astype(np.uint8)]
+    ts = [rng.integers(0, 4, 70).astype(np.uint8), big_t, rng.integers(0, 4, 90).astype(np.uint8)]
+    pairs = ab.PackedPairs.from_lists(qs, ts)
+    M = ab.dna_matrix(3, -2)
+    res = ab.align_batch(N.LOCAL, pairs, M, 6, 1)
+    sc = ab.score_batch(N.LOCAL, pairs, M, 6, 1)
+    for i in range(3):
+        ref = O.align_pair("local", qs[i], ts[i], 6.0, 1.0, M, lean=True)
+        assert res.status[i] == ref["status"] == sc.status[i]
+        assert res.f[i] == ref["f"] == sc.f[i] and res.corner[i] == ref["corner"] == sc.corner[i]
+        qa, ta = res.alignment(i)
+        assert (qa == ref["q_aln"]).all() and (ta == ref["t_aln"]).all()
