@@ -25,6 +25,8 @@
 // Static penalty only, exactly like kernels_band.cuh (global mode: cell (1,1) pays del, every
 // other cell ext, simple/mod.rs:72,88-92; local mode with del == ext).
 #pragma once
+#include <climits>
+
 #include "kernels_band.cuh"
 
 namespace alnr {
@@ -50,6 +52,8 @@ struct TileLane {
   int *rowp;        // &my_row[c0] of the next tile
   int best_v;
   uint32_t best_y, best_x;
+  int best_key;     // LOCAL: the band's best cell of this lane as value * 16 + (3 - r) * 4 + (3 - j) ...
+  uint32_t best_ti; // ... and its tile
   int corner;
   bool has_corner;
 };
@@ -110,8 +114,11 @@ __device__ __forceinline__ void tile_step(TileLane &L, const int4 *sm_sc, const 
   const int corner_in = L.diag0;
   L.diag0 = up[3];
   uint32_t word = 0;
-  bool hit = false;
-  int v[4][4];
+  // LOCAL: the tile's best cell as one key, value * 16 + (3 - r) * 4 + (3 - j): the first maximum in
+  // row-major order (simple/mod.rs:212) is the largest key.  (Comparing every cell with the lane's
+  // best and walking the 16 cells on a hit — the first form — ran the walk at nearly every step of
+  // the lower-left half of a matrix of similar sequences: scores rise towards the diagonal.)
+  int tkey = INT_MIN;
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
     uint32_t sym = (qw >> (8 * j)) & 0xffu;
@@ -132,7 +139,11 @@ __device__ __forceinline__ void tile_step(TileLane &L, const int4 *sm_sc, const 
       diag = L.h[r];
       L.h[r] = mx;
       hup = mx;
-      if (LOCAL) { hit |= mx >= L.best_v; v[r][j] = mx; }
+      if (LOCAL) {
+        int k = mx * 16 + ((3 - r) * 4 + (3 - j));
+        if (EDGE == 2 && c0 + j >= n) k = INT_MIN;  // columns past n are computed and never read
+        tkey = max(tkey, k);
+      }
     }
     L.bot[j] = hup;
     if (EDGE == 2 && c0 + j + 1 == n) {
@@ -141,20 +152,8 @@ __device__ __forceinline__ void tile_step(TileLane &L, const int4 *sm_sc, const 
         if (yl0 + r + 1 == m) { L.corner = L.h[r]; L.has_corner = true; }
     }
   }
-  if (LOCAL && hit) {  // rare: first maximum in row-major order (simple/mod.rs:212)
-#pragma unroll
-    for (int r = 0; r < 4; ++r) {
-      const uint32_t y = yl0 + r + 1;
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const uint32_t x = c0 + j + 1;
-        const int w = v[r][j];
-        if (y <= m && x <= n && (w > L.best_v || (w == L.best_v && y < L.best_y))) {
-          L.best_v = w; L.best_y = y; L.best_x = x;
-        }
-      }
-    }
-  }
+  // a later tile of the same rows only wins with a larger value or, at equal value, a smaller row
+  if (LOCAL && (tkey >> 2) > (L.best_key >> 2)) { L.best_key = tkey; L.best_ti = ti; }
   if (store_d) __stcs(L.dptr, word);
   ++L.dptr;
   if (row_out) __stcg(reinterpret_cast<int4 *>(L.rowp), make_int4(L.bot[0], L.bot[1], L.bot[2], L.bot[3]));
@@ -188,7 +187,7 @@ __device__ __forceinline__ void tile_step_stateful(TileLane &L, TileStateful &Z,
   const int corner_in = L.diag0;
   L.diag0 = up[3];
   uint32_t word = 0;
-  bool hit = false;
+  int tkey = INT_MIN;  // as in tile_step
   int v[4][4];
   constexpr bool LOCAL = true;
   uint32_t dm4 = 0;  // row 1: which of the tile's 4 columns pay del
@@ -217,7 +216,12 @@ __device__ __forceinline__ void tile_step_stateful(TileLane &L, TileStateful &Z,
       diag = L.h[r];
       L.h[r] = mx;
       hup = mx;
-      if (LOCAL) { hit |= mx >= L.best_v; v[r][j] = mx; }
+      if (LOCAL) {
+        int k = mx * 16 + ((3 - r) * 4 + (3 - j));
+        if (EDGE == 2 && c0 + j >= n) k = INT_MIN;
+        tkey = max(tkey, k);
+        v[r][j] = mx;
+      }
     }
     L.bot[j] = hup;
     if (EDGE == 2 && c0 + j + 1 == n) {
@@ -226,20 +230,7 @@ __device__ __forceinline__ void tile_step_stateful(TileLane &L, TileStateful &Z,
         if (yl0 + r + 1 == m) { L.corner = L.h[r]; L.has_corner = true; }
     }
   }
-  if (LOCAL && hit) {  // rare: first maximum in row-major order (simple/mod.rs:212)
-#pragma unroll
-    for (int r = 0; r < 4; ++r) {
-      const uint32_t y = yl0 + r + 1;
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const uint32_t x = c0 + j + 1;
-        const int w = v[r][j];
-        if (y <= m && x <= n && (w > L.best_v || (w == L.best_v && y < L.best_y))) {
-          L.best_v = w; L.best_y = y; L.best_x = x;
-        }
-      }
-    }
-  }
+  if ((tkey >> 2) > (L.best_key >> 2)) { L.best_key = tkey; L.best_ti = ti; }
   if (Z.last_band) {  // zeros of row m: the next pass's row 1 pays del one column later
     const uint32_t zr = m - 1u - yl0;  // the lane's row that is row m (>= 4: another lane's)
     uint32_t zm = 0;
@@ -294,15 +285,27 @@ __global__ void __launch_bounds__(32) fill_tile_kernel(BandArgs a) {
       L.h[r] = v;
     }
     __syncwarp();
-    for (uint32_t sym = 0; sym < V; ++sym)
-      sm_sc[sym * 32 + lane] = make_int4(__ldg(a.matrix + trow[0] + sym), __ldg(a.matrix + trow[1] + sym),
-                                         __ldg(a.matrix + trow[2] + sym), __ldg(a.matrix + trow[3] + sym));
+    for (uint32_t sym = 0; sym < V; ++sym) {
+      int4 sc = make_int4(__ldg(a.matrix + trow[0] + sym), __ldg(a.matrix + trow[1] + sym),
+                          __ldg(a.matrix + trow[2] + sym), __ldg(a.matrix + trow[3] + sym));
+      if (LOCAL) {
+        // rows past m (last band) must never hold the maximum: with these scores their cells stay
+        // below the cell of row m above them (they reach it only through top - pen)
+        constexpr int kNever = -(1 << 20);
+        if (yl0 + 1 > m) sc.x = kNever;
+        if (yl0 + 2 > m) sc.y = kNever;
+        if (yl0 + 3 > m) sc.z = kNever;
+        if (yl0 + 4 > m) sc.w = kNever;
+      }
+      sm_sc[sym * 32 + lane] = sc;
+    }
     L.diag0 = (LOCAL || yl0 == 0) ? 0 : -(int)yl0 * del;  // H[yl0][0]
 #pragma unroll
     for (int j = 0; j < 4; ++j) L.bot[j] = 0;
     L.qp = a.q;
     L.qw = tile_load_q4(L.qp);
     L.corner = 0; L.has_corner = false;
+    L.best_key = 15; L.best_ti = 0;  // value 0 with the best cell code: only a positive cell wins
     const int *top_row = band ? a.rows + (size_t)(band - 1) * npad : nullptr;
     const bool store_d = yl0 < m && a.D != nullptr;  // score-only calls pass no D scratch
     const bool last_band = band + 1 == a.nbands;
@@ -390,6 +393,12 @@ __global__ void __launch_bounds__(32) fill_tile_kernel(BandArgs a) {
       }
     }
     TILE_STAMP(5);
+    if (LOCAL && (L.best_key >> 4) > 0) {  // the band's best cell of this lane into the running arg-max
+      const int v = L.best_key >> 4;
+      const uint32_t y = yl0 + (3u - (((uint32_t)L.best_key >> 2) & 3u)) + 1u;
+      const uint32_t x = 4u * L.best_ti + (3u - ((uint32_t)L.best_key & 3u)) + 1u;
+      if (v > L.best_v || (v == L.best_v && y < L.best_y)) { L.best_v = v; L.best_y = y; L.best_x = x; }
+    }
     if (last_band && L.has_corner && !refill) *a.corner_out = L.corner;
     __syncwarp();
   }
