@@ -205,9 +205,11 @@ __device__ __forceinline__ void tile_step_stateful(TileLane &L, TileStateful &Z,
     int hup = up[j];
 #pragma unroll
     for (int r = 0; r < 4; ++r) {
-      int pen = (hup == 0) ? del : ext;
-      if (r == 0 && yl0 == 0) pen = ((dm4 >> j) & 1u) ? del : ext;  // H[0][x] is 0 by definition, not a Beginning
-      const int top = hup - pen, left = L.h[r] - pen, dg = diag + sc[r];
+      // both penalties are applied before the cell above is known to be a Beginning or not: the
+      // zero test then only selects (one level less on the step's dependent chain)
+      bool z = hup == 0;
+      if (r == 0 && yl0 == 0) z = ((dm4 >> j) & 1u) != 0;  // H[0][x] is 0 by definition, not a Beginning
+      const int top = z ? hup - del : hup - ext, left = z ? L.h[r] - del : L.h[r] - ext, dg = diag + sc[r];
       const int mx = max(max(top, left), dg);
       uint32_t code = (mx == left) ? DIR_LEFT : DIR_DIAGONAL;  // enums.rs:23/:41
       code = (mx == top) ? DIR_TOP : code;                     // enums.rs:21/:39
