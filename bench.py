@@ -49,6 +49,7 @@ def parse():
     ap.add_argument("--parity-pairs", type=int, default=4096, help="pairs of the timed batch checked against the oracle")
     ap.add_argument("--c4-len", type=int, default=100000)
     ap.add_argument("--c5-pairs", type=int, default=2000)
+    ap.add_argument("--protein-pairs", type=int, default=100000, help="side config: size of the protein batch")
     ap.add_argument("--c5-mats", type=int, default=100)
     return ap.parse_args()
 
@@ -281,6 +282,39 @@ def side_configs(a, lib, local, rank, world, int_peak, dist, torch):
                          "roofline": roof(cells, fill / 3e3), "cpu_port_gcups": out["c4_2e4"]["cpu_port_gcups"],
                          "hbm_d_write_gbs": cells * 0.25 / (fill / 3e3) / 1e9,
                          "what": "device-resident fill + traceback of one %d x %d pair" % (len(q), len(t))}
+
+        # ---- beyond BASELINE's five: a large PROTEIN batch (VERDICT: "no large-batch protein number
+        # exists"): 10^5 pairs of 270-330 aa, BLOSUM62, local, del=11 ext=2 — the INT32 one-warp-per-pair
+        # kernel (the packed 16-bit strip kernel is DNA-only), device-resident, with traceback
+        base = W.protein_pairs(0, min(a.protein_pairs, 20000), 270, 330)  # generated pair by pair on the host:
+        reps = max(1, a.protein_pairs // base.count)                       # 20 000 distinct pairs, repeated
+        lists = [base.pair(i) for i in range(base.count)] * reps
+        pp = ab.PackedPairs.from_lists([x[0] for x in lists], [x[1] for x in lists])
+        Mp = ab.get_blosum62()
+        db = ab.DeviceBatch(N.LOCAL, pp, Mp, 11, 2, device=local)
+        db.run_timed(1, profile_fill=False)
+        ms, _ = db.run_timed(3, profile_fill=False)
+        res = db.download()
+        db.close()
+        ns = min(256, pp.count)
+        sub = ab.PackedPairs.from_lists([lists[i][0] for i in range(ns)], [lists[i][1] for i in range(ns)])
+        t0 = time.perf_counter()
+        ref = O.align_batch("local", sub, 11.0, 2.0, Mp, threads=os.cpu_count() or 1)
+        cpu = time.perf_counter() - t0
+        okp = bool((res.f[:ns] == ref["f"]).all() and
+                   (np.asarray(res.coords[:ns]).reshape(ns, -1) == np.asarray(ref["coords"]).reshape(ns, -1)).all())
+        for i in range(0, ns, 7):
+            L = int(ref["aln_len"][i])
+            qa, ta = res.alignment(i)
+            okp = okp and len(qa) == L and bool((qa == ref["q_aln"][i, :L]).all() and (ta == ref["t_aln"][i, :L]).all())
+        qo, to = np.diff(pp.q_off), np.diff(pp.t_off)
+        cells = float((qo.astype(np.float64) * to).sum())
+        out["protein_batch"] = {"gcups": cells / (ms / 3e3) / 1e9, "ms": ms / 3, "parity": okp,
+                                "parity_how": "oracle on the first %d pairs (f, coords; every 7th string)" % ns,
+                                "roofline": roof(cells, ms / 3e3),
+                                "cpu_port_gcups": float((qo[:ns].astype(np.float64) * to[:ns]).sum()) / cpu / 1e9,
+                                "what": "not a BASELINE config: %d protein pairs of 270-330 aa, BLOSUM62, local, del=11 "
+                                        "ext=2, device-resident fill + traceback (INT32 warp kernel)" % pp.count}
 
     # ---- C5: heuristic matrix search, pairs sharded over the ranks, NCCL all-reduce of the block sums
     P, K = a.c5_pairs, a.c5_mats
