@@ -1,6 +1,7 @@
 #!/bin/bash
-# the round-end sequence on one GPU: every GPU test, then the bench record
+# the round-end sequence on one GPU: every GPU test, the smoke entry, then the bench record
 cd "$GRAFT_REPO_ROOT" 2>/dev/null || cd /root/repo
 O=gpurun_out
 timeout 1500 python -m pytest tests -m gpu -x -q > $O/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -4 $O/pytest_gpu.log
+timeout 300 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" 2>&1 | tail -2
 bash scripts/gpu_bench_n1.sh
