@@ -316,3 +316,37 @@ def test_stateful_local_score_only_and_in_batch():
         assert res.f[i] == ref["f"] == sc.f[i] and res.corner[i] == ref["corner"] == sc.corner[i]
         qa, ta = res.alignment(i)
         assert (qa == ref["q_aln"]).all() and (ta == ref["t_aln"]).all()
+
+
+@pytest.mark.parametrize("m,n", [(40, 140000), (140000, 36), (131, 33000), (4097, 1025)])
+def test_stateful_local_extreme_shapes(m, n, monkeypatch):
+    """Few columns, few rows, sizes around band / tile / map-word boundaries."""
+    rng = np.random.default_rng(m + n)
+    q = rng.integers(0, 4, n).astype(np.uint8)
+    t = rng.integers(0, 4, m).astype(np.uint8)
+    k = min(m, n)
+    t[:k] = np.where(rng.random(k) < 0.8, q[:k], t[:k])
+    M = ab.dna_matrix(2, -1)
+    ref = O.align_pair("local", q, t, 3.0, 1.0, M, lean=True)
+    monkeypatch.setenv("ALNR_WAVE_STATS", "1")
+    pairs = ab.PackedPairs.from_lists([q], [t])
+    db = ab.DeviceBatch(N.LOCAL, pairs, M, 3, 1)
+    db.run()
+    passes = db.rerun_count
+    res = db.download()
+    db.close()
+    assert 1 <= passes <= 8, passes
+    assert res.status[0] == ref["status"] == 0
+    assert res.f[0] == ref["f"] and res.corner[0] == ref["corner"]
+    qa, ta = res.alignment(0)
+    assert (qa == ref["q_aln"]).all() and (ta == ref["t_aln"]).all()
+
+
+def test_stateful_local_protein_long_pair():
+    pairs = W.protein_pairs(0, 1, 4300, 4300)
+    q, t = pairs.pair(0)
+    M = ab.get_blosum62()
+    ref = O.align_pair("local", q, t, 11.0, 1.0, M, lean=True)
+    r = ab.SimpleLocalAligner.from_seqs(q, t).perform_alignment(11, 1, M, want_matrices=False)
+    assert r.alignment.f == ref["f"] and r.corner_score == ref["corner"] and r.alignment.coords == ref["coords"]
+    assert (r.alignment.query == ref["q_aln"]).all() and (r.alignment.target == ref["t_aln"]).all()
