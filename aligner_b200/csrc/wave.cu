@@ -306,7 +306,8 @@ static int diff_run_pair(alnr_batch_impl &B, const Chunk &c, const DLayout &dl, 
   ALNR_CUDA(cudaMemsetAsync(B.d_band.p, 0, 16, B.stream));
   if (a.nbands > 1)  // every boundary value below row 0 starts as "not produced yet"
     ALNR_CUDA(cudaMemsetAsync(a.rows + a.npad, 0xff, (size_t)(a.nbands - 1) * a.npad * sizeof(uint16_t), B.stream));
-  const unsigned grid = std::min<unsigned>(a.nbands, resident);  // a waiter depends on lower bands only
+  unsigned grid = std::min<unsigned>(a.nbands, resident);  // a waiter depends on lower bands only
+  if (const char *e = std::getenv("ALNR_DIFF_GRID")) grid = std::min<unsigned>(grid, (unsigned)std::max(1, std::atoi(e)));
   fill_diff_kernel<<<grid, 32, 0, B.stream>>>(a);
   ALNR_LAUNCHED();
   diff_finish_kernel<<<1, 1, 0, B.stream>>>(a, fo, c.wave_pair);
