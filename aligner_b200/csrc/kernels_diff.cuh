@@ -263,12 +263,26 @@ __device__ __forceinline__ void diff_block(DiffLane &L, DiffBand &W, const DiffA
       /* other half still the preset in DRAM) waits for DRAM: the first half is therefore stored   */ \
       /* together with a sentinel second half, so that L2 always owns whole sectors.               */ \
       /* row_out + t0 = the group's first column t0 - 64; wraps while ramping up.                  */ \
+      /* The consumer asks for a group before it exists when it follows closely (every band's      */ \
+      /* ramp-up does): the NEXT sector is therefore written as sentinels too, or that early read   */ \
+      /* would fetch the preset from DRAM (~850 cycles; the rows outgrow L2 from n ~ 40 000 on).     */ \
+      const uint4 s4 = make_uint4(~0u, ~0u, ~0u, ~0u);                                                  \
       if (MODE == 0) {                                                                                  \
-        if (!(t0 & 8u)) __stcg(reinterpret_cast<uint4 *>(W.row_out + t0 + 8u), make_uint4(~0u, ~0u, ~0u, ~0u)); \
+        if (!(t0 & 8u)) {                                                                               \
+          __stcg(reinterpret_cast<uint4 *>(W.row_out + t0 + 8u), s4);                                   \
+          __stcg(reinterpret_cast<uint4 *>(W.row_out + t0 + 16u), s4);                                  \
+          __stcg(reinterpret_cast<uint4 *>(W.row_out + t0 + 24u), s4);                                  \
+        }                                                                                               \
         __stcg(reinterpret_cast<uint4 *>(W.row_out + t0), make_uint4(L.hv[0], L.hv[1], L.hv[2], L.hv[3])); \
       } else if (t0 - 64u < a.npad) { /* values of masked columns are garbage: never the sentinel */   \
         const uint32_t cap = 0xfffefffeu;                                                               \
-        if (!(t0 & 8u)) __stcg(reinterpret_cast<uint4 *>(W.row_out + t0 + 8u), make_uint4(~0u, ~0u, ~0u, ~0u)); \
+        if (!(t0 & 8u)) {                                                                               \
+          __stcg(reinterpret_cast<uint4 *>(W.row_out + t0 + 8u), s4);                                   \
+          if (t0 - 64u + 32u <= a.npad) {                                                               \
+            __stcg(reinterpret_cast<uint4 *>(W.row_out + t0 + 16u), s4);                                \
+            __stcg(reinterpret_cast<uint4 *>(W.row_out + t0 + 24u), s4);                                \
+          }                                                                                             \
+        }                                                                                               \
         __stcg(reinterpret_cast<uint4 *>(W.row_out + t0),                                               \
                make_uint4(__vminu2(L.hv[0], cap), __vminu2(L.hv[1], cap), __vminu2(L.hv[2], cap),       \
                           __vminu2(L.hv[3], cap)));                                                     \

@@ -278,15 +278,15 @@ static int diff_run_pair(alnr_batch_impl &B, const Chunk &c, const DLayout &dl, 
   }
   a.nbands = (a.m + kDiffBandRows - 1) / kDiffBandRows;
   a.npad = (a.n + 63) / 64 * 64;
-  // scratch: [pad 2][corner acc][pad][rows: nbands * npad 16-bit values][256 words of slack for the
+  // scratch: [pad 2][corner acc][pad to 128 bytes][rows: nbands * npad 16-bit values][256 words of slack for the
   // kernel's reads past the end of a row]
-  const size_t words = 4 + ((size_t)a.nbands * a.npad + 1) / 2 + 256;
+  const size_t words = 32 + ((size_t)a.nbands * a.npad + 1) / 2 + 256;
   if (B.d_band.n < words) {
     if (B.d_band.p) ALNR_CUDA(cudaStreamSynchronize(B.stream));  // an earlier pair may still use the old rows
     ALNR_CUDA(B.d_band.alloc(words));
   }
   a.corner_acc = B.d_band.p + 2;
-  a.rows = reinterpret_cast<uint16_t *>(B.d_band.p + 4);
+  a.rows = reinterpret_cast<uint16_t *>(B.d_band.p + 32);  // 128-byte aligned: a pair of groups is one 32-byte sector
   a.stamps = nullptr;
 #ifdef ALNR_DIFF_DEBUG
   static unsigned long long *d_stamps = nullptr;
