@@ -2,4 +2,4 @@
 cd "$GRAFT_REPO_ROOT" 2>/dev/null || cd /root/repo
 O=gpurun_out
 timeout 1500 python -m pytest tests -m gpu -x -q > $O/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -4 $O/pytest_gpu.log
-timeout 300 python scripts/stateful_probe.py 5000 50000 100000 2>&1 | tail -12
+timeout 300 python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -1
